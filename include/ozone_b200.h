@@ -1,0 +1,159 @@
+/*
+ * ozone_b200 -- C ABI of the B200-native solve-and-differentiate engine.
+ *
+ * The reference (LSDOlab/ozone) is pure Python and has NO native interface: its integrators
+ * hand every operation to csdl_alpha.  These entry points are therefore what a binding for the
+ * hot path WOULD bind; each one names the reference code it replaces (paths relative to the
+ * reference checkout).  INTEGRATION.md shows the ctypes stub a maintainer would add.
+ *
+ * Conventions
+ *   - every data pointer is a DEVICE pointer owned by the caller; the library never allocates
+ *     or frees user-visible memory.  Scratch comes from a caller-provided workspace whose size
+ *     is returned by the *_workspace_bytes query.
+ *   - `stream` is a cudaStream_t passed as void*; all work is enqueued on it, no host sync
+ *     unless stated.
+ *   - return value: 0 ok; < 0 invalid argument / CUDA error (text via oz_last_error()).
+ *     Numerical trouble (Newton / Picard not converged, non-finite) is reported per trajectory
+ *     in the `status` array, never by the return code.
+ *   - dtype: OZ_F64 or OZ_F32 selects the arithmetic AND storage type of every real array.
+ *
+ * Device layout (structure of arrays, trajectory index innermost):
+ *     y0      [d][N]            initial conditions                 (collections.py:175-182)
+ *     h       [n]  or [n][N]    step sizes        (h_shared = 1/0) (timespan.py:63-76)
+ *     p       [nt][P] or [nt][P][N]  dynamic parameters at the nt = n+1 grid points
+ *                               (p_shared = 1/0)                   (collections.py:239-249)
+ *     th      [S]  or [S][N]    static parameters (th_shared = 1/0)
+ *     hist    [nt][d][N]        state history incl. the IC row     (time_marching.py:120)
+ *     ckpt    [nc+1][d][N]      states at the checkpoint boundaries (time_marching_uniform.py:43,128)
+ *     prof    [nt][NPROF][N]    profile outputs                    (time_marching.py:97-122)
+ *     field   [NFIELD][N]       field outputs (sum over time)      (time_marching.py:104-112)
+ * For the grid right-hand side (OZ_RHS_DIFFUSION_REACTION) there is ONE trajectory whose
+ * components are the grid cells: N = 1 and d = nx (set in `d_override`).
+ */
+#ifndef OZONE_B200_H
+#define OZONE_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#if defined(__GNUC__)
+#define OZ_API __attribute__((visibility("default")))
+#else
+#define OZ_API
+#endif
+
+#define OZ_MAX_STAGES 7
+
+enum { OZ_F64 = 0, OZ_F32 = 1 };
+
+/* Registered device right-hand sides: the reference's Python callbacks restated as device
+ * functors behind func_wrapper (ozone/func_wrapper.py:90-107). */
+enum {
+    OZ_RHS_LOTKA_VOLTERRA = 0,      /* examples/simple_examples/lotka_volterra.py:51-62 */
+    OZ_RHS_VAN_DER_POL = 1,         /* ozone/paper_examples/van_der_pol/main_model.py:6-14 */
+    OZ_RHS_LUNAR_ASCENT = 2,        /* ozone/paper_examples/ascent_system/main_model.py:6-21 */
+    OZ_RHS_AFFINE = 3,              /* ozone/tests/test_correctness/test_1_simple/utils.py:6-7; tutorial.ipynb */
+    OZ_RHS_QUAD_DECAY = 4,          /* ozone/tests/test_correctness/test_3_large/utils.py:23-30 */
+    OZ_RHS_GENERAL3 = 5,            /* ozone/tests/test_correctness/test_2_general/utils.py:43-84 */
+    OZ_RHS_DIFFUSION_REACTION = 6,  /* ozone/paper_examples/pde_control/pde_control.py:11-81 */
+    OZ_RHS_COUNT = 7
+};
+
+enum { OZ_STATUS_OK = 0, OZ_STATUS_NOT_CONVERGED = 1, OZ_STATUS_SINGULAR = 2, OZ_STATUS_NONFINITE = 4 };
+
+/* One descriptor for the forward solve and its adjoint.  Unused pointers are NULL. */
+typedef struct oz_problem {
+    /* ---- method: ozone/glms/GLMs.py:19-42 (A, B, C = A.1, explicit flag); U = 1, V = 1 ---- */
+    int32_t rhs_id;
+    int32_t dtype;
+    int32_t num_stages;
+    int32_t is_explicit;
+    double A[OZ_MAX_STAGES * OZ_MAX_STAGES];   /* row-major, leading dimension OZ_MAX_STAGES */
+    double B[OZ_MAX_STAGES];
+    double C[OZ_MAX_STAGES];
+    /* ---- sizes ---- */
+    int64_t N;            /* trajectories */
+    int32_t n;            /* steps; nt = n + 1 */
+    int32_t num_inner;    /* checkpointing: inner steps per segment (time_marching_uniform.py:27); 0 = none */
+    int32_t h_shared, p_shared, th_shared;
+    int32_t d_override;   /* grid RHS only: number of cells nx */
+    /* ---- implicit stage solver: time_marching.py:217-221 (Newton, tolerance 1e-7) ---- */
+    double newton_tol;
+    int32_t newton_max_iter;
+    int32_t reserved0;
+    double rhs_cfg[8];    /* RHS constants that are not differentiated (grid RHS: dx, beta_t, beta_u, gamma) */
+    /* ---- inputs ---- */
+    const void* y0;
+    const void* h;
+    const void* p;
+    const void* th;
+    /* ---- forward outputs ---- */
+    void* hist;
+    void* ckpt;
+    void* yfinal;
+    void* prof;
+    void* field;
+    int32_t* status;      /* [N] OR-ed OZ_STATUS_* flags, or NULL */
+    int32_t* iters;       /* [N] total Newton iterations (implicit) / sweeps (Picard), or NULL */
+    /* ---- adjoint inputs: cotangents of the forward outputs ---- */
+    const void* hist_bar;
+    const void* final_bar;
+    const void* prof_bar;
+    const void* field_bar;
+    /* ---- adjoint outputs (gradients, same layout as the inputs; shared inputs get the sum) ---- */
+    void* y0_bar;
+    void* h_bar;
+    void* p_bar;
+    void* th_bar;
+    /* ---- scratch + stream ---- */
+    void* ws;
+    size_t ws_bytes;
+    void* stream;
+} oz_problem;
+
+/* Library / build identification. */
+OZ_API int oz_version(void);
+OZ_API const char* oz_last_error(void);
+
+/* Sizes of a registered right-hand side: what FuncWrapper discovers on its first call
+ * (ozone/func_wrapper.py:100-104).  kind: 0 = per-trajectory (batched), 1 = grid. */
+OZ_API int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfield, int* kind);
+
+/* Evaluate f (and the outputs) at `nodes` points: FuncWrapper.evaluate (ozone/func_wrapper.py:90-107).
+ * y [d][nodes], p [P][nodes], th [S] or [S][nodes]; dy [d][nodes], prof [NPROF][nodes], field [NFIELD][nodes]. */
+OZ_API int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* p, void* dy, void* prof, void* field);
+
+/* TimeMarching.integrate: ozone/integrators/time_marching.py:6-59 (loop), :143-245 (stages,
+ * explicit and Newton), :247-260 (update), :97-141 (outputs).  With num_inner > 0 it is
+ * TimeMarchingUniform.integrate (ozone/integrators/time_marching_uniform.py:7-150): only `ckpt`
+ * needs to be retained for the reverse sweep. */
+OZ_API int oz_tm_forward(const oz_problem* pb);
+
+/* Reverse sweep of the same loop: what csdl derives from the stacked loop
+ * (time_marching.py:51 stack_all=True; call sites examples/simple_examples/lotka_volterra.py:76-79,
+ * ozone/tests/run_ode.py:66-69).  Reads `hist` (or `ckpt` + recompute when num_inner > 0). */
+OZ_API size_t oz_tm_adjoint_workspace_bytes(const oz_problem* pb);
+OZ_API int oz_tm_adjoint(const oz_problem* pb);
+
+/* PicardIteration.solve: ozone/integrators/picard_iteration.py:9-65 (sweep), vector_based.py:33-53
+ * (outputs).  `guess` [n][d][N] or NULL (collections.py:125-133).  Writes hist/prof/field/yfinal,
+ * per-trajectory sweep counts in `iters`, OZ_STATUS_NOT_CONVERGED in `status`. */
+OZ_API size_t oz_picard_workspace_bytes(const oz_problem* pb);
+OZ_API int oz_picard_forward(const oz_problem* pb, const void* guess, double tol, int max_sweeps);
+
+/* Collocation.solve: ozone/integrators/collocation.py:33-50.  Y [n][s][d][N], y [n][d][N];
+ * c1 [n][s][d][N], c2 [n][d][N].  The VJP returns (dc)^T mu for an optimiser
+ * (ozone/tests/run_ode.py:49-58): Y_bar, y_bar plus pb->y0_bar/h_bar/p_bar/th_bar. */
+OZ_API int oz_colloc_residual(const oz_problem* pb, const void* Y, const void* y, void* c1, void* c2);
+OZ_API size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb);
+OZ_API int oz_colloc_vjp(const oz_problem* pb, const void* Y, const void* y, const void* mu1, const void* mu2,
+                  void* Y_bar, void* y_bar);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* OZONE_B200_H */

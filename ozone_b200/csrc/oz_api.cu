@@ -1,0 +1,162 @@
+// extern "C" boundary of liboz_b200.so (declared in include/ozone_b200.h).
+#include <cstdarg>
+#include "oz_common.cuh"
+#include "oz_rhs.cuh"
+#include "oz_tm_launch.cuh"
+
+namespace oz {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof(g_err), fmt, ap);
+    va_end(ap);
+}
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+    if (!cached[dev]) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+// one dispatcher per batched RHS (defined in oz_tm_<rhs>.cu)
+int tm_lotka_volterra(const oz_problem*, int, size_t*, const EvalArgs*);
+int tm_van_der_pol(const oz_problem*, int, size_t*, const EvalArgs*);
+int tm_lunar_ascent(const oz_problem*, int, size_t*, const EvalArgs*);
+int tm_affine(const oz_problem*, int, size_t*, const EvalArgs*);
+int tm_quad_decay(const oz_problem*, int, size_t*, const EvalArgs*);
+int tm_general3(const oz_problem*, int, size_t*, const EvalArgs*);
+// grid RHS (oz_pde.cu)
+int pde_dispatch(const oz_problem*, int, size_t*, const EvalArgs*);
+// parallel-in-time paths (oz_picard.cu, oz_colloc.cu)
+int picard_dispatch(const oz_problem*, int mode, size_t* ws_bytes, const void* guess, double tol, int max_sweeps);
+int colloc_dispatch(const oz_problem*, int mode, size_t* ws_bytes, const void* Y, const void* y, const void* mu1,
+                    const void* mu2, void* o1, void* o2);
+
+struct RhsInfo {
+    int d, P, S, nprof, nfield, kind;
+};
+static const RhsInfo kInfo[OZ_RHS_COUNT] = {
+    {RhsLotkaVolterra::D, RhsLotkaVolterra::P, RhsLotkaVolterra::S, RhsLotkaVolterra::NPROF, RhsLotkaVolterra::NFIELD, 0},
+    {RhsVanDerPol::D, RhsVanDerPol::P, RhsVanDerPol::S, RhsVanDerPol::NPROF, RhsVanDerPol::NFIELD, 0},
+    {RhsLunarAscent::D, RhsLunarAscent::P, RhsLunarAscent::S, RhsLunarAscent::NPROF, RhsLunarAscent::NFIELD, 0},
+    {RhsAffine::D, RhsAffine::P, RhsAffine::S, RhsAffine::NPROF, RhsAffine::NFIELD, 0},
+    {RhsQuadDecay::D, RhsQuadDecay::P, RhsQuadDecay::S, RhsQuadDecay::NPROF, RhsQuadDecay::NFIELD, 0},
+    {RhsGeneral3::D, RhsGeneral3::P, RhsGeneral3::S, RhsGeneral3::NPROF, RhsGeneral3::NFIELD, 0},
+    {-1, 1, 0, 0, 1, 1},  // diffusion-reaction: d = nx comes from d_override
+};
+
+static int check_problem(const oz_problem* pb) {
+    OZ_REQUIRE(pb != nullptr, "null problem descriptor");
+    OZ_REQUIRE(pb->rhs_id >= 0 && pb->rhs_id < OZ_RHS_COUNT, "unknown rhs_id %d", pb->rhs_id);
+    OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
+    OZ_REQUIRE(pb->num_stages >= 1 && pb->num_stages <= OZ_MAX_STAGES, "num_stages %d out of range", pb->num_stages);
+    OZ_REQUIRE(pb->N >= 1, "N must be >= 1 (got %lld)", (long long)pb->N);
+    OZ_REQUIRE(pb->n >= 1, "at least one step is required (got %d)", pb->n);
+    OZ_REQUIRE(pb->num_inner >= 0 && (pb->num_inner == 0 || pb->n % pb->num_inner == 0),
+               "number of steps (%d) must be divisible by the inner segment length (%d)", pb->n, pb->num_inner);
+    return 0;
+}
+
+static int route(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    switch (pb->rhs_id) {
+        case OZ_RHS_LOTKA_VOLTERRA: return tm_lotka_volterra(pb, mode, ws_bytes, ev);
+        case OZ_RHS_VAN_DER_POL: return tm_van_der_pol(pb, mode, ws_bytes, ev);
+        case OZ_RHS_LUNAR_ASCENT: return tm_lunar_ascent(pb, mode, ws_bytes, ev);
+        case OZ_RHS_AFFINE: return tm_affine(pb, mode, ws_bytes, ev);
+        case OZ_RHS_QUAD_DECAY: return tm_quad_decay(pb, mode, ws_bytes, ev);
+        case OZ_RHS_GENERAL3: return tm_general3(pb, mode, ws_bytes, ev);
+        case OZ_RHS_DIFFUSION_REACTION: return pde_dispatch(pb, mode, ws_bytes, ev);
+    }
+    set_error("unknown rhs_id %d", pb->rhs_id);
+    return -1;
+}
+
+}  // namespace oz
+
+using namespace oz;
+
+extern "C" {
+
+int oz_version(void) { return 100; }
+
+const char* oz_last_error(void) { return g_err; }
+
+int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfield, int* kind) {
+    OZ_REQUIRE(rhs_id >= 0 && rhs_id < OZ_RHS_COUNT, "unknown rhs_id %d", rhs_id);
+    const RhsInfo& r = kInfo[rhs_id];
+    if (d) *d = r.d;
+    if (P) *P = r.P;
+    if (S) *S = r.S;
+    if (nprof) *nprof = r.nprof;
+    if (nfield) *nfield = r.nfield;
+    if (kind) *kind = r.kind;
+    return 0;
+}
+
+int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* p, void* dy, void* prof, void* field) {
+    OZ_REQUIRE(pb != nullptr, "null problem descriptor");
+    OZ_REQUIRE(pb->rhs_id >= 0 && pb->rhs_id < OZ_RHS_COUNT, "unknown rhs_id %d", pb->rhs_id);
+    OZ_REQUIRE(nodes >= 0, "negative node count");
+    EvalArgs ev{nodes, y, p, dy, prof, field};
+    return route(pb, TM_RHS_EVAL, nullptr, &ev);
+}
+
+int oz_tm_forward(const oz_problem* pb) {
+    if (int rc = check_problem(pb)) return rc;
+    OZ_REQUIRE(pb->y0 && pb->h, "y0 and h are required");
+    return route(pb, TM_FORWARD, nullptr, nullptr);
+}
+
+size_t oz_tm_adjoint_workspace_bytes(const oz_problem* pb) {
+    if (check_problem(pb)) return (size_t)-1;
+    size_t bytes = 0;
+    if (route(pb, TM_ADJOINT_WS, &bytes, nullptr)) return (size_t)-1;
+    return bytes;
+}
+
+int oz_tm_adjoint(const oz_problem* pb) {
+    if (int rc = check_problem(pb)) return rc;
+    OZ_REQUIRE(pb->y0 && pb->h, "y0 and h are required");
+    return route(pb, TM_ADJOINT, nullptr, nullptr);
+}
+
+size_t oz_picard_workspace_bytes(const oz_problem* pb) {
+    if (check_problem(pb)) return (size_t)-1;
+    size_t bytes = 0;
+    if (picard_dispatch(pb, 1, &bytes, nullptr, 0.0, 0)) return (size_t)-1;
+    return bytes;
+}
+
+int oz_picard_forward(const oz_problem* pb, const void* guess, double tol, int max_sweeps) {
+    if (int rc = check_problem(pb)) return rc;
+    return picard_dispatch(pb, 0, nullptr, guess, tol, max_sweeps);
+}
+
+int oz_colloc_residual(const oz_problem* pb, const void* Y, const void* y, void* c1, void* c2) {
+    if (int rc = check_problem(pb)) return rc;
+    return colloc_dispatch(pb, 0, nullptr, Y, y, nullptr, nullptr, c1, c2);
+}
+
+size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb) {
+    if (check_problem(pb)) return (size_t)-1;
+    size_t bytes = 0;
+    if (colloc_dispatch(pb, 2, &bytes, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr)) return (size_t)-1;
+    return bytes;
+}
+
+int oz_colloc_vjp(const oz_problem* pb, const void* Y, const void* y, const void* mu1, const void* mu2, void* Y_bar,
+                  void* y_bar) {
+    if (int rc = check_problem(pb)) return rc;
+    return colloc_dispatch(pb, 1, nullptr, Y, y, mu1, mu2, Y_bar, y_bar);
+}
+
+}  // extern "C"

@@ -1,0 +1,541 @@
+// Fused general-linear-method time-marching kernels (forward + reverse sweep), one trajectory
+// per thread, batch innermost in memory so a warp's 32 trajectories read/write 32 consecutive
+// scalars.  State, stage values, Newton iterates and the tableau never touch HBM.
+//
+//   forward  : ozone/integrators/time_marching.py:6-59, :143-260  (+ time_marching_uniform.py for checkpoints)
+//   adjoint  : the reverse sweep csdl derives from that loop (call sites lotka_volterra.py:76-79, run_ode.py:66-69)
+#pragma once
+#include "oz_common.cuh"
+#include "oz_linalg.cuh"
+
+namespace oz {
+
+template <class R>
+struct Dims {
+    static constexpr int D = R::D, P = R::P, SP = R::S, NP = R::NPROF, NF = R::NFIELD;
+    static constexpr int P1 = AtLeast1<P>::value, S1 = AtLeast1<SP>::value, NP1 = AtLeast1<NP>::value,
+                         NF1 = AtLeast1<NF>::value;
+};
+
+// row `row` of a [rows][N] (per trajectory) or [rows] (shared) array
+template <typename T>
+OZ_D T ld_in(const T* base, long long row, long long N, long long i, int shared) {
+    return shared ? __ldg(base + row) : __ldg(base + row * N + i);
+}
+
+template <class R, typename T>
+OZ_D void load_params(const TmArgs<T>& a, int k, long long i, T* p) {
+#pragma unroll
+    for (int c = 0; c < R::P; ++c) p[c] = ld_in(a.p, (long long)k * R::P + c, a.N, i, a.p_shared);
+}
+
+// stage-abscissa interpolation, ozone/collections.py:277-289
+template <class R, typename T, int S>
+OZ_D void stage_params(const Tableau<T>& tab, const T* plo, const T* phi, T (*ps)[Dims<R>::P1]) {
+#pragma unroll
+    for (int s = 0; s < S; ++s)
+#pragma unroll
+        for (int c = 0; c < R::P; ++c) ps[s][c] = plo[c] * (T(1) - tab.C[s]) + phi[c] * tab.C[s];
+}
+
+// ---------------------------------------------------------------------------------------------
+// Stage solve.  Explicit: time_marching.py:154-188.  Implicit: Newton on
+// R(Y) = Y - (A (x) I) h F(Y) - 1 (x) y, initial value 1 (x) y, residual tested before each update
+// (time_marching.py:189-243).  On return F holds f at the final stage values Y.
+template <class R, typename T, int S, bool IMPL>
+OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R>::P1], const T* th,
+                       T (*Y)[R::D], T (*F)[R::D], unsigned char* smem, int& status, int& iters) {
+    constexpr int D = R::D;
+    const Tableau<T>& tab = a.tab;
+    if constexpr (!IMPL) {
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+#pragma unroll
+            for (int c = 0; c < D; ++c) {
+                T acc = T(0);
+#pragma unroll
+                for (int j = 0; j < i; ++j) acc += tab.a(i, j) * F[j][c];
+                Y[i][c] = y[c] + h * acc;
+            }
+            R::f(Y[i], ps[i], th, F[i]);
+        }
+    } else {
+        constexpr int M = S * D;
+        using Sys = SmemSystem<T, M>;
+        Sys sys = Sys::carve(smem, blockDim.x, threadIdx.x);
+#pragma unroll
+        for (int i = 0; i < S; ++i)
+#pragma unroll
+            for (int c = 0; c < D; ++c) Y[i][c] = y[c];
+        for (int it = 0;; ++it) {
+#pragma unroll
+            for (int i = 0; i < S; ++i) R::f(Y[i], ps[i], th, F[i]);
+            T rn2 = T(0);
+#pragma unroll
+            for (int i = 0; i < S; ++i)
+#pragma unroll
+                for (int c = 0; c < D; ++c) {
+                    T acc = T(0);
+#pragma unroll
+                    for (int j = 0; j < S; ++j) acc += tab.a(i, j) * F[j][c];
+                    const T r = Y[i][c] - h * acc - y[c];
+                    sys.v(i * D + c) = -r;
+                    rn2 += r * r;
+                }
+            if (!(rn2 == rn2)) {  // NaN: give up, flag
+                status |= OZ_STATUS_NONFINITE;
+                break;
+            }
+            if (sqrt(rn2) < a.newton_tol) break;
+            if (it >= a.newton_max_iter) {
+                status |= OZ_STATUS_NOT_CONVERGED;
+                break;
+            }
+            // Newton matrix: block (i, j) = delta_ij I - h a_ij J_f(Y_j)
+#pragma unroll
+            for (int j = 0; j < S; ++j) {
+                T J[D * D];
+                R::jac(Y[j], ps[j], th, J);
+#pragma unroll
+                for (int i = 0; i < S; ++i) {
+                    const T ha = h * tab.a(i, j);
+#pragma unroll
+                    for (int r = 0; r < D; ++r)
+#pragma unroll
+                        for (int c = 0; c < D; ++c)
+                            sys.m(i * D + r, j * D + c) = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+                }
+            }
+            if (!sys.factor()) {
+                status |= OZ_STATUS_SINGULAR;
+                break;
+            }
+            sys.solve();
+#pragma unroll
+            for (int i = 0; i < S; ++i)
+#pragma unroll
+                for (int c = 0; c < D; ++c) Y[i][c] += sys.v(i * D + c);
+            ++iters;
+        }
+    }
+}
+
+// y+ = y + h sum_i b_i F_i   (time_marching.py:247-260, V = 1)
+template <class R, typename T, int S>
+OZ_D void advance(const Tableau<T>& tab, T* y, T h, const T (*F)[R::D]) {
+#pragma unroll
+    for (int c = 0; c < R::D; ++c) {
+        T acc = T(0);
+#pragma unroll
+        for (int i = 0; i < S; ++i) acc += tab.B[i] * F[i][c];
+        y[c] += h * acc;
+    }
+}
+
+// =============================================================================================
+template <class R, typename T, int S, bool IMPL>
+__global__ void __launch_bounds__(128) tm_forward_kernel(const TmArgs<T> a) {
+    using DM = Dims<R>;
+    constexpr int D = DM::D;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= a.N) return;
+    const long long N = a.N;
+
+    T y[D], th[DM::S1], plo[DM::P1], phi[DM::P1], ps[S][DM::P1], Y[S][D], F[S][D];
+    T prof[DM::NP1], fld[DM::NF1], facc[DM::NF1];
+#pragma unroll
+    for (int c = 0; c < D; ++c) y[c] = __ldg(a.y0 + c * N + i);
+#pragma unroll
+    for (int c = 0; c < DM::SP; ++c) th[c] = ld_in(a.th, c, N, i, a.th_shared);
+    load_params<R>(a, 0, i, plo);
+    int status = 0, iters = 0;
+
+    if (a.hist)
+#pragma unroll
+        for (int c = 0; c < D; ++c) a.hist[c * N + i] = y[c];
+    if (a.ckpt)
+#pragma unroll
+        for (int c = 0; c < D; ++c) a.ckpt[c * N + i] = y[c];
+    constexpr bool HAS_OUT = (DM::NP + DM::NF) > 0;
+    if constexpr (HAS_OUT) {  // outputs at the initial condition (time_marching.py:104-112)
+        R::out(y, plo, th, prof, facc);
+        if (a.prof)
+#pragma unroll
+            for (int c = 0; c < DM::NP; ++c) a.prof[c * N + i] = prof[c];
+    }
+
+    for (int k = 0; k < a.n; ++k) {
+        const T h = ld_in(a.h, k, N, i, a.h_shared);
+        load_params<R>(a, k + 1, i, phi);
+        stage_params<R, T, S>(a.tab, plo, phi, ps);
+        solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
+        advance<R, T, S>(a.tab, y, h, F);
+        if (a.hist)
+#pragma unroll
+            for (int c = 0; c < D; ++c) a.hist[((long long)(k + 1) * D + c) * N + i] = y[c];
+        if (a.ckpt && a.num_inner > 0 && (k + 1) % a.num_inner == 0) {
+            const long long o = (k + 1) / a.num_inner;
+#pragma unroll
+            for (int c = 0; c < D; ++c) a.ckpt[(o * D + c) * N + i] = y[c];
+        }
+        if constexpr (HAS_OUT) {  // raw grid-point parameters (time_marching.py:30-32)
+            R::out(y, phi, th, prof, fld);
+            if (a.prof)
+#pragma unroll
+                for (int c = 0; c < DM::NP; ++c) a.prof[((long long)(k + 1) * DM::NP + c) * N + i] = prof[c];
+#pragma unroll
+            for (int c = 0; c < DM::NF; ++c) facc[c] += fld[c];
+        }
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) plo[c] = phi[c];
+    }
+    if (a.yfinal)
+#pragma unroll
+        for (int c = 0; c < D; ++c) a.yfinal[c * N + i] = y[c];
+    if constexpr (DM::NF > 0) {
+        if (a.field)
+#pragma unroll
+            for (int c = 0; c < DM::NF; ++c) a.field[c * N + i] = facc[c];
+    }
+    if (a.status) a.status[i] = status;
+    if (a.iters) a.iters[i] = iters;
+}
+
+// =============================================================================================
+// Adjoint scratch layout (units of T):
+//   [ rows_h * W | rows_p * W | rows_th * W | segment states ni * D * N ]
+// where rows_x = number of scalars of a batch-SHARED input x (0 if per trajectory), W = warps in
+// the grid.  Each warp writes its shuffle-reduced partial; reduce_rows_kernel sums the W partials
+// in a fixed order, so shared-input gradients are deterministic (no fp atomics).
+struct AdjWs {
+    long long W, rows_h, rows_p, rows_th, seg_elems;
+    long long off_h, off_p, off_th, off_seg, total;
+};
+
+template <class R>
+inline AdjWs tm_adjoint_ws_layout(const oz_problem* pb, int block) {
+    AdjWs w;
+    const long long nblocks = (pb->N + block - 1) / block;
+    w.W = nblocks * (block / 32);
+    w.rows_h = (pb->h_shared && pb->h_bar) ? pb->n : 0;
+    w.rows_p = (pb->p_shared && pb->p_bar) ? (long long)(pb->n + 1) * R::P : 0;
+    w.rows_th = (pb->th_shared && pb->th_bar) ? R::S : 0;
+    w.seg_elems = (pb->num_inner > 0 && !pb->hist) ? (long long)pb->num_inner * R::D * pb->N : 0;
+    w.off_h = 0;
+    w.off_p = w.off_h + w.rows_h * w.W;
+    w.off_th = w.off_p + w.rows_p * w.W;
+    w.off_seg = w.off_th + w.rows_th * w.W;
+    w.off_seg = (w.off_seg + 31) / 32 * 32;
+    w.total = w.off_seg + w.seg_elems;
+    return w;
+}
+
+template <typename T>
+struct AdjWsPtr {
+    T* h;
+    T* p;
+    T* th;
+    T* seg;
+    long long W;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(256) reduce_rows_kernel(const T* __restrict__ part, long long W, T* __restrict__ out) {
+    __shared__ T sm[256];
+    const long long row = blockIdx.x;
+    T acc = T(0);
+    for (long long w = threadIdx.x; w < W; w += 256) acc += part[row * W + w];
+    sm[threadIdx.x] = acc;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if (threadIdx.x < s) sm[threadIdx.x] += sm[threadIdx.x + s];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) out[row] = sm[0];
+}
+
+// One reverse step.  In: y = y_k, lam = dL/dy_{k+1}.  Out: lam = dL/dy_k (without direct
+// cotangents of y_k), hb, pb_lo / pb_hi (contributions to p_bar[k] / p_bar[k+1]), tb +=.
+//   G_i = h b_i lam + h sum_j a_ji Ybar_j,  Ybar_j = J_y(Y_j)^T G_j
+//   explicit: back-substitution i = S-1..0;  implicit: M^T Ybar = blk(J^T)(h b (x) lam), M the Newton matrix
+template <class R, typename T, int S, bool IMPL>
+OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R>::P1], const T* th, T* lam,
+                       T& hb, T* pb_lo, T* pb_hi, T* tb, unsigned char* smem, int& status, int& iters) {
+    using DM = Dims<R>;
+    constexpr int D = DM::D;
+    const Tableau<T>& tab = a.tab;
+    T Y[S][D], F[S][D], Yb[S][D];
+    solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
+
+    if constexpr (IMPL) {
+        constexpr int M = S * D;
+        using Sys = SmemSystem<T, M>;
+        Sys sys = Sys::carve(smem, blockDim.x, threadIdx.x);
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            T J[D * D];
+            R::jac(Y[j], ps[j], th, J);
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
+                const T ha = h * tab.a(i, j);
+#pragma unroll
+                for (int r = 0; r < D; ++r)
+#pragma unroll
+                    for (int c = 0; c < D; ++c)
+                        sys.m(i * D + r, j * D + c) = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+            }
+            // right-hand side block j:  J_j^T (h b_j lam)
+#pragma unroll
+            for (int c = 0; c < D; ++c) {
+                T acc = T(0);
+#pragma unroll
+                for (int r = 0; r < D; ++r) acc += J[r * D + c] * lam[r];
+                sys.v(j * D + c) = h * tab.B[j] * acc;
+            }
+        }
+        if (!sys.factor()) status |= OZ_STATUS_SINGULAR;
+        sys.solve_transposed();
+#pragma unroll
+        for (int i = 0; i < S; ++i)
+#pragma unroll
+            for (int c = 0; c < D; ++c) Yb[i][c] = sys.v(i * D + c);
+    }
+
+    hb = T(0);
+#pragma unroll
+    for (int c = 0; c < DM::P; ++c) {
+        pb_lo[c] = T(0);
+        pb_hi[c] = T(0);
+    }
+#pragma unroll
+    for (int i = S - 1; i >= 0; --i) {
+        T G[D], pbi[DM::P1];
+#pragma unroll
+        for (int c = 0; c < DM::P1; ++c) pbi[c] = T(0);
+#pragma unroll
+        for (int c = 0; c < D; ++c) {
+            T acc = tab.B[i] * lam[c];
+            if constexpr (IMPL) {
+#pragma unroll
+                for (int j = 0; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
+            } else {
+#pragma unroll
+                for (int j = i + 1; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
+            }
+            G[c] = h * acc;
+        }
+        if constexpr (IMPL) {
+            T dummy[D];
+#pragma unroll
+            for (int c = 0; c < D; ++c) dummy[c] = T(0);
+            R::vjp(Y[i], ps[i], th, G, dummy, pbi, tb);
+        } else {
+#pragma unroll
+            for (int c = 0; c < D; ++c) Yb[i][c] = T(0);
+            R::vjp(Y[i], ps[i], th, G, Yb[i], pbi, tb);
+        }
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) {
+            pb_lo[c] += (T(1) - tab.C[i]) * pbi[c];
+            pb_hi[c] += tab.C[i] * pbi[c];
+        }
+    }
+    // h_bar = sum_i b_i F_i . lam + sum_i Ybar_i . sum_j a_ij F_j   (no division by h: h = 0 is legal)
+#pragma unroll
+    for (int c = 0; c < D; ++c) {
+        T accb = T(0);
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+            accb += tab.B[i] * F[i][c];
+            T af = T(0);
+            if constexpr (IMPL) {
+#pragma unroll
+                for (int j = 0; j < S; ++j) af += tab.a(i, j) * F[j][c];
+            } else {
+#pragma unroll
+                for (int j = 0; j < i; ++j) af += tab.a(i, j) * F[j][c];
+            }
+            hb += Yb[i][c] * af;
+        }
+        hb += accb * lam[c];
+    }
+#pragma unroll
+    for (int c = 0; c < D; ++c) {
+        T acc = T(0);
+#pragma unroll
+        for (int i = 0; i < S; ++i) acc += Yb[i][c];
+        lam[c] += acc;
+    }
+}
+
+template <class R, typename T, int S, bool IMPL>
+__global__ void __launch_bounds__(128) tm_adjoint_kernel(const TmArgs<T> a, const AdjWsPtr<T> ws) {
+    using DM = Dims<R>;
+    constexpr int D = DM::D;
+    constexpr bool HAS_OUT = (DM::NP + DM::NF) > 0;
+    extern __shared__ __align__(16) unsigned char smem[];
+    const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool valid = gi < a.N;
+    const long long i = valid ? gi : a.N - 1;  // idle lanes shadow the last trajectory and never store
+    const long long N = a.N;
+    const long long warp = gi >> 5;
+    const int lane = threadIdx.x & 31;
+    const int n = a.n;
+
+    T th[DM::S1], tb[DM::S1], lam[D], y[D], plo[DM::P1], phi[DM::P1], ps[S][DM::P1];
+    T pb_next[DM::P1], pb_lo[DM::P1], pb_hi[DM::P1], vf[DM::NF1], vp[DM::NP1];
+    int status = 0, iters = 0;
+#pragma unroll
+    for (int c = 0; c < DM::SP; ++c) th[c] = ld_in(a.th, c, N, i, a.th_shared);
+#pragma unroll
+    for (int c = 0; c < DM::S1; ++c) tb[c] = T(0);
+#pragma unroll
+    for (int c = 0; c < DM::P1; ++c) pb_next[c] = T(0);
+#pragma unroll
+    for (int c = 0; c < DM::NF; ++c) vf[c] = a.field_bar ? __ldg(a.field_bar + c * N + i) : T(0);
+
+    const bool use_seg = (a.num_inner > 0) && (a.hist == nullptr);
+    auto state_ptr = [&](int k) -> const T* {  // where y_k lives
+        if (!use_seg) return a.hist + (long long)k * D * N;
+        return ws.seg + (long long)(k % a.num_inner) * D * N;
+    };
+    auto emit_p = [&](int k) {  // p_bar[k] is complete
+        if (!a.p_bar) return;
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) {
+            if (a.p_shared) {
+                const T s = warp_sum(valid ? pb_next[c] : T(0));
+                if (lane == 0) ws.p[((long long)k * DM::P + c) * ws.W + warp] = s;
+            } else if (valid) {
+                a.p_bar[((long long)k * DM::P + c) * N + i] = pb_next[c];
+            }
+        }
+    };
+    // direct cotangents of y_k: history row, profile/field outputs evaluated at (y_k, p[k])
+    auto direct = [&](int k, const T* yk, const T* pk) {
+        if (a.hist_bar)
+#pragma unroll
+            for (int c = 0; c < D; ++c) lam[c] += __ldg(a.hist_bar + ((long long)k * D + c) * N + i);
+        if constexpr (HAS_OUT) {
+#pragma unroll
+            for (int c = 0; c < DM::NP; ++c)
+                vp[c] = a.prof_bar ? __ldg(a.prof_bar + ((long long)k * DM::NP + c) * N + i) : T(0);
+            R::out_vjp(yk, pk, th, vp, vf, lam, pb_next, tb);
+        }
+    };
+
+    // ---- terminal condition: lam = dL/dy_n
+#pragma unroll
+    for (int c = 0; c < D; ++c) lam[c] = a.final_bar ? __ldg(a.final_bar + c * N + i) : T(0);
+    load_params<R>(a, n, i, phi);
+    if constexpr (HAS_OUT) {
+        const T* src = use_seg ? a.ckpt + (long long)(n / a.num_inner) * D * N : a.hist + (long long)n * D * N;
+#pragma unroll
+        for (int c = 0; c < D; ++c) y[c] = __ldg(src + c * N + i);
+    }
+    direct(n, y, phi);
+
+    const int ni = use_seg ? a.num_inner : n;
+    const int nseg = use_seg ? n / a.num_inner : 1;
+    for (int o = nseg - 1; o >= 0; --o) {
+        const int lo = o * ni;
+        if (use_seg) {
+            // recompute the inner states of this segment from its checkpoint
+            // (time_marching_uniform.py:77-125: the inner loop is not stacked)
+            T Y[S][D], F[S][D], qlo[DM::P1], qhi[DM::P1];
+#pragma unroll
+            for (int c = 0; c < D; ++c) y[c] = __ldg(a.ckpt + ((long long)o * D + c) * N + i);
+            load_params<R>(a, lo, i, qlo);
+            for (int q = 0; q < ni; ++q) {
+                if (valid)
+#pragma unroll
+                    for (int c = 0; c < D; ++c) ws.seg[((long long)q * D + c) * N + i] = y[c];
+                if (q == ni - 1) break;
+                const T h = ld_in(a.h, lo + q, N, i, a.h_shared);
+                load_params<R>(a, lo + q + 1, i, qhi);
+                stage_params<R, T, S>(a.tab, qlo, qhi, ps);
+                int st2 = 0, it2 = 0;
+                solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, st2, it2);
+                advance<R, T, S>(a.tab, y, h, F);
+#pragma unroll
+                for (int c = 0; c < DM::P; ++c) qlo[c] = qhi[c];
+            }
+        }
+        for (int k = lo + ni - 1; k >= lo; --k) {
+            const T* src = state_ptr(k);
+#pragma unroll
+            for (int c = 0; c < D; ++c) y[c] = use_seg ? src[c * N + i] : __ldg(src + c * N + i);
+            const T h = ld_in(a.h, k, N, i, a.h_shared);
+            load_params<R>(a, k, i, plo);
+            stage_params<R, T, S>(a.tab, plo, phi, ps);
+            T hb;
+            adjoint_step<R, T, S, IMPL>(a, y, h, ps, th, lam, hb, pb_lo, pb_hi, tb, smem, status, iters);
+#pragma unroll
+            for (int c = 0; c < DM::P; ++c) pb_next[c] += pb_hi[c];
+            emit_p(k + 1);
+#pragma unroll
+            for (int c = 0; c < DM::P; ++c) pb_next[c] = pb_lo[c];
+            if (a.h_bar) {
+                if (a.h_shared) {
+                    const T s = warp_sum(valid ? hb : T(0));
+                    if (lane == 0) ws.h[(long long)k * ws.W + warp] = s;
+                } else if (valid) {
+                    a.h_bar[(long long)k * N + i] = hb;
+                }
+            }
+            direct(k, y, plo);
+#pragma unroll
+            for (int c = 0; c < DM::P; ++c) phi[c] = plo[c];
+        }
+    }
+    emit_p(0);
+    if (a.y0_bar && valid)
+#pragma unroll
+        for (int c = 0; c < D; ++c) a.y0_bar[c * N + i] = lam[c];
+    if (a.th_bar) {
+#pragma unroll
+        for (int c = 0; c < DM::SP; ++c) {
+            if (a.th_shared) {
+                const T s = warp_sum(valid ? tb[c] : T(0));
+                if (lane == 0) ws.th[(long long)c * ws.W + warp] = s;
+            } else if (valid) {
+                a.th_bar[c * N + i] = tb[c];
+            }
+        }
+    }
+    if (a.status && valid && status) atomicOr(a.status + i, status);
+}
+
+// =============================================================================================
+// FuncWrapper.evaluate (ozone/func_wrapper.py:90-107) for `nodes` points.
+template <class R, typename T>
+__global__ void __launch_bounds__(128) rhs_eval_kernel(long long nodes, int th_shared, const T* __restrict__ y,
+                                                       const T* __restrict__ p, const T* __restrict__ th,
+                                                       T* __restrict__ dy, T* __restrict__ prof, T* __restrict__ field) {
+    using DM = Dims<R>;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nodes) return;
+    T yy[DM::D], pp[DM::P1], tt[DM::S1], d[DM::D], pr[DM::NP1], fl[DM::NF1];
+#pragma unroll
+    for (int c = 0; c < DM::D; ++c) yy[c] = y[c * nodes + i];
+#pragma unroll
+    for (int c = 0; c < DM::P; ++c) pp[c] = p[c * nodes + i];
+#pragma unroll
+    for (int c = 0; c < DM::SP; ++c) tt[c] = th_shared ? th[c] : th[c * nodes + i];
+    R::f(yy, pp, tt, d);
+    if (dy)
+#pragma unroll
+        for (int c = 0; c < DM::D; ++c) dy[c * nodes + i] = d[c];
+    if constexpr ((DM::NP + DM::NF) > 0) {
+        R::out(yy, pp, tt, pr, fl);
+        if (prof)
+#pragma unroll
+            for (int c = 0; c < DM::NP; ++c) prof[c * nodes + i] = pr[c];
+        if (field)
+#pragma unroll
+            for (int c = 0; c < DM::NF; ++c) field[c * nodes + i] = fl[c];
+    }
+}
+
+}  // namespace oz

@@ -1,0 +1,129 @@
+// Host-side launch + (stage count, explicit/implicit, dtype) dispatch for one right-hand side.
+// Each oz_tm_<rhs>.cu instantiates dispatch_tm<R> so the RHS files compile in parallel.
+#pragma once
+#include "oz_tm_kernels.cuh"
+
+namespace oz {
+
+enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3 };
+
+struct EvalArgs {
+    long long nodes;
+    const void *y, *p;
+    void *dy, *prof, *field;
+};
+
+constexpr size_t kSmemBudget = 200 * 1024;
+
+template <class R, typename T, int S, bool IMPL>
+int pick_block(size_t* smem) {
+    if constexpr (!IMPL) {
+        *smem = 0;
+        return 128;
+    } else {
+        const size_t per = SmemSystem<T, S * R::D>::bytes_per_thread();
+        int block = 64;
+        while (block > 32 && per * block > kSmemBudget) block >>= 1;
+        *smem = per * block;
+        return per * block <= 227 * 1024 ? block : -1;
+    }
+}
+
+template <class R, typename T, int S, bool IMPL>
+int run_tm(const oz_problem* pb, int mode, size_t* ws_bytes) {
+    size_t smem = 0;
+    const int block = pick_block<R, T, S, IMPL>(&smem);
+    OZ_REQUIRE(block > 0, "implicit system of %d unknowns per step does not fit in shared memory", S * R::D);
+    cudaStream_t stream = (cudaStream_t)pb->stream;
+    const long long nblocks = (pb->N + block - 1) / block;
+    OZ_REQUIRE(nblocks < (1ll << 31), "batch too large for one launch");
+    TmArgs<T> a = make_tm_args<T>(pb);
+
+    if (mode == TM_FORWARD) {
+        auto kern = tm_forward_kernel<R, T, S, IMPL>;
+        if (smem > 48 * 1024)
+            OZ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)nblocks, block, smem, stream>>>(a);
+        OZ_CUDA_CHECK(cudaGetLastError());
+        return 0;
+    }
+    const AdjWs w = tm_adjoint_ws_layout<R>(pb, block);
+    if (mode == TM_ADJOINT_WS) {
+        *ws_bytes = (size_t)w.total * sizeof(T);
+        return 0;
+    }
+    OZ_REQUIRE(pb->hist || (pb->ckpt && pb->num_inner > 0), "adjoint needs hist, or ckpt with num_inner > 0");
+    OZ_REQUIRE((size_t)w.total * sizeof(T) <= pb->ws_bytes && (w.total == 0 || pb->ws),
+               "adjoint workspace too small: need %zu bytes, got %zu", (size_t)w.total * sizeof(T), pb->ws_bytes);
+    a.W = w.W;
+    AdjWsPtr<T> wp;
+    wp.h = a.ws + w.off_h;
+    wp.p = a.ws + w.off_p;
+    wp.th = a.ws + w.off_th;
+    wp.seg = a.ws + w.off_seg;
+    wp.W = w.W;
+    auto kern = tm_adjoint_kernel<R, T, S, IMPL>;
+    if (smem > 48 * 1024)
+        OZ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    kern<<<(unsigned)nblocks, block, smem, stream>>>(a, wp);
+    OZ_CUDA_CHECK(cudaGetLastError());
+    if (w.rows_h) reduce_rows_kernel<T><<<(unsigned)w.rows_h, 256, 0, stream>>>(wp.h, w.W, a.h_bar);
+    if (w.rows_p) reduce_rows_kernel<T><<<(unsigned)w.rows_p, 256, 0, stream>>>(wp.p, w.W, a.p_bar);
+    if (w.rows_th) reduce_rows_kernel<T><<<(unsigned)w.rows_th, 256, 0, stream>>>(wp.th, w.W, a.th_bar);
+    OZ_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+template <class R, typename T>
+int dispatch_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
+    const int s = pb->num_stages;
+    if (pb->is_explicit) {
+        switch (s) {
+            case 1: return run_tm<R, T, 1, false>(pb, mode, ws_bytes);
+            case 2: return run_tm<R, T, 2, false>(pb, mode, ws_bytes);
+            case 3: return run_tm<R, T, 3, false>(pb, mode, ws_bytes);
+            case 4: return run_tm<R, T, 4, false>(pb, mode, ws_bytes);
+            case 7: return run_tm<R, T, 7, false>(pb, mode, ws_bytes);
+        }
+    } else {
+        switch (s) {
+            case 1: return run_tm<R, T, 1, true>(pb, mode, ws_bytes);
+            case 2: return run_tm<R, T, 2, true>(pb, mode, ws_bytes);
+            case 3: return run_tm<R, T, 3, true>(pb, mode, ws_bytes);
+        }
+    }
+    set_error("no kernel for %s method with %d stages", pb->is_explicit ? "an explicit" : "an implicit", s);
+    return -1;
+}
+
+template <class R>
+int dispatch_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    if (mode == TM_RHS_EVAL) {
+        cudaStream_t stream = (cudaStream_t)pb->stream;
+        const unsigned grid = (unsigned)((ev->nodes + 127) / 128);
+        if (grid == 0) return 0;
+        if (pb->dtype == OZ_F64)
+            rhs_eval_kernel<R, double><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const double*)ev->y,
+                                                               (const double*)ev->p, (const double*)pb->th,
+                                                               (double*)ev->dy, (double*)ev->prof, (double*)ev->field);
+        else
+            rhs_eval_kernel<R, float><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const float*)ev->y,
+                                                              (const float*)ev->p, (const float*)pb->th, (float*)ev->dy,
+                                                              (float*)ev->prof, (float*)ev->field);
+        OZ_CUDA_CHECK(cudaGetLastError());
+        return 0;
+    }
+    if (pb->dtype == OZ_F64) return dispatch_stage<R, double>(pb, mode, ws_bytes);
+    if (pb->dtype == OZ_F32) return dispatch_stage<R, float>(pb, mode, ws_bytes);
+    set_error("unknown dtype %d", pb->dtype);
+    return -1;
+}
+
+}  // namespace oz
+
+#define OZ_INSTANTIATE_TM(RHS, FN)                                                                     \
+    namespace oz {                                                                                     \
+    int FN(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {                     \
+        return dispatch_tm<RHS>(pb, mode, ws_bytes, ev);                                               \
+    }                                                                                                  \
+    }

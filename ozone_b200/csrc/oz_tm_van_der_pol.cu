@@ -1,0 +1,5 @@
+// Time-marching kernels (forward + reverse sweep, all stage counts, fp64 + fp32) for one
+// registered right-hand side.  One translation unit per RHS so the build parallelises.
+#include "oz_rhs.cuh"
+#include "oz_tm_launch.cuh"
+OZ_INSTANTIATE_TM(oz::RhsVanDerPol, tm_van_der_pol)

@@ -1,0 +1,239 @@
+"""Host-side plumbing between packed torch tensors and the C ABI.
+
+Everything numeric happens in ``liboz_b200.so``; torch provides device memory, the current
+stream and the autograd tape.  Packed layouts are the ones documented in
+``include/ozone_b200.h`` (structure of arrays, trajectory index innermost).
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field, replace
+from typing import Optional
+
+import torch
+
+from . import _native as nat
+from .glms import GLMMethod, MAX_STAGES
+
+
+@dataclass
+class SolveSpec:
+    """Static description of one solve (everything that is not a differentiable tensor)."""
+    rhs_name: str
+    method: GLMMethod
+    N: int
+    n: int
+    dtype: torch.dtype = torch.float64
+    h_shared: bool = True
+    p_shared: bool = False
+    th_shared: bool = False
+    num_inner: int = 0                 # > 0: TimeMarchingCheckpoints segment length
+    store_history: bool = True
+    newton_tol: float = 1e-7           # ozone/integrators/time_marching.py:220
+    newton_max_iter: int = 100
+    d_override: int = 0                # grid RHS: number of cells
+    rhs_cfg: tuple = ()
+    want_status: bool = True
+    info: dict = field(default_factory=dict)
+
+    def __post_init__(self):
+        self.rhs_id = nat.RHS_IDS[self.rhs_name]
+        if not self.info:
+            self.info = nat.rhs_info(self.rhs_id)
+        if self.info['kind'] == 1:
+            self.info = dict(self.info, d=int(self.d_override))
+        if self.dtype not in (torch.float64, torch.float32):
+            raise TypeError(f'unsupported dtype {self.dtype}; the kernels compute in float64 or float32')
+
+    @property
+    def d(self):
+        return self.info['d']
+
+    @property
+    def nt(self):
+        return self.n + 1
+
+
+def _ptr(t: Optional[torch.Tensor]):
+    return None if t is None or t.numel() == 0 else t.data_ptr()
+
+
+def _chk(t: Optional[torch.Tensor], spec: SolveSpec, shape, name):
+    if t is None:
+        return None
+    if not t.is_cuda:
+        raise RuntimeError(f'{name} must live on a CUDA device (ozone_b200 has no CPU path)')
+    if t.dtype != spec.dtype:
+        raise TypeError(f'{name} has dtype {t.dtype}, expected {spec.dtype}')
+    if tuple(t.shape) != tuple(shape):
+        raise ValueError(f'{name} has shape {tuple(t.shape)}, expected {tuple(shape)}')
+    return t.contiguous()
+
+
+def make_problem(spec: SolveSpec) -> nat.OzProblem:
+    pb = nat.OzProblem()
+    m = spec.method
+    s = m.num_stages
+    if s > MAX_STAGES:
+        raise ValueError(f'{s} stages exceed the device tableau storage ({MAX_STAGES})')
+    pb.rhs_id, pb.dtype = spec.rhs_id, (nat.OZ_F64 if spec.dtype == torch.float64 else nat.OZ_F32)
+    pb.num_stages, pb.is_explicit = s, int(m.explicit)
+    for i in range(s):
+        for j in range(s):
+            pb.A[i * MAX_STAGES + j] = float(m.A[i, j])
+        pb.B[i] = float(m.B[0, i])
+        pb.C[i] = float(m.C[i, 0])
+    pb.N, pb.n, pb.num_inner = spec.N, spec.n, spec.num_inner
+    pb.h_shared, pb.p_shared, pb.th_shared = int(spec.h_shared), int(spec.p_shared), int(spec.th_shared)
+    pb.d_override = int(spec.d_override)
+    pb.newton_tol, pb.newton_max_iter = float(spec.newton_tol), int(spec.newton_max_iter)
+    for i, v in enumerate(spec.rhs_cfg):
+        pb.rhs_cfg[i] = float(v)
+    pb.stream = torch.cuda.current_stream().cuda_stream
+    return pb
+
+
+def input_shapes(spec: SolveSpec):
+    d, P, S, N, n = spec.d, spec.info['P'], spec.info['S'], spec.N, spec.n
+    return dict(
+        y0=(d, N),
+        h=(n,) if spec.h_shared else (n, N),
+        p=(n + 1, P) if spec.p_shared else (n + 1, P, N),
+        th=(S,) if spec.th_shared else (S, N),
+    )
+
+
+def _set_inputs(pb, spec, y0, h, p, th):
+    shp = input_shapes(spec)
+    y0 = _chk(y0, spec, shp['y0'], 'y0')
+    h = _chk(h, spec, shp['h'], 'h')
+    p = _chk(p, spec, shp['p'], 'p') if spec.info['P'] else None
+    th = _chk(th, spec, shp['th'], 'th') if spec.info['S'] else None
+    pb.y0, pb.h, pb.p, pb.th = _ptr(y0), _ptr(h), _ptr(p), _ptr(th)
+    return y0, h, p, th
+
+
+def tm_forward(spec: SolveSpec, y0, h, p=None, th=None, keep_history=None):
+    """oz_tm_forward.  Returns dict(hist, ckpt, final, prof, field, status, iters); absent outputs are None."""
+    dev = y0.device
+    pb = make_problem(spec)
+    keep = _set_inputs(pb, spec, y0, h, p, th)
+    d, N, nt = spec.d, spec.N, spec.nt
+    keep_history = spec.store_history if keep_history is None else keep_history
+    new = lambda *shape: torch.empty(shape, dtype=spec.dtype, device=dev)
+    out = dict(hist=None, ckpt=None, final=new(d, N), prof=None, field=None, status=None, iters=None)
+    if keep_history:
+        out['hist'] = new(nt, d, N)
+    if spec.num_inner > 0:
+        out['ckpt'] = new(spec.n // spec.num_inner + 1, d, N)
+    if spec.info['nprof']:
+        out['prof'] = new(nt, spec.info['nprof'], N)
+    if spec.info['nfield']:
+        out['field'] = new(spec.info['nfield'], N)
+    if spec.want_status:
+        out['status'] = torch.zeros(N, dtype=torch.int32, device=dev)
+        out['iters'] = torch.zeros(N, dtype=torch.int32, device=dev)
+    pb.hist, pb.ckpt, pb.yfinal = _ptr(out['hist']), _ptr(out['ckpt']), _ptr(out['final'])
+    pb.prof, pb.field = _ptr(out['prof']), _ptr(out['field'])
+    pb.status, pb.iters = _ptr(out['status']), _ptr(out['iters'])
+    nat.check(nat.lib.oz_tm_forward(C.byref(pb)), 'oz_tm_forward')
+    del keep
+    return out
+
+
+def tm_adjoint(spec: SolveSpec, y0, h, p, th, hist=None, ckpt=None, hist_bar=None, final_bar=None,
+               prof_bar=None, field_bar=None, need=('y0', 'h', 'p', 'th'), status=None):
+    """oz_tm_adjoint.  Returns dict(y0, h, p, th) of gradients shaped like the inputs."""
+    dev = y0.device
+    pb = make_problem(spec)
+    keep = _set_inputs(pb, spec, y0, h, p, th)
+    d, N, nt = spec.d, spec.N, spec.nt
+    shp = input_shapes(spec)
+    hist = _chk(hist, spec, (nt, d, N), 'hist')
+    ckpt = _chk(ckpt, spec, (spec.n // spec.num_inner + 1, d, N), 'ckpt') if spec.num_inner > 0 else None
+    hist_bar = _chk(hist_bar, spec, (nt, d, N), 'hist_bar')
+    final_bar = _chk(final_bar, spec, (d, N), 'final_bar')
+    prof_bar = _chk(prof_bar, spec, (nt, spec.info['nprof'], N), 'prof_bar') if spec.info['nprof'] else None
+    field_bar = _chk(field_bar, spec, (spec.info['nfield'], N), 'field_bar') if spec.info['nfield'] else None
+    pb.hist, pb.ckpt = _ptr(hist), _ptr(ckpt)
+    pb.hist_bar, pb.final_bar, pb.prof_bar, pb.field_bar = map(_ptr, (hist_bar, final_bar, prof_bar, field_bar))
+    grads = {}
+    for k in ('y0', 'h', 'p', 'th'):
+        size_ok = all(s > 0 for s in shp[k])
+        grads[k] = torch.zeros(shp[k], dtype=spec.dtype, device=dev) if (k in need and size_ok) else None
+    pb.y0_bar, pb.h_bar, pb.p_bar, pb.th_bar = (_ptr(grads[k]) for k in ('y0', 'h', 'p', 'th'))
+    pb.status = _ptr(status)
+    ws_bytes = nat.lib.oz_tm_adjoint_workspace_bytes(C.byref(pb))
+    if ws_bytes == C.c_size_t(-1).value:
+        raise nat.OzError(f'oz_tm_adjoint_workspace_bytes: {nat.lib.oz_last_error().decode()}')
+    ws = torch.empty(max(ws_bytes, 8), dtype=torch.uint8, device=dev)
+    pb.ws, pb.ws_bytes = ws.data_ptr(), ws_bytes
+    nat.check(nat.lib.oz_tm_adjoint(C.byref(pb)), 'oz_tm_adjoint')
+    del keep
+    return grads
+
+
+class _TimeMarch(torch.autograd.Function):
+    """Solve + reverse sweep on the autograd tape.  Inputs are packed; outputs are
+    (hist | empty, final, prof | empty, field | empty, status, iters)."""
+
+    @staticmethod
+    def forward(ctx, spec: SolveSpec, y0, h, p, th):
+        needs = [t is not None and t.requires_grad for t in (y0, h, p, th)]
+        any_grad = any(needs)
+        keep_hist = spec.store_history or (any_grad and spec.num_inner == 0)
+        out = tm_forward(spec, y0, h, p, th, keep_history=keep_hist)
+        ctx.spec, ctx.needs = spec, needs
+        ctx.has = dict(hist=out['hist'] is not None, prof=out['prof'] is not None, field=out['field'] is not None)
+        ctx.status = out['status']
+        saved = [y0, h, p, th, out['hist'], out['ckpt']]
+        ctx.present = [t is not None for t in saved]
+        ctx.save_for_backward(*[t for t in saved if t is not None])
+        e = lambda: torch.empty(0, dtype=spec.dtype, device=y0.device)
+        hist = out['hist'] if (spec.store_history and out['hist'] is not None) else e()
+        ret = (hist, out['final'], out['prof'] if out['prof'] is not None else e(),
+               out['field'] if out['field'] is not None else e(),
+               out['status'] if out['status'] is not None else torch.empty(0, dtype=torch.int32, device=y0.device),
+               out['iters'] if out['iters'] is not None else torch.empty(0, dtype=torch.int32, device=y0.device))
+        ctx.mark_non_differentiable(ret[4], ret[5])
+        ctx.hist_returned = hist.numel() > 0
+        return ret
+
+    @staticmethod
+    def backward(ctx, g_hist, g_final, g_prof, g_field, _gs, _gi):
+        spec = ctx.spec
+        it = iter(ctx.saved_tensors)
+        y0, h, p, th, hist, ckpt = [next(it) if present else None for present in ctx.present]
+        need = tuple(k for k, flag in zip(('y0', 'h', 'p', 'th'), ctx.needs) if flag)
+        fix = lambda g, ok: g.contiguous() if (ok and g is not None and g.numel() > 0) else None
+        grads = tm_adjoint(spec, y0, h, p, th, hist=hist, ckpt=ckpt,
+                           hist_bar=fix(g_hist, ctx.hist_returned), final_bar=fix(g_final, True),
+                           prof_bar=fix(g_prof, ctx.has['prof']), field_bar=fix(g_field, ctx.has['field']),
+                           need=need, status=ctx.status)
+        return (None,) + tuple(grads[k] if flag else None for k, flag in zip(('y0', 'h', 'p', 'th'), ctx.needs))
+
+
+def time_march(spec: SolveSpec, y0, h, p=None, th=None):
+    """Differentiable packed solve: returns dict(hist, final, prof, field, status, iters)."""
+    hist, final, prof, fld, status, iters = _TimeMarch.apply(spec, y0, h, p, th)
+    none_if_empty = lambda t: t if t.numel() > 0 else None
+    return dict(hist=none_if_empty(hist), final=final, prof=none_if_empty(prof), field=none_if_empty(fld),
+                status=none_if_empty(status), iters=none_if_empty(iters))
+
+
+def rhs_eval(spec: SolveSpec, y, p=None, th=None):
+    """oz_rhs_eval: f and the outputs at `nodes` points; y (d, nodes), p (P, nodes)."""
+    pb = make_problem(replace(spec, N=1) if False else spec)
+    nodes = y.shape[1]
+    info = spec.info
+    dev = y.device
+    y = y.contiguous()
+    p = p.contiguous() if (p is not None and info['P']) else None
+    th = th.contiguous() if (th is not None and info['S']) else None
+    pb.th = _ptr(th)
+    pb.th_shared = int(th is None or th.dim() == 1)
+    dy = torch.empty_like(y)
+    prof = torch.empty((info['nprof'], nodes), dtype=spec.dtype, device=dev) if info['nprof'] else None
+    fld = torch.empty((info['nfield'], nodes), dtype=spec.dtype, device=dev) if info['nfield'] else None
+    nat.check(nat.lib.oz_rhs_eval(C.byref(pb), nodes, _ptr(y), _ptr(p), _ptr(dy), _ptr(prof), _ptr(fld)), 'oz_rhs_eval')
+    return dy, prof, fld

@@ -1,0 +1,121 @@
+"""Parity of the CUDA time-marching path (through the C ABI) with the oracle: states, outputs and
+adjoint gradients.  Tolerances are the north star's: 1e-10 relative in fp64, 1e-5 in fp32."""
+import numpy as np
+import pytest
+import torch
+
+from tests import cases
+from tests.gpu_util import run_pair, relerr, np_, unshare
+
+pytestmark = pytest.mark.gpu
+
+TOL = {torch.float64: 1e-10, torch.float32: 1e-5}
+
+
+def _compare(case, method, dtype=torch.float64, tol=1e-7, fwd_tol=None, grad_tol=None, **kw):
+    spec, fwd, ref, g, gref = run_pair(case, method, dtype, tol=tol, **kw)
+    ft = TOL[dtype] if fwd_tol is None else fwd_tol
+    gt = TOL[dtype] if grad_tol is None else grad_tol
+    if fwd['hist'] is not None:
+        assert relerr(np_(fwd['hist']), ref['history']) < ft
+    assert relerr(np_(fwd['final']), ref['final']) < ft
+    if fwd['prof'] is not None:
+        assert relerr(np_(fwd['prof']), ref['profile']) < ft
+    if fwd['field'] is not None:
+        assert relerr(np_(fwd['field']), ref['field']) < ft
+    assert int(fwd['status'].max()) == 0
+    for k in ('y0', 'h', 'p', 'th'):
+        if g[k] is None:
+            continue
+        assert relerr(unshare(g[k], gref[k]), gref[k]) < gt, k
+    return spec, fwd, ref, g, gref
+
+
+@pytest.mark.parametrize('dtype', [torch.float64, torch.float32])
+def test_config1_lotka_volterra_rk4_single_trajectory(dtype):
+    _compare(cases.lotka_volterra_inputs(N=1), 'RK4', dtype, grad_tol=None if dtype == torch.float64 else 5e-5)
+
+
+@pytest.mark.parametrize('method', ['ForwardEuler', 'ExplicitMidpoint', 'HeunsMethod', 'RalstonsMethod',
+                                    'KuttaThirdOrder', 'RK4', 'RK6'])
+def test_every_explicit_method_lotka_volterra_batch(method):
+    _compare(cases.lotka_volterra_inputs(N=257, nt=41), method)
+
+
+def test_lotka_volterra_per_trajectory_parameters_and_steps():
+    c = cases.lotka_volterra_inputs(N=100, nt=31, shared_a=False)
+    rng = np.random.default_rng(5)
+    c['h'] = c['h'][:, None] * (1.0 + 0.1 * rng.random((30, 100)))
+    _compare(c, 'RK4')
+
+
+def test_reference_test3_goldens_on_device():
+    # ozone/tests/test_correctness/test_3_large/utils.py:55-74 -- exact RK4 values, now from the GPU
+    c = cases.test3_inputs()
+    spec, fwd, ref, g, gref = _compare(c, 'RK4')
+    assert np_(fwd['hist']).sum() == pytest.approx(6794.12754072, rel=1e-11)
+    from ozone_b200 import engine
+    from tests.gpu_util import dev_inputs
+    y0, h, p, th = dev_inputs(c, spec)
+    ones = torch.ones_like(fwd['hist'])
+    gg = engine.tm_adjoint(spec, y0, h, p, th, hist=fwd['hist'], hist_bar=ones)
+    assert np.linalg.norm(np_(gg['y0'])) == pytest.approx(555.6297961976778, rel=1e-12)
+    assert np.linalg.norm(np_(gg['h'])) == pytest.approx(12570.03729508261, rel=1e-12)
+    assert np.linalg.norm(np_(gg['th'])) == pytest.approx(43.805547522344185, rel=1e-12)
+    assert np.linalg.norm(np_(gg['p'])) == pytest.approx(203.55862089571335, rel=1e-12)
+
+
+@pytest.mark.parametrize('method', ['RK4', 'Trapezoidal'])
+def test_reference_test2_general_three_states_with_outputs(method):
+    _compare(cases.test2_inputs(), method, tol=1e-13)
+
+
+def test_reference_test1_and_tutorial():
+    _compare(cases.test1_inputs(), 'RK4')
+    _compare(cases.test1_inputs(), 'Trapezoidal', tol=1e-13)
+    spec, fwd, *_ = _compare(cases.tutorial_inputs(), 'GaussLegendre4')
+    gold = [1.0, 0.74364452, 0.47414541, 0.19082879, -0.10701378, -0.42012707, -0.74929402,
+            -1.09533772, -1.45912346, -1.8415609, -2.24360632]     # tutorial.ipynb:161-171
+    assert np.allclose(np_(fwd['hist'])[:, 0, 0], gold, rtol=0, atol=5.1e-9)
+    assert int(fwd['iters'][0]) == 10                               # "converged in 1 iterations" x 10 steps
+
+
+@pytest.mark.parametrize('method', ['BackwardEuler', 'ImplicitMidpoint', 'Trapezoidal', 'GaussLegendre2',
+                                    'GaussLegendre4', 'GaussLegendre6', 'Lobatto2', 'Lobatto4', 'RadauI3', 'RadauI5',
+                                    'RadauII3', 'RadauII5'])
+def test_config2_van_der_pol_every_implicit_method(method):
+    # tight Newton tolerance on both sides -> agreement at 1e-10
+    _compare(cases.van_der_pol_inputs(N=200), method, tol=1e-12)
+
+
+def test_config2_van_der_pol_reference_newton_tolerance():
+    # with the reference's own tolerance (1e-7, time_marching.py:220) both sides stop at the same
+    # iteration; quadratic convergence leaves them far closer than 1e-7
+    spec, fwd, ref, g, gref = _compare(cases.van_der_pol_inputs(N=200), 'GaussLegendre6', tol=1e-7,
+                                       fwd_tol=1e-7, grad_tol=1e-6)
+    assert np.array_equal(np_(fwd['iters']), ref['newton_iters'].sum(axis=0))
+
+
+def test_config2_fp32():
+    _compare(cases.van_der_pol_inputs(N=64), 'GaussLegendre4', torch.float32, tol=1e-5, fwd_tol=2e-5, grad_tol=2e-4)
+
+
+@pytest.mark.parametrize('method', ['RK4', 'GaussLegendre4'])
+def test_lunar_ascent_time_marching(method):
+    _compare(cases.ascent_inputs(N=33, nt=21), method, tol=1e-13)
+
+
+@pytest.mark.parametrize('method,ni', [('RK4', 6), ('RK4', 10), ('GaussLegendre4', 5)])
+def test_checkpointed_reverse_sweep_recomputes_the_same_gradients(method, ni):
+    # TimeMarchingCheckpoints: only nc+1 boundary states are kept, the reverse sweep recomputes
+    # (time_marching_uniform.py:77-125); nc = 5 on the 30-step reference problem (test_2_general/test_solution.py:29-45)
+    _compare(cases.test2_inputs(), method, tol=1e-13, num_inner=ni, store_history=False)
+    c = cases.lotka_volterra_inputs(N=70, nt=31)
+    _compare(c, method, tol=1e-13, num_inner=ni, store_history=False)
+
+
+def test_zero_step_size_is_legal():
+    # test_api_odeproblem.py:57 uses step_vector=[0.0, 1.0]
+    c = cases.lotka_volterra_inputs(N=3, nt=3)
+    c['h'] = np.array([0.0, 0.1])
+    _compare(c, 'RK4')
