@@ -87,6 +87,7 @@ struct RhsVanDerPol {
 struct RhsLunarAscent {
     static constexpr int ID = OZ_RHS_LUNAR_ASCENT, D = 7, P = 3, S = 0, NPROF = 0, NFIELD = 0;
     static constexpr double kT = 1.8335634, kVex = 3049.87, kG0 = 1.625, kR0 = 1738100.0;
+    static constexpr double kSqrtG0R0 = 1680.5988516002265;  // sqrt(g0 * R0) = sqrt(2824412.5)
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T*, T* dy) {
         const T Tm = T(kT) / y[6];
@@ -96,7 +97,7 @@ struct RhsLunarAscent {
         dy[3] = -y[0] + Tm * p[0];
         dy[4] = -y[1] + Tm * p[1];
         dy[5] = -y[2] + Tm * p[2];
-        dy[6] = T(-(kT / kVex) * 1680.6323214790313);  // sqrt(g0*R0) = sqrt(2824412.5)
+        dy[6] = T(-(kT / kVex) * kSqrtG0R0);
     }
     template <typename T>
     OZ_D static void jac(const T* y, const T* p, const T*, T* J) {

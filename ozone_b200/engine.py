@@ -237,3 +237,59 @@ def rhs_eval(spec: SolveSpec, y, p=None, th=None):
     fld = torch.empty((info['nfield'], nodes), dtype=spec.dtype, device=dev) if info['nfield'] else None
     nat.check(nat.lib.oz_rhs_eval(C.byref(pb), nodes, _ptr(y), _ptr(p), _ptr(dy), _ptr(prof), _ptr(fld)), 'oz_rhs_eval')
     return dy, prof, fld
+
+
+class TmPlan:
+    """A solve with every buffer allocated once: repeated forward()/adjoint() calls only enqueue
+    kernels (no allocation, no host sync).  This is what a caller inside an optimisation loop
+    uses; ``bench.py`` times it."""
+
+    def __init__(self, spec: SolveSpec, device='cuda', grads=('y0', 'h', 'p', 'th'), cotangents=('final',)):
+        self.spec = spec
+        dev = torch.device(device)
+        d, N, n, nt = spec.d, spec.N, spec.n, spec.nt
+        info = spec.info
+        new = lambda *shape: torch.zeros(shape, dtype=spec.dtype, device=dev)
+        shp = input_shapes(spec)
+        self.y0, self.h = new(*shp['y0']), new(*shp['h'])
+        self.p = new(*shp['p']) if info['P'] else None
+        self.th = new(*shp['th']) if info['S'] else None
+        self.hist = new(nt, d, N) if (spec.store_history or spec.num_inner == 0) else None
+        self.ckpt = new(n // spec.num_inner + 1, d, N) if spec.num_inner > 0 else None
+        self.final = new(d, N)
+        self.prof = new(nt, info['nprof'], N) if info['nprof'] else None
+        self.field = new(info['nfield'], N) if info['nfield'] else None
+        self.status = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.iters = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.hist_bar = new(nt, d, N) if 'hist' in cotangents else None
+        self.final_bar = new(d, N) if 'final' in cotangents else None
+        self.prof_bar = new(nt, info['nprof'], N) if ('prof' in cotangents and info['nprof']) else None
+        self.field_bar = new(info['nfield'], N) if ('field' in cotangents and info['nfield']) else None
+        self.grad = {k: (new(*shp[k]) if (k in grads and all(s > 0 for s in shp[k])) else None)
+                     for k in ('y0', 'h', 'p', 'th')}
+        pb = make_problem(spec)
+        pb.y0, pb.h, pb.p, pb.th = map(_ptr, (self.y0, self.h, self.p, self.th))
+        pb.hist, pb.ckpt, pb.yfinal = _ptr(self.hist), _ptr(self.ckpt), _ptr(self.final)
+        pb.prof, pb.field = _ptr(self.prof), _ptr(self.field)
+        pb.status, pb.iters = _ptr(self.status), _ptr(self.iters)
+        pb.hist_bar, pb.final_bar = _ptr(self.hist_bar), _ptr(self.final_bar)
+        pb.prof_bar, pb.field_bar = _ptr(self.prof_bar), _ptr(self.field_bar)
+        pb.y0_bar, pb.h_bar, pb.p_bar, pb.th_bar = (_ptr(self.grad[k]) for k in ('y0', 'h', 'p', 'th'))
+        ws_bytes = nat.lib.oz_tm_adjoint_workspace_bytes(C.byref(pb))
+        if ws_bytes == C.c_size_t(-1).value:
+            raise nat.OzError(f'oz_tm_adjoint_workspace_bytes: {nat.lib.oz_last_error().decode()}')
+        self.ws = torch.empty(max(ws_bytes, 8), dtype=torch.uint8, device=dev)
+        pb.ws, pb.ws_bytes = self.ws.data_ptr(), ws_bytes
+        self.pb = pb
+        # kernels of ours enqueued by one forward() / one adjoint() call
+        shared_rows = sum(1 for k, flag in (('h', spec.h_shared), ('p', spec.p_shared), ('th', spec.th_shared))
+                          if flag and self.grad[k] is not None)
+        self.launches_forward, self.launches_adjoint = 1, 1 + shared_rows
+
+    def forward(self):
+        self.pb.stream = torch.cuda.current_stream().cuda_stream
+        nat.check(nat.lib.oz_tm_forward(C.byref(self.pb)), 'oz_tm_forward')
+
+    def adjoint(self):
+        self.pb.stream = torch.cuda.current_stream().cuda_stream
+        nat.check(nat.lib.oz_tm_adjoint(C.byref(self.pb)), 'oz_tm_adjoint')
