@@ -153,6 +153,16 @@ OZ_API size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb);
 OZ_API int oz_colloc_vjp(const oz_problem* pb, const void* Y, const void* y, const void* mu1, const void* mu2,
                   void* Y_bar, void* y_bar);
 
+/* No counterpart in the reference.  Same reverse sweep as oz_tm_adjoint, for callers that cannot
+ * allocate device memory (plug-ins inside a host application that owns the GPU, real-time loops,
+ * FFI stubs without an allocator): pb->ws / pb->ws_bytes are ignored and the scratch is a 4 MiB
+ * array built into the library (oz_static_scratch_bytes()).  Problems needing more are refused
+ * (rc < 0, see oz_last_error).  The first call on a device resolves the array's address: make it
+ * outside stream capture.  All calls on a device share the array, so calls that may overlap on the
+ * GPU race; nothing in it needs clearing between calls.  Allocates nothing. */
+OZ_API size_t oz_static_scratch_bytes(void);
+OZ_API int oz_tm_adjoint_static(const oz_problem* pb);
+
 #ifdef __cplusplus
 }
 #endif

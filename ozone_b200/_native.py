@@ -57,6 +57,8 @@ SYMBOLS = {
     'oz_tm_forward': (C.c_int, [_PB]),
     'oz_tm_adjoint_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_adjoint': (C.c_int, [_PB]),
+    'oz_static_scratch_bytes': (C.c_size_t, []),
+    'oz_tm_adjoint_static': (C.c_int, [_PB]),
     'oz_picard_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_picard_forward': (C.c_int, [_PB, C.c_void_p, C.c_double, C.c_int]),
     'oz_colloc_residual': (C.c_int, [_PB, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
