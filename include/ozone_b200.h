@@ -85,7 +85,11 @@ typedef struct oz_problem {
     double newton_tol;
     int32_t newton_max_iter;
     int32_t reserved0;
-    double rhs_cfg[8];    /* RHS constants that are not differentiated (grid RHS: dx, beta_t, beta_u, gamma) */
+    double rhs_cfg[8];    /* RHS constants that are not differentiated (grid RHS: dx, beta_t, beta_u, gamma, H_lo, H_hi) */
+    /* Picard only: the packed-component ranges of the states in insertion order, relaxed one after
+     * another (block Gauss-Seidel, picard_iteration.py:35).  0 blocks = one block = Jacobi. */
+    int32_t num_state_blocks;
+    int32_t state_block_lo[9];
     /* ---- inputs ---- */
     const void* y0;
     const void* h;

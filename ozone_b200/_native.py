@@ -37,6 +37,7 @@ class OzProblem(C.Structure):
         ('h_shared', C.c_int32), ('p_shared', C.c_int32), ('th_shared', C.c_int32), ('d_override', C.c_int32),
         ('newton_tol', C.c_double), ('newton_max_iter', C.c_int32), ('reserved0', C.c_int32),
         ('rhs_cfg', C.c_double * 8),
+        ('num_state_blocks', C.c_int32), ('state_block_lo', C.c_int32 * 9),
         ('y0', C.c_void_p), ('h', C.c_void_p), ('p', C.c_void_p), ('th', C.c_void_p),
         ('hist', C.c_void_p), ('ckpt', C.c_void_p), ('yfinal', C.c_void_p), ('prof', C.c_void_p),
         ('field', C.c_void_p), ('status', C.c_void_p), ('iters', C.c_void_p),

@@ -1,6 +1,7 @@
 // Shared device/host helpers for the ozone_b200 kernels (sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <math_constants.h>
 #include <cstdint>
 #include <cstdio>
 #include <cstring>
@@ -32,6 +33,7 @@ void set_error(const char* fmt, ...);
     } while (0)
 
 constexpr int kMaxS = OZ_MAX_STAGES;
+constexpr size_t kSmemBudget = 200 * 1024;  // dynamic shared memory we size blocks for (227 KB is the hard cap)
 
 // Tableau as seen by a kernel: passed BY VALUE inside the kernel parameter block, i.e. it sits in
 // the constant bank and every access is a uniform (warp-broadcast) load.  No __constant__ symbol,

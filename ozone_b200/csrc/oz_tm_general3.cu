@@ -2,4 +2,4 @@
 // registered right-hand side.  One translation unit per RHS so the build parallelises.
 #include "oz_rhs.cuh"
 #include "oz_tm_launch.cuh"
-OZ_INSTANTIATE_TM(oz::RhsGeneral3, tm_general3)
+OZ_INSTANTIATE_TM(oz::RhsGeneral3, general3)

@@ -2,6 +2,8 @@
 // Each oz_tm_<rhs>.cu instantiates dispatch_tm<R> so the RHS files compile in parallel.
 #pragma once
 #include "oz_tm_kernels.cuh"
+#include "oz_picard_kernels.cuh"
+#include "oz_colloc_kernels.cuh"
 
 namespace oz {
 
@@ -12,8 +14,6 @@ struct EvalArgs {
     const void *y, *p;
     void *dy, *prof, *field;
 };
-
-constexpr size_t kSmemBudget = 200 * 1024;
 
 template <class R, typename T, int S, bool IMPL>
 int pick_block(size_t* smem) {
@@ -121,9 +121,17 @@ int dispatch_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs
 
 }  // namespace oz
 
-#define OZ_INSTANTIATE_TM(RHS, FN)                                                                     \
-    namespace oz {                                                                                     \
-    int FN(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {                     \
-        return dispatch_tm<RHS>(pb, mode, ws_bytes, ev);                                               \
-    }                                                                                                  \
+#define OZ_INSTANTIATE_TM(RHS, NAME)                                                                     \
+    namespace oz {                                                                                       \
+    int tm_##NAME(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {                \
+        return dispatch_tm<RHS>(pb, mode, ws_bytes, ev);                                                 \
+    }                                                                                                    \
+    int picard_##NAME(const oz_problem* pb, const void* guess, double tol, int max_sweeps, const int* blk_lo, \
+                      int nblocks) {                                                                     \
+        return dispatch_picard<RHS>(pb, guess, tol, max_sweeps, blk_lo, nblocks);                        \
+    }                                                                                                    \
+    int colloc_##NAME(const oz_problem* pb, int mode, size_t* ws_bytes, const void* Y, const void* y,    \
+                      const void* mu1, const void* mu2, void* o1, void* o2) {                            \
+        return dispatch_colloc<RHS>(pb, mode, ws_bytes, Y, y, mu1, mu2, o1, o2);                         \
+    }                                                                                                    \
     }

@@ -2,4 +2,4 @@
 // registered right-hand side.  One translation unit per RHS so the build parallelises.
 #include "oz_rhs.cuh"
 #include "oz_tm_launch.cuh"
-OZ_INSTANTIATE_TM(oz::RhsLotkaVolterra, tm_lotka_volterra)
+OZ_INSTANTIATE_TM(oz::RhsLotkaVolterra, lotka_volterra)

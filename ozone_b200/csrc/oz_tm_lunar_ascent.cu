@@ -2,4 +2,4 @@
 // registered right-hand side.  One translation unit per RHS so the build parallelises.
 #include "oz_rhs.cuh"
 #include "oz_tm_launch.cuh"
-OZ_INSTANTIATE_TM(oz::RhsLunarAscent, tm_lunar_ascent)
+OZ_INSTANTIATE_TM(oz::RhsLunarAscent, lunar_ascent)

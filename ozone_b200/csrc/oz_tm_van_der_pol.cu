@@ -2,4 +2,4 @@
 // registered right-hand side.  One translation unit per RHS so the build parallelises.
 #include "oz_rhs.cuh"
 #include "oz_tm_launch.cuh"
-OZ_INSTANTIATE_TM(oz::RhsVanDerPol, tm_van_der_pol)
+OZ_INSTANTIATE_TM(oz::RhsVanDerPol, van_der_pol)

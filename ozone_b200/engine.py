@@ -34,6 +34,7 @@ class SolveSpec:
     d_override: int = 0                # grid RHS: number of cells
     rhs_cfg: tuple = ()
     want_status: bool = True
+    state_blocks: tuple = ()           # Picard: packed-component offsets of the states (block Gauss-Seidel order)
     info: dict = field(default_factory=dict)
 
     def __post_init__(self):
@@ -89,6 +90,10 @@ def make_problem(spec: SolveSpec) -> nat.OzProblem:
     pb.newton_tol, pb.newton_max_iter = float(spec.newton_tol), int(spec.newton_max_iter)
     for i, v in enumerate(spec.rhs_cfg):
         pb.rhs_cfg[i] = float(v)
+    if spec.state_blocks:
+        pb.num_state_blocks = len(spec.state_blocks) - 1
+        for i, v in enumerate(spec.state_blocks):
+            pb.state_block_lo[i] = int(v)
     pb.stream = torch.cuda.current_stream().cuda_stream
     return pb
 
@@ -293,3 +298,153 @@ class TmPlan:
     def adjoint(self):
         self.pb.stream = torch.cuda.current_stream().cuda_stream
         nat.check(nat.lib.oz_tm_adjoint(C.byref(self.pb)), 'oz_tm_adjoint')
+
+
+# ------------------------------------------------------------------------------------------------
+def picard_forward(spec: SolveSpec, y0, h, p=None, th=None, guess=None, tol=1e-10, max_sweeps=2000):
+    """oz_picard_forward: all (step, stage) nodes relaxed at once; returns the same dict as tm_forward."""
+    dev = y0.device
+    pb = make_problem(spec)
+    keep = _set_inputs(pb, spec, y0, h, p, th)
+    d, N, nt = spec.d, spec.N, spec.nt
+    guess = _chk(guess, spec, (spec.n, d, N), 'guess')
+    new = lambda *shape: torch.empty(shape, dtype=spec.dtype, device=dev)
+    out = dict(hist=new(nt, d, N), ckpt=None, final=new(d, N), prof=None, field=None,
+               status=torch.zeros(N, dtype=torch.int32, device=dev), iters=torch.zeros(N, dtype=torch.int32, device=dev))
+    if spec.info['nprof']:
+        out['prof'] = new(nt, spec.info['nprof'], N)
+    if spec.info['nfield']:
+        out['field'] = new(spec.info['nfield'], N)
+    pb.hist, pb.yfinal, pb.prof, pb.field = _ptr(out['hist']), _ptr(out['final']), _ptr(out['prof']), _ptr(out['field'])
+    pb.status, pb.iters = _ptr(out['status']), _ptr(out['iters'])
+    nat.check(nat.lib.oz_picard_forward(C.byref(pb), _ptr(guess), float(tol), int(max_sweeps)), 'oz_picard_forward')
+    del keep
+    return out
+
+
+class _Picard(torch.autograd.Function):
+    """Picard solve on the tape.  The converged iterate satisfies the same discrete equations as
+    time marching, so its reverse sweep is the time-marching adjoint evaluated on the solved history
+    (implicit-function theorem: no need to differentiate through the sweeps)."""
+
+    @staticmethod
+    def forward(ctx, spec, guess, tol, max_sweeps, y0, h, p, th):
+        out = picard_forward(spec, y0, h, p, th, guess=guess, tol=tol, max_sweeps=max_sweeps)
+        ctx.spec = replace(spec, num_inner=0)
+        ctx.needs = [t is not None and t.requires_grad for t in (y0, h, p, th)]
+        saved = [y0, h, p, th, out['hist']]
+        ctx.present = [t is not None for t in saved]
+        ctx.save_for_backward(*[t for t in saved if t is not None])
+        ctx.has = dict(prof=out['prof'] is not None, field=out['field'] is not None)
+        e = lambda: torch.empty(0, dtype=spec.dtype, device=y0.device)
+        ret = (out['hist'], out['final'], out['prof'] if out['prof'] is not None else e(),
+               out['field'] if out['field'] is not None else e(), out['status'], out['iters'])
+        ctx.mark_non_differentiable(ret[4], ret[5])
+        return ret
+
+    @staticmethod
+    def backward(ctx, g_hist, g_final, g_prof, g_field, _gs, _gi):
+        it = iter(ctx.saved_tensors)
+        y0, h, p, th, hist = [next(it) if present else None for present in ctx.present]
+        need = tuple(k for k, flag in zip(('y0', 'h', 'p', 'th'), ctx.needs) if flag)
+        fix = lambda g, ok: g.contiguous() if (ok and g is not None and g.numel() > 0) else None
+        grads = tm_adjoint(ctx.spec, y0, h, p, th, hist=hist, hist_bar=fix(g_hist, True), final_bar=fix(g_final, True),
+                           prof_bar=fix(g_prof, ctx.has['prof']), field_bar=fix(g_field, ctx.has['field']), need=need)
+        return (None, None, None, None) + tuple(grads[k] if flag else None
+                                                for k, flag in zip(('y0', 'h', 'p', 'th'), ctx.needs))
+
+
+def picard(spec: SolveSpec, y0, h, p=None, th=None, guess=None, tol=1e-10, max_sweeps=2000):
+    hist, final, prof, fld, status, iters = _Picard.apply(spec, guess, tol, max_sweeps, y0, h, p, th)
+    none_if_empty = lambda t: t if t.numel() > 0 else None
+    return dict(hist=hist if spec.store_history else None, final=final, prof=none_if_empty(prof),
+                field=none_if_empty(fld), status=status, iters=iters)
+
+
+# ------------------------------------------------------------------------------------------------
+def colloc_residual(spec: SolveSpec, y0, h, p, th, Y, y):
+    dev = y0.device
+    pb = make_problem(spec)
+    keep = _set_inputs(pb, spec, y0, h, p, th)
+    n, s, d, N = spec.n, spec.method.num_stages, spec.d, spec.N
+    Y = _chk(Y, spec, (n, s, d, N), 'stage design variables')
+    y = _chk(y, spec, (n, d, N), 'state design variables')
+    c1 = torch.empty((n, s, d, N), dtype=spec.dtype, device=dev)
+    c2 = torch.empty((n, d, N), dtype=spec.dtype, device=dev)
+    nat.check(nat.lib.oz_colloc_residual(C.byref(pb), _ptr(Y), _ptr(y), _ptr(c1), _ptr(c2)), 'oz_colloc_residual')
+    del keep
+    return c1, c2
+
+
+def colloc_vjp(spec: SolveSpec, y0, h, p, th, Y, y, mu1, mu2, need=('y0', 'h', 'p', 'th')):
+    """oz_colloc_vjp: gradient of <mu1, c1> + <mu2, c2> w.r.t. (Y, y, y0, h, p, th)."""
+    dev = y0.device
+    pb = make_problem(spec)
+    keep = _set_inputs(pb, spec, y0, h, p, th)
+    n, s, d, N = spec.n, spec.method.num_stages, spec.d, spec.N
+    Y = _chk(Y, spec, (n, s, d, N), 'stage design variables')
+    y = _chk(y, spec, (n, d, N), 'state design variables')
+    mu1 = _chk(mu1, spec, (n, s, d, N), 'mu1')
+    mu2 = _chk(mu2, spec, (n, d, N), 'mu2')
+    shp = input_shapes(spec)
+    grads = {k: (torch.zeros(shp[k], dtype=spec.dtype, device=dev) if (k in need and all(v > 0 for v in shp[k])) else None)
+             for k in ('y0', 'h', 'p', 'th')}
+    if grads['th'] is not None and not spec.th_shared:
+        raise NotImplementedError('collocation gradients of per-trajectory static parameters are not implemented')
+    pb.y0_bar, pb.h_bar, pb.p_bar, pb.th_bar = (_ptr(grads[k]) for k in ('y0', 'h', 'p', 'th'))
+    Yb, yb = torch.empty_like(Y), torch.empty_like(y)
+    ws_bytes = nat.lib.oz_colloc_vjp_workspace_bytes(C.byref(pb))
+    if ws_bytes == C.c_size_t(-1).value:
+        raise nat.OzError(f'oz_colloc_vjp_workspace_bytes: {nat.lib.oz_last_error().decode()}')
+    ws = torch.empty(max(ws_bytes, 8), dtype=torch.uint8, device=dev)
+    pb.ws, pb.ws_bytes = ws.data_ptr(), ws_bytes
+    nat.check(nat.lib.oz_colloc_vjp(C.byref(pb), _ptr(Y), _ptr(y), _ptr(mu1), _ptr(mu2), _ptr(Yb), _ptr(yb)),
+              'oz_colloc_vjp')
+    del keep
+    return dict(grads, Y=Yb, y=yb)
+
+
+class _Collocation(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, spec, y0, h, p, th, Y, y):
+        c1, c2 = colloc_residual(spec, y0, h, p, th, Y, y)
+        ctx.spec = spec
+        ctx.needs = [t is not None and t.requires_grad for t in (y0, h, p, th, Y, y)]
+        saved = [y0, h, p, th, Y, y]
+        ctx.present = [t is not None for t in saved]
+        ctx.save_for_backward(*[t for t in saved if t is not None])
+        return c1, c2
+
+    @staticmethod
+    def backward(ctx, mu1, mu2):
+        it = iter(ctx.saved_tensors)
+        y0, h, p, th, Y, y = [next(it) if present else None for present in ctx.present]
+        need = tuple(k for k, flag in zip(('y0', 'h', 'p', 'th'), ctx.needs[:4]) if flag)
+        g = colloc_vjp(ctx.spec, y0, h, p, th, Y, y, mu1.contiguous(), mu2.contiguous(), need=need)
+        order = ('y0', 'h', 'p', 'th', 'Y', 'y')
+        return (None,) + tuple(g[k] if flag else None for k, flag in zip(order, ctx.needs))
+
+
+def collocation(spec: SolveSpec, y0, h, p, th, Y, y):
+    """Differentiable constraints (c1, c2) of ozone/integrators/collocation.py:48-50."""
+    return _Collocation.apply(spec, y0, h, p, th, Y, y)
+
+
+def outputs_on_history(spec: SolveSpec, hist, p, th):
+    """vector_based.py:33-49: profile outputs at every grid point of a solved history and field outputs
+    summed over time, with the RAW parameters.  (Values only: not on the autograd tape.)"""
+    nt, d, N = hist.shape
+    info = spec.info
+    y = hist.detach().permute(1, 0, 2).reshape(d, nt * N).contiguous()
+    pp = None
+    if info['P']:
+        pd = p.detach()
+        pp = (pd.unsqueeze(-1).expand(nt, info['P'], N) if spec.p_shared else pd).permute(1, 0, 2).reshape(info['P'], nt * N).contiguous()
+    tt = None
+    if info['S']:
+        td = th.detach()
+        tt = td if spec.th_shared else td.unsqueeze(1).expand(info['S'], nt, N).reshape(info['S'], nt * N).contiguous()
+    _, prof, fld = rhs_eval(spec, y, pp, tt)
+    prof = prof.reshape(info['nprof'], nt, N).permute(1, 0, 2).contiguous() if prof is not None else None
+    fld = fld.reshape(info['nfield'], nt, N).sum(dim=1) if fld is not None else None
+    return prof, fld
