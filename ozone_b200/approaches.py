@@ -31,7 +31,7 @@ class PicardIteration(_Approach):
 
     def __init__(self, tolerance: Optional[float] = None, max_iter: int = 2000) -> None:
         # max_iter: ozone/integrators/picard_iteration.py:35.  The tolerance is a csdl default the
-        # reference does not set; here it defaults to 1e-10 (fp64) / 1e-5 (fp32).
+        # reference does not set; here it defaults to 1e-10 (fp64) / 1e-4 (fp32).
         super().__init__()
         self.tolerance, self.max_iter = tolerance, max_iter
 

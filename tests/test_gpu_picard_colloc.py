@@ -55,7 +55,7 @@ def test_picard_general3_three_state_blocks_with_outputs():
 
 def test_picard_fp32_and_long_horizon_reports_non_convergence():
     c = cases.lotka_volterra_inputs(N=64, nt=101)
-    spec, out, ref = _picard_pair(c, 'RK4', (0, 1, 2), tol=1e-5, dtype=torch.float32)
+    spec, out, ref = _picard_pair(c, 'RK4', (0, 1, 2), tol=1e-4, dtype=torch.float32)   # fp32 residual floor of 800 unknowns ~ 2e-5
     assert int(out['status'].max()) == 0
     assert relerr(np_(out['hist']), ref['history']) < 2e-5
     # the sweep diverges for long horizons; the kernel must flag it per trajectory, not return NaN silently
