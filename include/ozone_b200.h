@@ -90,6 +90,10 @@ typedef struct oz_problem {
      * another (block Gauss-Seidel, picard_iteration.py:35).  0 blocks = one block = Jacobi. */
     int32_t num_state_blocks;
     int32_t state_block_lo[9];
+    /* Grid RHS, slab mode (grid_nx_global > 0): this call integrates cells [grid_x_off, grid_x_off + d_override)
+     * of a grid of grid_nx_global cells; only local cells [grid_own_lo, grid_own_hi) count in the grid-wide
+     * sums (J_space, u_bar, h_bar).  Used by the spatial shard; 0 = the whole grid is local. */
+    int64_t grid_x_off, grid_nx_global, grid_own_lo, grid_own_hi;
     /* ---- inputs ---- */
     const void* y0;
     const void* h;
@@ -135,6 +139,7 @@ OZ_API int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const
  * explicit and Newton), :247-260 (update), :97-141 (outputs).  With num_inner > 0 it is
  * TimeMarchingUniform.integrate (ozone/integrators/time_marching_uniform.py:7-150): only `ckpt`
  * needs to be retained for the reverse sweep. */
+OZ_API size_t oz_tm_forward_workspace_bytes(const oz_problem* pb);   /* 0 for per-trajectory RHS; grid RHS: ping-pong + partial sums */
 OZ_API int oz_tm_forward(const oz_problem* pb);
 
 /* Reverse sweep of the same loop: what csdl derives from the stacked loop

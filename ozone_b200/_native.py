@@ -38,6 +38,7 @@ class OzProblem(C.Structure):
         ('newton_tol', C.c_double), ('newton_max_iter', C.c_int32), ('reserved0', C.c_int32),
         ('rhs_cfg', C.c_double * 8),
         ('num_state_blocks', C.c_int32), ('state_block_lo', C.c_int32 * 9),
+        ('grid_x_off', C.c_int64), ('grid_nx_global', C.c_int64), ('grid_own_lo', C.c_int64), ('grid_own_hi', C.c_int64),
         ('y0', C.c_void_p), ('h', C.c_void_p), ('p', C.c_void_p), ('th', C.c_void_p),
         ('hist', C.c_void_p), ('ckpt', C.c_void_p), ('yfinal', C.c_void_p), ('prof', C.c_void_p),
         ('field', C.c_void_p), ('status', C.c_void_p), ('iters', C.c_void_p),
@@ -55,6 +56,7 @@ SYMBOLS = {
     'oz_last_error': (C.c_char_p, []),
     'oz_rhs_info': (C.c_int, [C.c_int, _IP, _IP, _IP, _IP, _IP, _IP]),
     'oz_rhs_eval': (C.c_int, [_PB, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'oz_tm_forward_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_forward': (C.c_int, [_PB]),
     'oz_tm_adjoint_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_adjoint': (C.c_int, [_PB]),

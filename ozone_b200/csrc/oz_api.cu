@@ -110,6 +110,14 @@ int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* 
     return route(pb, TM_RHS_EVAL, nullptr, &ev);
 }
 
+size_t oz_tm_forward_workspace_bytes(const oz_problem* pb) {
+    if (check_problem(pb)) return (size_t)-1;
+    if (kInfo[pb->rhs_id].kind == 0) return 0;
+    size_t bytes = 0;
+    if (pde_dispatch(pb, 100, &bytes, nullptr)) return (size_t)-1;
+    return bytes;
+}
+
 int oz_tm_forward(const oz_problem* pb) {
     if (int rc = check_problem(pb)) return rc;
     OZ_REQUIRE(pb->y0 && pb->h, "y0 and h are required");

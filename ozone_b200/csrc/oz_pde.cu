@@ -1,5 +1,521 @@
+// Grid right-hand side: nonlinear diffusion-reaction PDE (ozone/paper_examples/pde_control/pde_control.py:11-81)
+// under TimeMarching / TimeMarchingCheckpoints with any EXPLICIT tableau.
+//
+//   x_j' = (x_{j-1} - 2 x_j + x_{j+1}) / dx^2 + beta_T (exp(-gamma/(1+x_j)) - exp(-gamma)) + beta_U (H_j u - x_j)
+//   zero Dirichlet ghosts (:32-35), H_j = 1 for round(0.3 nx) <= j < round(0.7 nx) (:15-16)
+//   field output J_space = (100/nx) sum_j x_j^2 + 20 u^2 with the rebound dx = 1/nx (:62-76)
+//
+// One trajectory whose d = nx components are the cells, so the parallel axis is SPACE.  One launch
+// advances the whole grid by one step with all s stages fused: a CTA loads its tile plus a halo of
+// s cells per side, the stage values circulate through one shared-memory line (each stencil
+// application invalidates one more halo cell per side), F_i stay in registers, and only y_{k+1}
+// is written.  HBM traffic per cell-step is one read + one write (2w), not 2w per stage.
+// The reverse step re-derives the stages the same way and then runs the transposed stage chain
+// (the 3-point stencil is symmetric, so it is the same access pattern on the multipliers) with a
+// halo of 2s.  Grid-wide sums (J_space, u_bar, h_bar) are per-CTA partials reduced in a fixed order.
+//
+// `x_off`/`own_lo`/`own_hi` let a rank run the same kernels on a slab [x_off, x_off + nx) of a larger
+// grid: reductions only count the cells it owns (see ozone_b200/parallel.py for the halo exchange).
 #include "oz_common.cuh"
 #include "oz_tm_launch.cuh"
+
 namespace oz {
-int pde_dispatch(const oz_problem*, int, size_t*, const EvalArgs*) { set_error("grid RHS not built yet"); return -1; }
+
+constexpr int kPdeBlock = 256;
+constexpr int kPdeCpt = 4;                        // cells per thread
+constexpr int kPdeExt = kPdeBlock * kPdeCpt;      // cells per CTA including halos
+
+template <typename T>
+struct PdeRhs {
+    T inv_dx2, beta_t, beta_u, gamma, bt_emg;
+    long long h_lo, h_hi;  // global cell range where the control acts
+    OZ_D T f(T xm, T x, T xp, T u, bool in_h) const {
+        return (xm - T(2) * x + xp) * inv_dx2 + beta_t * exp(-gamma / (T(1) + x)) - bt_emg +
+               beta_u * ((in_h ? u : T(0)) - x);
+    }
+    OZ_D T diag(T x) const {  // d(reaction + transfer)/dx
+        const T q = T(1) / (T(1) + x);
+        return beta_t * exp(-gamma * q) * gamma * q * q - beta_u;
+    }
+};
+
+template <typename T>
+struct PdeArgs {
+    Tableau<T> tab;
+    PdeRhs<T> rhs;
+    long long nx;        // cells in this (local) domain; outside is zero
+    long long x_off;     // global index of local cell 0 (for the control mask)
+    long long own_lo, own_hi;  // local range whose cells count in reductions
+    long long nx_global;
+    const T* y_in;
+    T* y_out;
+    const T* h;          // &h[k]
+    const T* u_lo;       // &p[k], &p[k+1]
+    const T* u_hi;
+    T* part_sq;          // [ncta] partial sums of y_out^2 over owned cells (or nullptr)
+    // adjoint
+    const T* lam_in;     // lambda_{k+1}
+    T* lam_out;          // lambda_k
+    const T* hist_bar_k; // direct cotangent of y_k or nullptr
+    const T* field_bar;  // device scalar (or nullptr): cotangent of the field output
+    T fb_scale;          // 200 / nx_global: d J_space / d y_j = fb_scale * y_j
+    T* part_h;           // [ncta]
+    T* part_ulo;         // [ncta]
+    T* part_uhi;         // [ncta]
+};
+
+template <typename T>
+OZ_D T block_sum(T v, T* sm) {
+    v = warp_sum(v);
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __syncthreads();
+    if (lane == 0) sm[w] = v;
+    __syncthreads();
+    T r = T(0);
+    if (threadIdx.x < 32) {
+        r = threadIdx.x < (blockDim.x >> 5) ? sm[threadIdx.x] : T(0);
+        r = warp_sum(r);
+    }
+    return r;  // valid in warp 0
 }
+
+// stages of one explicit step on the CTA's extended tile: F[i][m] for the cells this thread owns
+template <typename T, int S>
+OZ_D void pde_stages(const PdeArgs<T>& a, T h, T ulo, T uhi, const T* yv, const bool* inside, const bool* in_h,
+                     T (*F)[kPdeCpt], T* line) {
+    const Tableau<T>& tab = a.tab;
+#pragma unroll
+    for (int i = 0; i < S; ++i) {
+        T Yi[kPdeCpt];
+        const T ui = ulo * (T(1) - tab.C[i]) + uhi * tab.C[i];
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) {
+            T acc = T(0);
+#pragma unroll
+            for (int j = 0; j < i; ++j) acc += tab.a(i, j) * F[j][m];
+            Yi[m] = inside[m] ? yv[m] + h * acc : T(0);
+            line[1 + threadIdx.x + m * kPdeBlock] = Yi[m];
+        }
+        __syncthreads();
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) {
+            const int e = threadIdx.x + m * kPdeBlock;
+            F[i][m] = inside[m] ? a.rhs.f(line[e], Yi[m], line[e + 2], ui, in_h[m]) : T(0);
+        }
+        __syncthreads();
+    }
+}
+
+template <typename T, int S>
+__global__ void __launch_bounds__(kPdeBlock) pde_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line[kPdeExt + 2];
+    __shared__ T red[32];
+    constexpr int HALO = S;
+    const long long interior = kPdeExt - 2 * HALO;
+    const long long base = (long long)blockIdx.x * interior - HALO;
+    if (threadIdx.x == 0) {
+        line[0] = T(0);
+        line[kPdeExt + 1] = T(0);
+    }
+    T yv[kPdeCpt], F[S][kPdeCpt];
+    bool inside[kPdeCpt], in_h[kPdeCpt];
+#pragma unroll
+    for (int m = 0; m < kPdeCpt; ++m) {
+        const long long j = base + threadIdx.x + m * kPdeBlock;
+        inside[m] = j >= 0 && j < a.nx;
+        yv[m] = inside[m] ? __ldg(a.y_in + j) : T(0);
+        const long long g = j + a.x_off;
+        in_h[m] = g >= a.rhs.h_lo && g < a.rhs.h_hi;
+    }
+    const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
+    pde_stages<T, S>(a, h, ulo, uhi, yv, inside, in_h, F, line);
+    T acc2 = T(0);
+#pragma unroll
+    for (int m = 0; m < kPdeCpt; ++m) {
+        const int e = threadIdx.x + m * kPdeBlock;
+        const long long j = base + e;
+        if (e >= HALO && e < kPdeExt - HALO && inside[m]) {
+            T acc = T(0);
+#pragma unroll
+            for (int i = 0; i < S; ++i) acc += a.tab.B[i] * F[i][m];
+            const T yn = yv[m] + h * acc;
+            a.y_out[j] = yn;
+            if (j >= a.own_lo && j < a.own_hi) acc2 += yn * yn;
+        }
+    }
+    if (a.part_sq) {
+        const T s = block_sum(acc2, red);
+        if (threadIdx.x == 0) a.part_sq[blockIdx.x] = s;
+    }
+}
+
+// sum of squares of a vector over the owned cells (J_space of the initial condition)
+template <typename T>
+__global__ void __launch_bounds__(kPdeBlock) pde_sumsq_kernel(const T* __restrict__ y, long long own_lo, long long own_hi,
+                                                              T* __restrict__ part) {
+    __shared__ T red[32];
+    T acc = T(0);
+    for (long long j = own_lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; j < own_hi;
+         j += (long long)gridDim.x * blockDim.x)
+        acc += y[j] * y[j];
+    const T s = block_sum(acc, red);
+    if (threadIdx.x == 0) part[blockIdx.x] = s;
+}
+
+template <typename T, int S>
+__global__ void __launch_bounds__(kPdeBlock) pde_adjoint_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line[kPdeExt + 2];
+    __shared__ T red[32];
+    constexpr int HALO = 2 * S;
+    const Tableau<T>& tab = a.tab;
+    const long long interior = kPdeExt - 2 * HALO;
+    const long long base = (long long)blockIdx.x * interior - HALO;
+    if (threadIdx.x == 0) {
+        line[0] = T(0);
+        line[kPdeExt + 1] = T(0);
+    }
+    T yv[kPdeCpt], lam[kPdeCpt], F[S][kPdeCpt], Yb[S][kPdeCpt];
+    bool inside[kPdeCpt], in_h[kPdeCpt];
+#pragma unroll
+    for (int m = 0; m < kPdeCpt; ++m) {
+        const long long j = base + threadIdx.x + m * kPdeBlock;
+        inside[m] = j >= 0 && j < a.nx;
+        yv[m] = inside[m] ? __ldg(a.y_in + j) : T(0);
+        lam[m] = inside[m] ? __ldg(a.lam_in + j) : T(0);
+        const long long g = j + a.x_off;
+        in_h[m] = g >= a.rhs.h_lo && g < a.rhs.h_hi;
+    }
+    const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
+    const T fbs = a.field_bar ? __ldg(a.field_bar) * a.fb_scale : T(0);
+    pde_stages<T, S>(a, h, ulo, uhi, yv, inside, in_h, F, line);
+
+    // transposed stage chain:  G_i = h (b_i lam + sum_{j>i} a_ji Ybar_j),  Ybar_i = J(Y_i)^T G_i
+    T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
+#pragma unroll
+    for (int i = S - 1; i >= 0; --i) {
+        T G[kPdeCpt];
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) {
+            T acc = tab.B[i] * lam[m];
+#pragma unroll
+            for (int j = i + 1; j < S; ++j) acc += tab.a(j, i) * Yb[j][m];
+            G[m] = inside[m] ? h * acc : T(0);
+            line[1 + threadIdx.x + m * kPdeBlock] = G[m];
+        }
+        __syncthreads();
+        T usum = T(0);
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) {
+            const int e = threadIdx.x + m * kPdeBlock;
+            const long long j = base + e;
+            T af = T(0);  // sum_j a_ij F_j  -> Y_i and the h_bar term
+#pragma unroll
+            for (int jj = 0; jj < i; ++jj) af += tab.a(i, jj) * F[jj][m];
+            const T Yi = yv[m] + h * af;
+            Yb[i][m] = inside[m] ? (line[e] - T(2) * G[m] + line[e + 2]) * a.rhs.inv_dx2 + a.rhs.diag(Yi) * G[m] : T(0);
+            const bool owned = e >= HALO && e < kPdeExt - HALO && inside[m] && j >= a.own_lo && j < a.own_hi;
+            if (owned) {
+                if (in_h[m]) usum += a.rhs.beta_u * G[m];
+                h_acc += Yb[i][m] * af;
+            }
+        }
+        u_lo_acc += (T(1) - tab.C[i]) * usum;
+        u_hi_acc += tab.C[i] * usum;
+        __syncthreads();
+    }
+#pragma unroll
+    for (int m = 0; m < kPdeCpt; ++m) {
+        const int e = threadIdx.x + m * kPdeBlock;
+        const long long j = base + e;
+        if (e >= HALO && e < kPdeExt - HALO && inside[m]) {
+            T bf = T(0), yb = T(0);
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
+                bf += tab.B[i] * F[i][m];
+                yb += Yb[i][m];
+            }
+            T out = lam[m] + yb + fbs * yv[m];
+            if (a.hist_bar_k) out += __ldg(a.hist_bar_k + j);
+            a.lam_out[j] = out;
+            if (j >= a.own_lo && j < a.own_hi) h_acc += bf * lam[m];
+        }
+    }
+    T s = block_sum(h_acc, red);
+    if (threadIdx.x == 0) a.part_h[blockIdx.x] = s;
+    s = block_sum(u_lo_acc, red);
+    if (threadIdx.x == 0) a.part_ulo[blockIdx.x] = s;
+    s = block_sum(u_hi_acc, red);
+    if (threadIdx.x == 0) a.part_uhi[blockIdx.x] = s;
+}
+
+// lam_n = final_bar + hist_bar[n] + field_bar * (200/nx) * y_n
+template <typename T>
+__global__ void pde_terminal_kernel(long long nx, const T* __restrict__ yn, const T* __restrict__ final_bar,
+                                    const T* __restrict__ hist_bar_n, const T* __restrict__ field_bar, T fb_scale,
+                                    T* __restrict__ lam) {
+    const long long j = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (j >= nx) return;
+    T v = (field_bar && yn) ? __ldg(field_bar) * fb_scale * yn[j] : T(0);
+    if (final_bar) v += final_bar[j];
+    if (hist_bar_n) v += hist_bar_n[j];
+    lam[j] = v;
+}
+
+// field = sum_k [ (100/nx) sum_cta part_sq[k][cta] + 20 u_k^2 ]   (one block, fixed order)
+template <typename T>
+__global__ void __launch_bounds__(256) pde_field_kernel(const T* __restrict__ part_sq, int nt, long long ncta,
+                                                        const T* __restrict__ u, T scale, T own_u, T* __restrict__ field) {
+    __shared__ T red[32];
+    T acc = T(0);
+    for (long long q = threadIdx.x; q < (long long)nt * ncta; q += blockDim.x) acc += part_sq[q];
+    acc *= scale;
+    for (int k = threadIdx.x; k < nt; k += blockDim.x) acc += own_u * T(20) * u[k] * u[k];
+    const T s = block_sum(acc, red);
+    if (threadIdx.x == 0) field[0] = s;
+}
+
+// h_bar[k] = sum_cta part_h[k][cta];  u_bar[k] = sum_cta (part_ulo[k] + part_uhi[k-1]) + own_u * 40 u_k field_bar
+template <typename T>
+__global__ void __launch_bounds__(256) pde_grads_kernel(int n, long long ncta, const T* __restrict__ part_h,
+                                                        const T* __restrict__ part_ulo, const T* __restrict__ part_uhi,
+                                                        const T* __restrict__ u, const T* __restrict__ field_bar,
+                                                        T* __restrict__ h_bar, T* __restrict__ u_bar) {
+    __shared__ T red[32];
+    const int k = blockIdx.x;  // 0..n
+    T ah = T(0), au = T(0);
+    for (long long c = threadIdx.x; c < ncta; c += blockDim.x) {
+        if (k < n) {
+            ah += part_h[(long long)k * ncta + c];
+            au += part_ulo[(long long)k * ncta + c];
+        }
+        if (k > 0) au += part_uhi[(long long)(k - 1) * ncta + c];
+    }
+    T s = block_sum(ah, red);
+    if (threadIdx.x == 0 && k < n && h_bar) h_bar[k] = s;
+    s = block_sum(au, red);
+    if (threadIdx.x == 0 && u_bar) u_bar[k] = s + (field_bar ? T(40) * field_bar[0] * u[k] : T(0));
+}
+
+struct PdeLayout {
+    long long nx, ncta_f, ncta_a, sq_blocks;
+    size_t off_ping, off_pong, off_sq, off_seg, off_lam0, off_lam1, off_ph, off_pulo, off_puhi, total_fwd, total_adj;
+};
+
+template <int S>
+static PdeLayout pde_layout(const oz_problem* pb) {
+    PdeLayout L;
+    L.nx = pb->d_override;
+    L.ncta_f = (L.nx + (kPdeExt - 2 * S) - 1) / (kPdeExt - 2 * S);
+    L.ncta_a = (L.nx + (kPdeExt - 4 * S) - 1) / (kPdeExt - 4 * S);
+    const size_t nx = (size_t)L.nx, nt = (size_t)pb->n + 1;
+    const size_t vec = (nx + 31) / 32 * 32;
+    // forward: ping, pong, part_sq[nt][ncta_f]
+    L.off_ping = 0;
+    L.off_pong = vec;
+    L.off_sq = 2 * vec;
+    L.total_fwd = L.off_sq + nt * (size_t)L.ncta_f;
+    // adjoint: segment states, lambda ping/pong, partials [n][ncta_a] x 3  (+ ping/pong for the replay)
+    const size_t ni = pb->hist ? 0 : (size_t)(pb->num_inner > 0 ? pb->num_inner : pb->n);
+    L.off_seg = 0;
+    L.off_lam0 = ni * vec;
+    L.off_lam1 = L.off_lam0 + vec;
+    L.off_ph = L.off_lam1 + vec;
+    L.off_pulo = L.off_ph + (size_t)pb->n * L.ncta_a;
+    L.off_puhi = L.off_pulo + (size_t)pb->n * L.ncta_a;
+    L.total_adj = L.off_puhi + (size_t)pb->n * L.ncta_a;
+    return L;
+}
+
+template <typename T>
+static PdeArgs<T> pde_base_args(const oz_problem* pb) {
+    PdeArgs<T> a;
+    memset(&a, 0, sizeof(a));
+    a.tab = make_tableau<T>(pb);
+    const double dx = pb->rhs_cfg[0], bt = pb->rhs_cfg[1], bu = pb->rhs_cfg[2], g = pb->rhs_cfg[3];
+    a.rhs.inv_dx2 = (T)(1.0 / (dx * dx));
+    a.rhs.beta_t = (T)bt;
+    a.rhs.beta_u = (T)bu;
+    a.rhs.gamma = (T)g;
+    a.rhs.bt_emg = (T)(bt * exp(-g));
+    a.rhs.h_lo = (long long)pb->rhs_cfg[4];
+    a.rhs.h_hi = (long long)pb->rhs_cfg[5];
+    a.nx = pb->d_override;
+    // slab mode (grid_nx_global > 0): this rank integrates cells [grid_x_off, grid_x_off + nx) of a larger grid
+    // and owns [grid_own_lo, grid_own_hi) of them (local indices) in the reductions
+    const bool slab = pb->grid_nx_global > 0;
+    a.x_off = slab ? pb->grid_x_off : 0;
+    a.nx_global = slab ? pb->grid_nx_global : a.nx;
+    a.own_lo = slab ? pb->grid_own_lo : 0;
+    a.own_hi = slab ? pb->grid_own_hi : a.nx;
+    return a;
+}
+
+template <typename T, int S>
+static int pde_forward(const oz_problem* pb) {
+    const PdeLayout L = pde_layout<S>(pb);
+    OZ_REQUIRE((size_t)L.total_fwd * sizeof(T) <= pb->ws_bytes && pb->ws, "grid forward workspace too small: need %zu bytes, got %zu",
+               (size_t)L.total_fwd * sizeof(T), pb->ws_bytes);
+    cudaStream_t st = (cudaStream_t)pb->stream;
+    T* ws = (T*)pb->ws;
+    const long long nx = L.nx;
+    const int n = pb->n, ni = pb->num_inner;
+    PdeArgs<T> a = pde_base_args<T>(pb);
+    const T* h = (const T*)pb->h;
+    const T* u = (const T*)pb->p;
+    T* hist = (T*)pb->hist;
+    T* ckpt = (T*)pb->ckpt;
+    T* part_sq = pb->field ? ws + L.off_sq : nullptr;
+    const T* cur = (const T*)pb->y0;
+    if (hist) OZ_CUDA_CHECK(cudaMemcpyAsync(hist, cur, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    if (ckpt) OZ_CUDA_CHECK(cudaMemcpyAsync(ckpt, cur, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    if (part_sq) {
+        OZ_CUDA_CHECK(cudaMemsetAsync(part_sq, 0, (size_t)L.ncta_f * sizeof(T), st));
+        pde_sumsq_kernel<T><<<(unsigned)(L.ncta_f < 1024 ? L.ncta_f : 1024), kPdeBlock, 0, st>>>(cur, a.own_lo, a.own_hi, part_sq);
+    }
+    for (int k = 0; k < n; ++k) {
+        T* out;
+        if (hist)
+            out = hist + (size_t)(k + 1) * nx;
+        else if (ckpt && ni > 0 && (k + 1) % ni == 0)
+            out = ckpt + (size_t)((k + 1) / ni) * nx;
+        else if (k == n - 1 && pb->yfinal)
+            out = (T*)pb->yfinal;
+        else
+            out = ws + ((k & 1) ? L.off_pong : L.off_ping);
+        a.y_in = cur;
+        a.y_out = out;
+        a.h = h + k;
+        a.u_lo = u + k;
+        a.u_hi = u + k + 1;
+        a.part_sq = part_sq ? part_sq + (size_t)(k + 1) * L.ncta_f : nullptr;
+        pde_step_kernel<T, S><<<(unsigned)L.ncta_f, kPdeBlock, 0, st>>>(a);
+        if (hist && ckpt && ni > 0 && (k + 1) % ni == 0)
+            OZ_CUDA_CHECK(cudaMemcpyAsync(ckpt + (size_t)((k + 1) / ni) * nx, out, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
+        cur = out;
+    }
+    OZ_CUDA_CHECK(cudaGetLastError());
+    if (pb->yfinal && cur != (const T*)pb->yfinal)
+        OZ_CUDA_CHECK(cudaMemcpyAsync(pb->yfinal, cur, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
+    if (pb->field) {
+        pde_field_kernel<T><<<1, 256, 0, st>>>(part_sq, n + 1, L.ncta_f, u, (T)(100.0 / (double)a.nx_global),
+                                               (T)((pb->grid_nx_global > 0 && pb->grid_x_off + pb->grid_own_lo != 0) ? 0.0 : 1.0), (T*)pb->field);
+        OZ_CUDA_CHECK(cudaGetLastError());
+    }
+    if (pb->status) OZ_CUDA_CHECK(cudaMemsetAsync(pb->status, 0, sizeof(int), st));
+    if (pb->iters) OZ_CUDA_CHECK(cudaMemsetAsync(pb->iters, 0, sizeof(int), st));
+    return 0;
+}
+
+template <typename T, int S>
+static int pde_adjoint(const oz_problem* pb) {
+    const PdeLayout L = pde_layout<S>(pb);
+    OZ_REQUIRE((size_t)L.total_adj * sizeof(T) <= pb->ws_bytes && pb->ws, "grid adjoint workspace too small: need %zu bytes, got %zu",
+               (size_t)L.total_adj * sizeof(T), pb->ws_bytes);
+    OZ_REQUIRE(pb->hist || pb->ckpt, "adjoint needs hist or ckpt");
+    cudaStream_t st = (cudaStream_t)pb->stream;
+    T* ws = (T*)pb->ws;
+    const long long nx = L.nx;
+    const size_t vec = ((size_t)nx + 31) / 32 * 32;
+    const int n = pb->n;
+    const bool use_seg = pb->hist == nullptr;
+    const int ni = use_seg ? (pb->num_inner > 0 ? pb->num_inner : n) : n;
+    const int nseg = n / ni;
+    PdeArgs<T> a = pde_base_args<T>(pb);
+    const T* h = (const T*)pb->h;
+    const T* u = (const T*)pb->p;
+    const T* hist = (const T*)pb->hist;
+    const T* ckpt = (const T*)pb->ckpt;
+    const T* hist_bar = (const T*)pb->hist_bar;
+    T* seg = ws + L.off_seg;
+    T* lam[2] = {ws + L.off_lam0, ws + L.off_lam1};
+    T* ph = ws + L.off_ph;
+    T* pulo = ws + L.off_pulo;
+    T* puhi = ws + L.off_puhi;
+    a.field_bar = (const T*)pb->field_bar;
+    a.fb_scale = (T)(200.0 / (double)a.nx_global);
+    const T* yn = use_seg ? (pb->num_inner > 0 ? ckpt + (size_t)(n / pb->num_inner) * nx : nullptr) : hist + (size_t)n * nx;
+    OZ_REQUIRE(yn != nullptr || !pb->field_bar, "a field cotangent needs the final state (hist, or ckpt with num_inner > 0)");
+    const unsigned gb = (unsigned)((nx + 255) / 256);
+    pde_terminal_kernel<T><<<gb, 256, 0, st>>>(nx, yn, (const T*)pb->final_bar,
+                                              hist_bar ? hist_bar + (size_t)n * nx : nullptr, a.field_bar, a.fb_scale, lam[0]);
+    int cur = 0;
+    for (int o = nseg - 1; o >= 0; --o) {
+        const int lo = o * ni;
+        if (use_seg) {
+            // replay the segment from its checkpoint (time_marching_uniform.py:77-125)
+            const T* start = (pb->num_inner > 0) ? ckpt + (size_t)o * nx : (const T*)pb->y0;
+            OZ_CUDA_CHECK(cudaMemcpyAsync(seg, start, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
+            for (int q = 0; q + 1 < ni; ++q) {
+                PdeArgs<T> f = a;
+                f.y_in = seg + (size_t)q * vec;
+                f.y_out = seg + (size_t)(q + 1) * vec;
+                f.h = h + lo + q;
+                f.u_lo = u + lo + q;
+                f.u_hi = u + lo + q + 1;
+                f.part_sq = nullptr;
+                pde_step_kernel<T, S><<<(unsigned)L.ncta_f, kPdeBlock, 0, st>>>(f);
+            }
+        }
+        for (int k = lo + ni - 1; k >= lo; --k) {
+            a.y_in = use_seg ? seg + (size_t)(k - lo) * vec : hist + (size_t)k * nx;
+            a.lam_in = lam[cur];
+            a.lam_out = (k == 0 && pb->y0_bar) ? (T*)pb->y0_bar : lam[cur ^ 1];
+            a.hist_bar_k = hist_bar ? hist_bar + (size_t)k * nx : nullptr;
+            a.h = h + k;
+            a.u_lo = u + k;
+            a.u_hi = u + k + 1;
+            a.part_h = ph + (size_t)k * L.ncta_a;
+            a.part_ulo = pulo + (size_t)k * L.ncta_a;
+            a.part_uhi = puhi + (size_t)k * L.ncta_a;
+            pde_adjoint_step_kernel<T, S><<<(unsigned)L.ncta_a, kPdeBlock, 0, st>>>(a);
+            cur ^= 1;
+        }
+    }
+    OZ_CUDA_CHECK(cudaGetLastError());
+    if (pb->h_bar || pb->p_bar) {
+        pde_grads_kernel<T><<<n + 1, 256, 0, st>>>(n, L.ncta_a, ph, pulo, puhi, u, a.field_bar, (T*)pb->h_bar, (T*)pb->p_bar);
+        OZ_CUDA_CHECK(cudaGetLastError());
+    }
+    return 0;
+}
+
+template <typename T>
+static int pde_by_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
+#define OZ_PDE_CASE(SS)                                                              \
+    case SS:                                                                         \
+        if (mode == TM_FORWARD) return pde_forward<T, SS>(pb);                       \
+        if (mode == TM_ADJOINT) return pde_adjoint<T, SS>(pb);                       \
+        if (mode == TM_ADJOINT_WS) {                                                 \
+            *ws_bytes = pde_layout<SS>(pb).total_adj * sizeof(T);                    \
+            return 0;                                                                \
+        }                                                                            \
+        *ws_bytes = pde_layout<SS>(pb).total_fwd * sizeof(T);                        \
+        return 0;
+    switch (pb->num_stages) {
+        OZ_PDE_CASE(1)
+        OZ_PDE_CASE(2)
+        OZ_PDE_CASE(3)
+        OZ_PDE_CASE(4)
+        OZ_PDE_CASE(7)
+    }
+#undef OZ_PDE_CASE
+    set_error("no grid kernel for %d stages", pb->num_stages);
+    return -1;
+}
+
+// mode: TM_FORWARD, TM_ADJOINT, TM_ADJOINT_WS, 100 = forward workspace query
+int pde_dispatch(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    OZ_REQUIRE(mode != TM_RHS_EVAL || ev, "internal: missing eval args");
+    if (mode == TM_RHS_EVAL) {
+        set_error("oz_rhs_eval is not available for the grid right-hand side");
+        return -1;
+    }
+    OZ_REQUIRE(pb->is_explicit, "the grid right-hand side supports explicit methods only "
+                                "(an implicit step would be a %d x %d Newton system per step)", pb->d_override, pb->d_override);
+    OZ_REQUIRE(pb->N == 1, "the grid right-hand side integrates one trajectory (N = 1)");
+    OZ_REQUIRE(pb->d_override >= 1, "d_override (number of cells) must be set");
+    OZ_REQUIRE(pb->h_shared, "the grid right-hand side needs a shared step vector");
+    return pb->dtype == OZ_F64 ? pde_by_stage<double>(pb, mode, ws_bytes) : pde_by_stage<float>(pb, mode, ws_bytes);
+}
+
+}  // namespace oz

@@ -141,9 +141,22 @@ def tm_forward(spec: SolveSpec, y0, h, p=None, th=None, keep_history=None):
     pb.hist, pb.ckpt, pb.yfinal = _ptr(out['hist']), _ptr(out['ckpt']), _ptr(out['final'])
     pb.prof, pb.field = _ptr(out['prof']), _ptr(out['field'])
     pb.status, pb.iters = _ptr(out['status']), _ptr(out['iters'])
+    ws = _forward_workspace(pb, dev)
     nat.check(nat.lib.oz_tm_forward(C.byref(pb)), 'oz_tm_forward')
-    del keep
+    del keep, ws
     return out
+
+
+def _forward_workspace(pb, dev):
+    """Grid right-hand sides need scratch for the forward sweep too (ping-pong state + partial sums)."""
+    ws_bytes = nat.lib.oz_tm_forward_workspace_bytes(C.byref(pb))
+    if ws_bytes == C.c_size_t(-1).value:
+        raise nat.OzError(f'oz_tm_forward_workspace_bytes: {nat.lib.oz_last_error().decode()}')
+    if ws_bytes == 0:
+        return None
+    ws = torch.empty(ws_bytes, dtype=torch.uint8, device=dev)
+    pb.ws, pb.ws_bytes = ws.data_ptr(), ws_bytes
+    return ws
 
 
 def tm_adjoint(spec: SolveSpec, y0, h, p, th, hist=None, ckpt=None, hist_bar=None, final_bar=None,
@@ -283,6 +296,10 @@ class TmPlan:
         ws_bytes = nat.lib.oz_tm_adjoint_workspace_bytes(C.byref(pb))
         if ws_bytes == C.c_size_t(-1).value:
             raise nat.OzError(f'oz_tm_adjoint_workspace_bytes: {nat.lib.oz_last_error().decode()}')
+        fwd_bytes = nat.lib.oz_tm_forward_workspace_bytes(C.byref(pb))
+        if fwd_bytes == C.c_size_t(-1).value:
+            raise nat.OzError(f'oz_tm_forward_workspace_bytes: {nat.lib.oz_last_error().decode()}')
+        ws_bytes = max(ws_bytes, fwd_bytes)           # forward and adjoint never run concurrently: one buffer
         self.ws = torch.empty(max(ws_bytes, 8), dtype=torch.uint8, device=dev)
         pb.ws, pb.ws_bytes = self.ws.data_ptr(), ws_bytes
         self.pb = pb

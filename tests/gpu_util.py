@@ -26,7 +26,7 @@ def make_spec(case, method, dtype=torch.float64, num_inner=0, store_history=True
     extra = {}
     if case['rhs'] == 'diffusion_reaction':
         nx = case['nx']
-        extra = dict(d_override=nx, rhs_cfg=(np.pi / nx, 16.0, 2.0, 2.0))
+        extra = dict(d_override=nx, rhs_cfg=(np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx))))
     return engine.SolveSpec(
         rhs_name=case['rhs'], method=get_integration_method(method), N=N, n=n, dtype=dtype,
         h_shared=(h.ndim == 1), p_shared=(p is None or p.shape[-1] == 1),

@@ -119,3 +119,25 @@ def test_zero_step_size_is_legal():
     c = cases.lotka_volterra_inputs(N=3, nt=3)
     c['h'] = np.array([0.0, 0.1])
     _compare(c, 'RK4')
+
+
+# ---------------------------------------------------------------------------------------------
+# config C3: nonlinear diffusion-reaction grid (pde_control.py), explicit methods, fused stages
+@pytest.mark.parametrize('method', ['ForwardEuler', 'HeunsMethod', 'KuttaThirdOrder', 'RK4', 'RK6'])
+@pytest.mark.parametrize('nx', [50, 3001])
+def test_config3_diffusion_reaction_grid_history_mode(method, nx):
+    c = cases.pde_inputs(nx=nx, n=12)
+    _compare(c, method)
+
+
+@pytest.mark.parametrize('nx,n,ni', [(777, 16, 4), (4100, 24, 6), (50, 9, 3)])
+def test_config3_checkpointed_grid_adjoint(nx, n, ni):
+    # TimeMarchingCheckpoints on the grid: only nc+1 states kept, segments replayed in the reverse sweep
+    c = cases.pde_inputs(nx=nx, n=n)
+    _compare(c, 'RK4', num_inner=ni, store_history=False)
+
+
+def test_config3_grid_fp32():
+    c = cases.pde_inputs(nx=2000, n=10)
+    # states to 1e-5; the step-size gradient sums O(1/dx^2) terms of both signs, fp32 keeps ~3 digits of it
+    _compare(c, 'RK4', torch.float32, fwd_tol=1e-5, grad_tol=5e-3)
