@@ -2,17 +2,18 @@
 """Headline benchmark: state-steps/s (forward + adjoint) of BASELINE.json config C2
 (Van der Pol, Gauss-Legendre 6 TimeMarching + adjoint, 65,536 parameter sets per GPU, nt = 40).
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload ...]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload NAME]
 
 One JSON line on rank 0.  A "step" = one forward solve + one reverse sweep over the whole batch
-(gradient of sum_b J_b(tf) w.r.t. every control value u[t, b] and every step size h[k]).
+(C2: gradient of sum_b J_b(tf) w.r.t. every control value u[t, b] and every step size h[k]).
   value : state-steps/s, inputs resident in HBM, CUDA-event time of the kernels, L2 flushed
-          between steps, max over ranks.  state-steps = N * d * n  (d = 3 states, n = 39 steps).
-  e2e   : same metric through the plan API with HOST (pinned) inputs: H2D of u and h, solve,
-          reverse sweep, D2H of the objective and both gradients inside the timed region.
-  roofline / cpu_baseline : see DESIGN.md section "Measurement".
-Under torchrun every rank owns its own 65,536 trajectories (weak scaling); the only collective
-is the all-reduce of the batch-shared gradient h_bar (39 scalars).
+          between steps, max over ranks.  state-steps = N * d * n.
+  e2e   : same metric through the plan API with HOST (pinned) inputs: H2D of the inputs, solve,
+          reverse sweep, D2H of the objective and the gradients inside the timed region.
+  roofline / cpu_baseline : see DESIGN.md "Measurement".
+Under torchrun every rank owns its own batch (weak scaling); the only collective is the
+all-reduce of the gradients of batch-shared inputs (a few hundred scalars).
+Other workloads (--workload) cover the remaining BASELINE configs; the default is the headline.
 """
 import argparse
 import json
@@ -27,21 +28,35 @@ import numpy as np
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
 
+# name: dict(kind, rhs, method, N per GPU, nt, horizon, dtype)
 WORKLOADS = {
-    # name: (rhs, method, N per GPU, nt, horizon)
-    'van_der_pol_gl6_tm_adjoint_N65536_nt40': ('van_der_pol', 'GaussLegendre6', 65536, 40, 15.0),
-    'van_der_pol_gl4_tm_adjoint_N65536_nt40': ('van_der_pol', 'GaussLegendre4', 65536, 40, 15.0),
-    'van_der_pol_gl2_tm_adjoint_N65536_nt40': ('van_der_pol', 'GaussLegendre2', 65536, 40, 15.0),
-    'lotka_volterra_rk4_tm_adjoint_N1M_nt101': ('lotka_volterra', 'RK4', 1 << 20, 101, 0.9),
-    'lotka_volterra_rk4_tm_adjoint_N1M_nt101_fp32': ('lotka_volterra', 'RK4', 1 << 20, 101, 0.9),
+    'van_der_pol_gl6_tm_adjoint_N65536_nt40': dict(kind='tm', rhs='van_der_pol', method='GaussLegendre6', N=65536, nt=40, T=15.0),
+    'van_der_pol_gl4_tm_adjoint_N65536_nt40': dict(kind='tm', rhs='van_der_pol', method='GaussLegendre4', N=65536, nt=40, T=15.0),
+    'van_der_pol_gl2_tm_adjoint_N65536_nt40': dict(kind='tm', rhs='van_der_pol', method='GaussLegendre2', N=65536, nt=40, T=15.0),
+    'lotka_volterra_rk4_tm_adjoint_N1M_nt101': dict(kind='tm', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9),
+    'lotka_volterra_rk4_tm_adjoint_N1M_nt101_fp32': dict(kind='tm', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, fp32=True),
+    'lotka_volterra_rk4_picard_adjoint_N1M_nt101': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9),
+    'lotka_volterra_rk4_picard_adjoint_N1M_nt101_fp32': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, fp32=True),
+    'diffusion_reaction_rk4_checkpoints_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32),
+    'lunar_ascent_rk4_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='RK4', N=16384, nt=101, T=0.1),
+    'lunar_ascent_gl6_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='GaussLegendre6', N=16384, nt=101, T=0.1),
 }
 DEFAULT_WORKLOAD = 'van_der_pol_gl6_tm_adjoint_N65536_nt40'
 
+ASCENT_IC = np.array([0.061663494666509, 0.055249439788994, -1.004110522066614, -0.465976472038572,
+                      -0.416909510597800, -0.084973690970470, 11846.599614336959 / 15103.])
 
-def synth_inputs(rhs, N, nt, horizon, seed):
+
+def synth_inputs(wl, N, seed):
     """Seeded synthetic batch of the named shape."""
     rng = np.random.default_rng(seed)
-    h = np.full(nt - 1, horizon / (nt - 1))
+    rhs, nt = wl['rhs'], wl['nt']
+    if rhs == 'diffusion_reaction':
+        nx = wl['nx']
+        dx = np.pi / nx
+        return dict(y0=0.5 * np.ones((nx, 1)), h=np.full(nt - 1, 0.4 * dx * dx),
+                    p=rng.uniform(-0.6, 0.0, size=(nt, 1, 1)), th=None)
+    h = np.full(nt - 1, wl['T'] / (nt - 1))
     if rhs == 'van_der_pol':
         return dict(y0=np.tile(np.array([[1.0], [1.0], [0.0]]), (1, N)), h=h,
                     p=rng.uniform(-0.75, 1.0, size=(nt, 1, N)), th=None)
@@ -49,18 +64,9 @@ def synth_inputs(rhs, N, nt, horizon, seed):
         t = np.arange(nt)
         return dict(y0=rng.uniform(1.5, 2.5, size=(2, N)), h=h, p=(1.0 + t / nt / 5.0).reshape(nt, 1, 1),
                     th=rng.uniform(0.4, 0.6, size=(1, N)))
+    if rhs == 'lunar_ascent':
+        return dict(y0=np.tile(ASCENT_IC[:, None], (1, N)), h=h, p=rng.uniform(-1.0, 1.0, size=(nt, 3, N)), th=None)
     raise KeyError(rhs)
-
-
-def algorithmic_bytes(rhs_info, N, n, w, p_shared, hist_cot):
-    """Compulsory HBM bytes of one forward and one adjoint launch (DESIGN.md 'Measurement')."""
-    d, P = rhs_info['d'], rhs_info['P']
-    pN = 1 if p_shared else N
-    fwd = w * (d * N + (n + 1) * P * pN + (n + 1) * d * N + d * N)      # y0, p | hist (incl. IC row), final
-    adj = w * (n * d * N + d * N + (n + 1) * P * pN + (n + 1) * P * pN)  # y_0..y_{n-1}, final_bar, p | p_bar
-    if hist_cot:
-        adj += w * (n + 1) * d * N
-    return fwd, adj
 
 
 class ClockSampler:
@@ -104,40 +110,74 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
+# CPU arm: the oracle (numpy port of the reference algorithm) on the host cores
 def _oracle_chunk(args):
     os.environ['OPENBLAS_NUM_THREADS'] = '1'      # as the reference's scripts do (ozone/tests/run_ode.py:2-4)
-    rhs_name, method, case = args
+    wl, case = args
     from oracle import rhs as R, integrators as I, adjoint as Adj
-    rhs = R.REGISTRY[rhs_name]()
-    out = I.time_marching(rhs, method, case['y0'], case['h'], case['p'], case['th'])
+    kind, method = wl['kind'], wl['method']
+    if wl['rhs'] == 'diffusion_reaction':
+        rhs = R.DiffusionReaction(case['y0'].shape[0])
+        out = I.time_marching(rhs, method, case['y0'], case['h'], case['p'], case['th'])
+        g = Adj.tm_adjoint(rhs, method, case['y0'], case['h'], case['p'], case['th'], history=out['history'],
+                           field_bar=np.ones_like(out['field']))
+        return float(out['field'].sum()), float(np.abs(g['p']).sum())
+    rhs = R.REGISTRY[wl['rhs']]()
+    if kind == 'colloc':
+        from oracle.tableaux import tableau
+        n, s = len(case['h']), tableau(method)[0].shape[0]
+        Y, y = I.collocation_guess(case['y0'], n, s)
+        c1, c2 = I.collocation_residual(rhs, method, case['y0'], case['h'], Y, y, case['p'], case['th'])
+        g = Adj.colloc_vjp(rhs, method, case['y0'], case['h'], Y, y, case['p'], case['th'], np.ones_like(c1), np.ones_like(c2))
+        return float(c1.sum()), float(np.abs(g['p']).sum())
+    if kind == 'picard':
+        out = I.picard(rhs, method, case['y0'], case['h'], case['p'], case['th'], tol=1e-12,
+                       state_blocks=[slice(0, 1), slice(1, 2)])
+    else:
+        out = I.time_marching(rhs, method, case['y0'], case['h'], case['p'], case['th'])
     fb = np.zeros_like(out['final'])
     fb[-1] = 1.0
     g = Adj.tm_adjoint(rhs, method, case['y0'], case['h'], case['p'], case['th'], history=out['history'], final_bar=fb)
     return float(out['final'][-1].sum()), float(np.abs(g['p']).sum())
 
 
-def cpu_port_throughput(rhs_name, method, nt, horizon, cores, traj_per_core, repeats=1):
-    """Time the oracle (numpy port of the reference algorithm) on `cores` processes, each solving
-    and differentiating `traj_per_core` trajectories.  Returns (state-steps/s, sample string)."""
+def cpu_port_throughput(wl, cores, units_per_core, repeats=1):
+    """Time the oracle on `cores` processes, each working on `units_per_core` trajectories (or, for
+    the grid workload, a grid of that many cells and 64 steps).  Returns (state-steps/s, sample, seconds)."""
     import multiprocessing as mp
     from ozone_b200 import _native as nat
-    d = nat.rhs_info(nat.RHS_IDS[rhs_name])['d']
     jobs = []
+    w = dict(wl)
+    if wl['rhs'] == 'diffusion_reaction':
+        w.update(nx=units_per_core, nt=65)
+        d, n = units_per_core, 64
+        per_job = d * n
+        what = f'{cores} processes x one {units_per_core}-cell grid, 64 steps'
+    else:
+        d = nat.rhs_info(nat.RHS_IDS[wl['rhs']])['d']
+        n = wl['nt'] - 1
+        per_job = units_per_core * d * n
+        what = f'{cores} processes x {units_per_core} trajectories'
     for c in range(cores):
-        case = synth_inputs(rhs_name, traj_per_core, nt, horizon, seed=100 + c)
-        jobs.append((rhs_name, method, case))
+        jobs.append((w, synth_inputs(w, units_per_core, seed=100 + c)))
     ctx = mp.get_context('fork')
     best = float('inf')
     with ctx.Pool(cores) as pool:
-        pool.map(_oracle_chunk, jobs[:cores])          # warm-up (imports, page-in)
+        small = dict(w)
+        if wl['rhs'] == 'diffusion_reaction':
+            small.update(nx=64)
+        pool.map(_oracle_chunk, [(small, synth_inputs(small, 8, seed=1))] * cores)     # warm-up (imports, page-in)
         for _ in range(repeats):
             t0 = time.perf_counter()
             pool.map(_oracle_chunk, jobs)
             best = min(best, time.perf_counter() - t0)
-    units = cores * traj_per_core * d * (nt - 1)
-    sample = (f'{cores} processes x {traj_per_core} trajectories, numpy oracle port (OPENBLAS_NUM_THREADS=1 each), '
-              f'forward + adjoint, best of {repeats}')
-    return units / best, sample, best
+    sample = (f'{what}, numpy oracle port of the reference algorithm (OPENBLAS_NUM_THREADS=1 each), '
+              f'{wl["kind"]} forward + adjoint, best of {repeats}')
+    return cores * per_job / best, sample, best
+
+
+CPU_SAMPLE = {'tm': 4096, 'picard': 256, 'colloc': 2048, 'grid': 4096}       # per core, ~10-30 s of CPU work in total
+CPU_SAMPLE_REF = {'tm': 1024, 'picard': 64, 'colloc': 512, 'grid': 2048}      # per step of --impl reference
 
 
 def run_reference(args, rank, world):
@@ -145,15 +185,15 @@ def run_reference(args, rank, world):
     (csdl_alpha is an un-vendored, uninstallable dependency), so this times the oracle port."""
     if rank != 0:
         return
-    rhs, method, N, nt, horizon = WORKLOADS[args.workload]
+    wl = WORKLOADS[args.workload]
     cores = os.cpu_count() or 1
-    per_core = args.cpu_traj_per_core or 1024
+    per_core = args.cpu_traj_per_core or CPU_SAMPLE_REF[wl['kind']]
     vals = []
     for _ in range(max(args.warmup, 0)):
-        cpu_port_throughput(rhs, method, nt, horizon, cores, max(per_core // 4, 8))
+        cpu_port_throughput(wl, cores, max(per_core // 4, 8))
     t_all = 0.0
     for _ in range(args.steps):
-        v, sample, dt = cpu_port_throughput(rhs, method, nt, horizon, cores, per_core)
+        v, sample, dt = cpu_port_throughput(wl, cores, per_core)
         vals.append(v)
         t_all += dt
     value = float(np.mean(vals))
@@ -161,8 +201,7 @@ def run_reference(args, rank, world):
         'impl': 'reference', 'metric': 'state-steps/sec (fwd+adjoint)', 'value': value, 'unit': 'state-steps/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t_all / args.steps,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': args.workload, 'note': 'each step is a bounded sample of the workload: '
-                   f'{cores * per_core} of {N} trajectories, same nt/method'},
+        'config': {'workload': args.workload, 'note': f'each step is a bounded sample of the workload ({sample})'},
         'cpu_baseline': {'value': value, 'unit': 'state-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
@@ -171,6 +210,133 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------
+class Runner:
+    """One workload on one rank: device-resident step (fwd, adj timed separately) and e2e step."""
+
+    def __init__(self, wl, name, rank, dev, args):
+        import torch
+        from ozone_b200 import engine
+        from ozone_b200.glms import get_integration_method
+        self.torch, self.engine = torch, engine
+        self.wl, self.kind = wl, wl['kind']
+        self.dtype = torch.float32 if wl.get('fp32') else torch.float64
+        self.w = 4 if wl.get('fp32') else 8
+        N, nt = wl['N'], wl['nt']
+        self.n = nt - 1
+        case = synth_inputs(wl, N, seed=rank)
+        self.p_shared = case['p'].shape[-1] == 1
+        extra = {}
+        if self.kind == 'grid':
+            nx = wl['nx']
+            extra = dict(d_override=nx, rhs_cfg=(np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx))),
+                         num_inner=self.n // wl['nc'], store_history=False)
+        if self.kind == 'picard':
+            extra = dict(state_blocks=(0, 1, 2))
+        self.spec = spec = engine.SolveSpec(
+            rhs_name=wl['rhs'], method=get_integration_method(wl['method']), N=N, n=self.n, dtype=self.dtype,
+            h_shared=True, p_shared=self.p_shared, th_shared=False, newton_tol=args.newton_tol,
+            **({'store_history': True} if self.kind != 'grid' else {}), **extra)
+        self.d = spec.d
+        self.units = N * self.d * self.n
+        want = ('h', 'p', 'th') if wl['rhs'] == 'lotka_volterra' else (('y0', 'h', 'p') if self.kind == 'grid' else ('h', 'p'))
+        cot = ('field',) if self.kind == 'grid' else ('final',)
+        self.plan = plan = engine.TmPlan(spec, device=dev, grads=want, cotangents=cot)
+        t = lambda a: torch.tensor(np.ascontiguousarray(a), dtype=self.dtype)
+        self.host = {'y0': t(case['y0']).pin_memory(), 'h': t(case['h']).pin_memory(),
+                     'p': t(case['p'][:, :, 0] if self.p_shared else case['p']).pin_memory()}
+        if case['th'] is not None:
+            self.host['th'] = t(case['th']).pin_memory()
+        for k, v in self.host.items():
+            getattr(plan, k).copy_(v)
+        if self.kind == 'grid':
+            plan.field_bar.fill_(1.0)
+        else:
+            plan.final_bar.zero_()
+            plan.final_bar[-1].fill_(1.0) if wl['rhs'] == 'van_der_pol' else plan.final_bar.fill_(1.0)
+        self.host_out = {k: torch.empty_like(g, device='cpu').pin_memory() for k, g in plan.grad.items() if g is not None}
+        self.obj = plan.field if self.kind == 'grid' else plan.final[-1]
+        self.host_obj = torch.empty_like(self.obj, device='cpu').pin_memory()
+        self.e2e_inputs = ('h', 'p')
+        self.h2d = sum(self.host[k].numel() * self.w for k in self.e2e_inputs)
+        self.d2h = sum(v.numel() * self.w for v in self.host_out.values()) + self.host_obj.numel() * self.w
+        self.launches = plan.launches_forward + plan.launches_adjoint
+        if self.kind == 'picard':
+            self.launches = 1 + plan.launches_adjoint
+        if self.kind == 'colloc':
+            s = spec.method.num_stages
+            rng = np.random.default_rng(1000 + rank)
+            dev_t = lambda a: torch.tensor(a, dtype=self.dtype, device=dev)
+            self.Y = dev_t(np.broadcast_to(case['y0'], (self.n, s, self.d, N)).copy())      # collections.py:129-133
+            self.y = dev_t(np.broadcast_to(case['y0'], (self.n, self.d, N)).copy())
+            self.mu1 = dev_t(rng.standard_normal((self.n, s, self.d, N)))
+            self.mu2 = dev_t(rng.standard_normal((self.n, self.d, N)))
+            self.launches = 2 + 1       # residual, vjp, h_bar reducer
+            self.host_colloc = None
+
+    # -- pieces timed separately on the device
+    def forward(self):
+        if self.kind == 'picard':
+            pl = self.plan
+            self.pic = self.engine.picard_forward(self.spec, pl.y0, pl.h, pl.p, pl.th, tol=1e-12 if self.w == 8 else 1e-4)
+        elif self.kind == 'colloc':
+            pl = self.plan
+            self.c = self.engine.colloc_residual(self.spec, pl.y0, pl.h, pl.p, pl.th, self.Y, self.y)
+        else:
+            self.plan.forward()
+
+    def adjoint(self):
+        if self.kind == 'picard':
+            pl = self.plan
+            self.g = self.engine.tm_adjoint(self.spec, pl.y0, pl.h, pl.p, pl.th, hist=self.pic['hist'], final_bar=pl.final_bar,
+                                            need=('h', 'p', 'th'))
+        elif self.kind == 'colloc':
+            pl = self.plan
+            self.g = self.engine.colloc_vjp(self.spec, pl.y0, pl.h, pl.p, pl.th, self.Y, self.y, self.mu1, self.mu2,
+                                            need=('h', 'p'))
+        else:
+            self.plan.adjoint()
+
+    def shared_grad(self):
+        if self.kind in ('picard', 'colloc'):
+            return self.g['h']
+        return self.plan.grad['h']
+
+    def e2e(self):
+        pl = self.plan
+        for k in self.e2e_inputs:
+            getattr(pl, k).copy_(self.host[k], non_blocking=True)
+        self.forward()
+        self.adjoint()
+
+    def e2e_readback(self):
+        if self.kind in ('picard', 'colloc'):
+            src = self.pic['final'][-1] if self.kind == 'picard' else self.c[1][-1, 0]
+            self.host_obj.copy_(src, non_blocking=True)
+            for k, v in self.host_out.items():
+                if self.g.get(k) is not None:
+                    v.copy_(self.g[k], non_blocking=True)
+        else:
+            self.host_obj.copy_(self.obj, non_blocking=True)
+            for k, v in self.host_out.items():
+                v.copy_(self.plan.grad[k], non_blocking=True)
+
+    def algorithmic_bytes(self):
+        """Compulsory HBM bytes of one forward and one adjoint call (DESIGN.md 'Measurement')."""
+        w, N, n, d = self.w, self.wl['N'], self.n, self.d
+        P = self.spec.info['P']
+        pN = 1 if self.p_shared else N
+        if self.kind == 'grid':       # per cell-step: fwd 2w; replay 2w; adjoint step 3w  (SURVEY 8d)
+            return 2 * w * d * n, 5 * w * d * n
+        if self.kind == 'colloc':
+            s = self.spec.method.num_stages
+            fwd = w * (2 * n * s * d * N + 2 * n * d * N + (n + 1) * P * pN)          # read Y, y, p; write c1, c2
+            adj = w * (3 * n * s * d * N + 3 * n * d * N + 2 * (n + 1) * P * pN)      # read mu1, mu2, Y, p; write Ybar, ybar, pbar
+            return fwd, adj
+        fwd = w * (d * N + (n + 1) * P * pN + (n + 1) * d * N + d * N)                # y0, p | hist (incl. IC row), final
+        adj = w * (n * d * N + d * N + (n + 1) * P * pN + (n + 1) * P * pN)           # y_0..y_{n-1}, final_bar, p | p_bar
+        return fwd, adj
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -179,7 +345,7 @@ def main():
     ap.add_argument('--impl', default='ours', choices=['ours', 'reference'])
     ap.add_argument('--workload', default=DEFAULT_WORKLOAD, choices=sorted(WORKLOADS))
     ap.add_argument('--cpu-traj-per-core', type=int, default=None,
-                    help='CPU sample size per core (default 4096 for cpu_baseline, 1024 per step for --impl reference)')
+                    help='CPU sample size per core (defaults: CPU_SAMPLE / CPU_SAMPLE_REF tables)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--newton-tol', type=float, default=1e-7)
     args = ap.parse_args()
@@ -194,8 +360,6 @@ def main():
 
     import torch
     import torch.distributed as dist
-    from ozone_b200 import engine, _native as nat
-    from ozone_b200.glms import get_integration_method
 
     if not torch.cuda.is_available():
         raise SystemExit('bench.py needs a CUDA device: ozone_b200 has no CPU path')
@@ -205,38 +369,9 @@ def main():
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
 
-    rhs, method, N, nt, horizon = WORKLOADS[args.workload]
-    fp32 = args.workload.endswith('fp32')
-    dtype = torch.float32 if fp32 else torch.float64
-    w = 4 if fp32 else 8
-    n = nt - 1
-    case = synth_inputs(rhs, N, nt, horizon, seed=rank)
-    p_shared = case['p'].shape[-1] == 1
-    spec = engine.SolveSpec(rhs_name=rhs, method=get_integration_method(method), N=N, n=n, dtype=dtype, h_shared=True,
-                            p_shared=p_shared, th_shared=False, store_history=True, newton_tol=args.newton_tol)
-    d = spec.d
-    want = ('h', 'p', 'th') if rhs == 'lotka_volterra' else ('h', 'p')
-    plan = engine.TmPlan(spec, device=dev, grads=want, cotangents=('final',))
-
-    # host (pinned) inputs and results for the e2e leg
-    def pin(a):
-        return torch.tensor(np.ascontiguousarray(a), dtype=dtype).pin_memory()
-    host = {'y0': pin(case['y0']), 'h': pin(case['h']), 'p': pin(case['p'][:, :, 0] if p_shared else case['p'])}
-    if case['th'] is not None:
-        host['th'] = pin(case['th'])
-    for k, v in host.items():
-        getattr(plan, k).copy_(v)
-    plan.final_bar.zero_()
-    plan.final_bar[-1].fill_(1.0) if rhs == 'van_der_pol' else plan.final_bar.fill_(1.0)
-    host_out = {k: torch.empty_like(g, device='cpu').pin_memory() for k, g in plan.grad.items() if g is not None}
-    host_obj = torch.empty(N, dtype=dtype).pin_memory()
-    h2d = sum(host[k].numel() * w for k in ('h', 'p'))
-    d2h = sum(v.numel() * w for v in host_out.values()) + host_obj.numel() * w
-
+    wl = WORKLOADS[args.workload]
+    run = Runner(wl, args.workload, rank, dev, args)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
-
-    def flush_l2():
-        flush.fill_(rank & 0xff)
 
     def barrier():
         if world > 1:
@@ -244,29 +379,25 @@ def main():
         torch.cuda.synchronize()
 
     def allreduce_shared():
-        if world > 1 and plan.grad['h'] is not None:
-            dist.all_reduce(plan.grad['h'])
+        g = run.shared_grad()
+        if world > 1 and g is not None:
+            dist.all_reduce(g)
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
     def device_step(times):
-        flush_l2()
+        flush.fill_(rank & 0xff)
         e0, e1, e2 = ev(), ev(), ev()
-        e0.record(); plan.forward(); e1.record(); plan.adjoint(); allreduce_shared(); e2.record()
+        e0.record(); run.forward(); e1.record(); run.adjoint(); allreduce_shared(); e2.record()
         times.append((e0, e1, e2))
 
     def e2e_step(times):
-        flush_l2()
+        flush.fill_(rank & 0xff)
         e0, e1 = ev(), ev()
         e0.record()
-        plan.h.copy_(host['h'], non_blocking=True)
-        plan.p.copy_(host['p'], non_blocking=True)
-        plan.forward()
-        plan.adjoint()
+        run.e2e()
         allreduce_shared()
-        host_obj.copy_(plan.final[-1], non_blocking=True)
-        for k, v in host_out.items():
-            v.copy_(plan.grad[k], non_blocking=True)
+        run.e2e_readback()
         e1.record()
         times.append((e0, e1))
 
@@ -297,21 +428,27 @@ def main():
     clocks = sampler.stop() if rank == 0 else None
     e2e_ms = float(np.sum([a.elapsed_time(b) for a, b in etimes]))
 
-    status_bad = int((plan.status != 0).sum().item())
-    mean_newton = float(plan.iters.double().mean().item()) / n
+    plan = run.plan
+    extra_cfg = {}
+    if run.kind == 'tm':
+        extra_cfg['not_converged'] = int((plan.status != 0).sum().item())
+        if not run.spec.method.explicit:
+            extra_cfg['mean_newton_iters_per_step'] = float(plan.iters.double().mean().item()) / run.n
+    if run.kind == 'picard':
+        extra_cfg['not_converged'] = int((run.pic['status'] != 0).sum().item())
+        extra_cfg['mean_sweeps'] = float(run.pic['iters'].double().mean().item())
 
     tot = torch.tensor([step_ms, e2e_ms, float(np.sum(fwd_ms)), float(np.sum(adj_ms))], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     step_ms, e2e_ms, fwd_tot, adj_tot = tot.tolist()
 
-    units_per_step = world * N * d * n
+    units_per_step = world * run.units
     value = units_per_step * args.steps / (step_ms * 1e-3)
     e2e_value = units_per_step * args.steps / (e2e_ms * 1e-3)
 
     if rank == 0:
-        info = spec.info
-        fwd_b, adj_b = algorithmic_bytes(info, N, n, w, p_shared, hist_cot=False)
+        fwd_b, adj_b = run.algorithmic_bytes()
         adj_avg_s = adj_tot / args.steps * 1e-3
         fwd_avg_s = fwd_tot / args.steps * 1e-3
         peaks = {}
@@ -321,30 +458,39 @@ def main():
             pass
         peak = float(peaks.get('hbm_gbs', 6650.0))
         achieved = adj_b / adj_avg_s / 1e9
-        roof = {'bound': 'hbm', 'kernel': 'tm_adjoint_kernel', 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
+        names = {'tm': ('tm_adjoint_kernel', 'tm_forward_kernel'), 'picard': ('tm_adjoint_kernel', 'picard_kernel'),
+                 'grid': ('pde_adjoint_step_kernel (+ replayed pde_step_kernel)', 'pde_step_kernel'),
+                 'colloc': ('colloc_vjp_kernel', 'colloc_residual_kernel')}[run.kind]
+        if run.kind == 'tm' and not run.spec.method.explicit:
+            note = ('implicit GL + Newton is FP64-ALU bound, not HBM bound (DESIGN.md); the HBM fraction is reported '
+                    'because the metric asks for it')
+        else:
+            note = 'HBM-bound path: the fraction is the figure of merit'
+        roof = {'bound': 'hbm', 'kernel': names[0], 'achieved': achieved, 'peak': peak, 'unit': 'GB/s',
                 'frac': achieved / peak, 'traffic': None,
                 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6650 GB/s',
                 'algorithmic_bytes_per_launch': adj_b, 'avg_launch_ms': adj_avg_s * 1e3,
-                'forward_kernel': {'achieved': fwd_b / fwd_avg_s / 1e9, 'frac': fwd_b / fwd_avg_s / 1e9 / peak,
+                'forward_kernel': {'kernel': names[1], 'achieved': fwd_b / fwd_avg_s / 1e9,
+                                   'frac': fwd_b / fwd_avg_s / 1e9 / peak,
                                    'algorithmic_bytes_per_launch': fwd_b, 'avg_launch_ms': fwd_avg_s * 1e3},
-                'note': 'implicit GL + Newton is FP64-ALU bound, not HBM bound (DESIGN.md); HBM fraction reported as the metric asks'
-                        if not spec.method.explicit else 'explicit RK step is HBM/FP64 balanced'}
+                'note': note}
         cpu = None
         if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            v, sample, _ = cpu_port_throughput(rhs, method, nt, horizon, cores, args.cpu_traj_per_core or 4096)
+            v, sample, _ = cpu_port_throughput(wl, cores, args.cpu_traj_per_core or CPU_SAMPLE[run.kind])
             cpu = {'value': v, 'unit': 'state-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample}
         line = {
             'metric': 'state-steps/sec (fwd+adjoint)', 'value': value, 'unit': 'state-steps/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': step_ms / args.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if fp32 else 'f64', 'data': 'synthetic',
-            'config': {'workload': args.workload, 'rhs': rhs, 'method': method, 'approach': 'TimeMarching + adjoint',
-                       'trajectories_per_gpu': N, 'num_times': nt, 'state_size': d, 'newton_tol': args.newton_tol,
-                       'mean_newton_iters_per_step': mean_newton, 'l2': 'flushed (256 MiB write) between timed steps',
-                       'parallelism': f'trajectory-batch x{world}', 'not_converged': status_bad},
-            'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': h2d, 'd2h_bytes_per_step': d2h,
-                    'ms_per_step': e2e_ms / args.steps},
-            'gpu_launches': args.steps * (plan.launches_forward + plan.launches_adjoint),
+            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if wl.get('fp32') else 'f64', 'data': 'synthetic',
+            'config': dict({'workload': args.workload, 'rhs': wl['rhs'], 'method': wl['method'], 'approach': run.kind,
+                            'trajectories_per_gpu': wl['N'], 'num_times': wl['nt'], 'state_size': run.d,
+                            'newton_tol': args.newton_tol, 'l2': 'flushed (256 MiB write) between timed steps',
+                            'parallelism': f'trajectory-batch x{world}' if run.kind != 'grid' else 'replicas only (bench); '
+                            'spatial shard: see ozone_b200/parallel.py'}, **extra_cfg),
+            'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
+                    'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps},
+            'gpu_launches': args.steps * run.launches,
             'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
             'wall_ms_timed_loop': t_wall * 1e3,
         }

@@ -307,6 +307,10 @@ class TmPlan:
         shared_rows = sum(1 for k, flag in (('h', spec.h_shared), ('p', spec.p_shared), ('th', spec.th_shared))
                           if flag and self.grad[k] is not None)
         self.launches_forward, self.launches_adjoint = 1, 1 + shared_rows
+        if spec.info['kind'] == 1:      # grid: one launch per step (+ sum-of-squares, field / terminal, replay, gradient reducers)
+            nseg = (n // spec.num_inner) if (spec.num_inner > 0 and self.hist is None) else 0
+            self.launches_forward = n + 2
+            self.launches_adjoint = 1 + (n - nseg if nseg else 0) + n + 1
 
     def forward(self):
         self.pb.stream = torch.cuda.current_stream().cuda_stream
