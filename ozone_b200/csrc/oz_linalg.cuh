@@ -115,4 +115,83 @@ struct SmemSystem {
     }
 };
 
+
+// ---------------------------------------------------------------------------------------------
+// Register-resident dense solve for small systems (M <= ~9): Gaussian elimination of the augmented
+// system [a | b] with every index static, so the matrix never leaves the register file (the shared-
+// memory LU above is bound by LDS/STS traffic: 3 shared accesses per DFMA).  Threshold partial
+// pivoting: rows are exchanged only when |a_kk| < 0.1 max_r |a_rk| (growth then stays bounded by
+// 11^(M-1) in theory, ~O(10) in practice), which keeps the common path free of data-dependent
+// register shuffling; the exchange itself is a chain of statically indexed, predicated row swaps.
+// The decision depends only on the thread's own data, so a trajectory's result does not depend on
+// its warp neighbours.  On return b holds the solution; false = a zero / non-finite pivot was met.
+// (column K is a template parameter: plain "#pragma unroll" on the column loop is not honoured by nvcc
+// beyond M = 4, which turns every index dynamic and sends the matrix to local memory)
+template <typename T, int M, int K>
+struct RegElim {
+    OZ_D static void run(T (&a)[M][M], T (&b)[M], bool& ok) {
+        if constexpr (K < M - 1) {
+            T best = fabs(a[K][K]);
+            int pr = K;
+#pragma unroll
+            for (int r = K + 1; r < M; ++r) {
+                const T cand = fabs(a[r][K]);
+                if (cand > best) {
+                    best = cand;
+                    pr = r;
+                }
+            }
+            if (fabs(a[K][K]) < T(0.1) * best) swap_rows<K + 1>(a, b, pr);
+        }
+        const T piv = a[K][K];
+        if (!(fabs(piv) > T(0)) || !isfinite(piv)) ok = false;
+        const T inv = T(1) / piv;
+        a[K][K] = inv;
+#pragma unroll
+        for (int r = K + 1; r < M; ++r) {
+            const T l = a[r][K] * inv;
+#pragma unroll
+            for (int c = K + 1; c < M; ++c) a[r][c] -= l * a[K][c];
+            b[r] -= l * b[K];
+        }
+        if constexpr (K + 1 < M) RegElim<T, M, K + 1>::run(a, b, ok);
+    }
+    template <int R>
+    OZ_D static void swap_rows(T (&a)[M][M], T (&b)[M], int pr) {
+        if constexpr (R < M) {
+            if (pr == R) {
+#pragma unroll
+                for (int c = K; c < M; ++c) {
+                    const T t = a[K][c];
+                    a[K][c] = a[R][c];
+                    a[R][c] = t;
+                }
+                const T t = b[K];
+                b[K] = b[R];
+                b[R] = t;
+            }
+            swap_rows<R + 1>(a, b, pr);
+        }
+    }
+};
+
+template <typename T, int M, int Rr>
+struct RegBack {
+    OZ_D static void run(T (&a)[M][M], T (&b)[M]) {
+        T acc = b[Rr];
+#pragma unroll
+        for (int c = Rr + 1; c < M; ++c) acc -= a[Rr][c] * b[c];
+        b[Rr] = acc * a[Rr][Rr];
+        if constexpr (Rr > 0) RegBack<T, M, Rr - 1>::run(a, b);
+    }
+};
+
+template <typename T, int M>
+OZ_D bool reg_solve(T (&a)[M][M], T (&b)[M]) {
+    bool ok = true;
+    RegElim<T, M, 0>::run(a, b, ok);
+    RegBack<T, M, M - 1>::run(a, b);
+    return ok;
+}
+
 }  // namespace oz

@@ -9,6 +9,9 @@
 //   vjp    (y, p, th, v[D])               -> yb[D] += J_y^T v,  pb[P] += J_p^T v,  tb[S] += J_th^T v
 //   out    (y, p, th)                     -> prof[NPROF], field[NFIELD]       (profile / field outputs)
 //   out_vjp(y, p, th, vprof, vfield)      -> yb, pb, tb  +=  transposed output Jacobians
+//   DQ                                    number of TRAILING states no right-hand side depends on (pure
+//                                         quadratures, zero Jacobian columns): the implicit stage solve
+//                                         eliminates them exactly and factors only the (D-DQ)-state system
 //
 // Packed orders follow the order in which the reference script adds states / parameters.
 #pragma once
@@ -19,6 +22,7 @@ namespace oz {
 // examples/simple_examples/lotka_volterra.py:51-62.  y = (y, x); p = (a); th = (c).
 struct RhsLotkaVolterra {
     static constexpr int ID = OZ_RHS_LOTKA_VOLTERRA, D = 2, P = 1, S = 1, NPROF = 1, NFIELD = 1;
+    static constexpr int DQ = 0;
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T* th, T* dy) {
         dy[0] = p[0] * y[0] - T(0.5) * y[0] * y[1];
@@ -53,6 +57,7 @@ struct RhsLotkaVolterra {
 // ozone/paper_examples/van_der_pol/main_model.py:6-14.  y = (x0, x1, J); p = (u).
 struct RhsVanDerPol {
     static constexpr int ID = OZ_RHS_VAN_DER_POL, D = 3, P = 1, S = 0, NPROF = 0, NFIELD = 0;
+    static constexpr int DQ = 1;  // J is a pure quadrature: no right-hand side depends on it
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T*, T* dy) {
         dy[0] = (T(1) - y[1] * y[1]) * y[0] - y[1] + p[0];
@@ -86,6 +91,7 @@ struct RhsVanDerPol {
 // ozone/paper_examples/ascent_system/main_model.py:6-21.  y = (rx, ry, rz, Vx, Vy, Vz, m); p = (ux, uy, uz).
 struct RhsLunarAscent {
     static constexpr int ID = OZ_RHS_LUNAR_ASCENT, D = 7, P = 3, S = 0, NPROF = 0, NFIELD = 0;
+    static constexpr int DQ = 0;
     static constexpr double kT = 1.8335634, kVex = 3049.87, kG0 = 1.625, kR0 = 1738100.0;
     static constexpr double kSqrtG0R0 = 1680.5988516002265;  // sqrt(g0 * R0) = sqrt(2824412.5)
     template <typename T>
@@ -137,6 +143,7 @@ struct RhsLunarAscent {
 // y' = th0*y + th1: test_1_simple/utils.py:6-7 (th = (-1, 0)); tutorial.ipynb (th = (0.5, -3)).
 struct RhsAffine {
     static constexpr int ID = OZ_RHS_AFFINE, D = 1, P = 0, S = 2, NPROF = 0, NFIELD = 0;
+    static constexpr int DQ = 0;
     template <typename T>
     OZ_D static void f(const T* y, const T*, const T* th, T* dy) { dy[0] = th[0] * y[0] + th[1]; }
     template <typename T>
@@ -156,6 +163,7 @@ struct RhsAffine {
 // ozone/tests/test_correctness/test_3_large/utils.py:23-30:  y' = -(y (dp + sp))^2.
 struct RhsQuadDecay {
     static constexpr int ID = OZ_RHS_QUAD_DECAY, D = 1, P = 1, S = 1, NPROF = 0, NFIELD = 0;
+    static constexpr int DQ = 0;
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T* th, T* dy) {
         const T w = y[0] * (p[0] + th[0]);
@@ -185,6 +193,7 @@ struct RhsQuadDecay {
 // profile = ('z' -> z11, 'x' -> x + y^2/4, 'y' -> z*z01*z10 + e^2 + a + d (2x2)); field = ('y' -> c*y, 'z' -> c*z).
 struct RhsGeneral3 {
     static constexpr int ID = OZ_RHS_GENERAL3, D = 6, P = 8, S = 1, NPROF = 6, NFIELD = 5;
+    static constexpr int DQ = 0;
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T* th, T* dy) {
         dy[0] = p[0] * y[0] - p[1] * y[0] * y[1];

@@ -17,6 +17,14 @@ struct Dims {
                          NF1 = AtLeast1<NF>::value;
 };
 
+// Implicit stage systems up to this many unknowns (after eliminating quadrature states) are solved in
+// registers (reg_solve); larger ones go through the shared-memory LU.
+// (fp64: a 6 x 6 augmented system is ~170 registers with the pivoting code; 7 x 7 already spills in context)
+template <class R, int S, typename T>
+constexpr bool use_reg_solve() {
+    return S * (R::D - R::DQ) <= (sizeof(T) == 4 ? 8 : 6);
+}
+
 // row `row` of a [rows][N] (per trajectory) or [rows] (shared) array
 template <typename T>
 OZ_D T ld_in(const T* base, long long row, long long N, long long i, int shared) {
@@ -58,6 +66,94 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 Y[i][c] = y[c] + h * acc;
             }
             R::f(Y[i], ps[i], th, F[i]);
+        }
+    } else if constexpr (use_reg_solve<R, S, T>()) {
+        // Register path.  States are split into DA active and DQ trailing quadrature states (zero Jacobian
+        // columns).  The full Newton system is block triangular, [M_aa 0; M_qa I] dY = -R, so
+        //   dY_a = -M_aa^-1 R_a ,   dY_q = -R_q + h sum_j a_ij J_j[q,a] dY_a[j]
+        // gives exactly the iterates of the full (S D) Newton while factoring only (S DA)^2 entries.
+        constexpr int DA = D - R::DQ, MA = S * DA;
+#pragma unroll
+        for (int i = 0; i < S; ++i)
+#pragma unroll
+            for (int c = 0; c < D; ++c) Y[i][c] = y[c];
+        for (int it = 0;; ++it) {
+#pragma unroll
+            for (int i = 0; i < S; ++i) R::f(Y[i], ps[i], th, F[i]);
+            T Rs[S][D];
+            T rn2 = T(0);
+#pragma unroll
+            for (int i = 0; i < S; ++i)
+#pragma unroll
+                for (int c = 0; c < D; ++c) {
+                    T acc = T(0);
+#pragma unroll
+                    for (int j = 0; j < S; ++j) acc += tab.a(i, j) * F[j][c];
+                    Rs[i][c] = Y[i][c] - h * acc - y[c];
+                    rn2 += Rs[i][c] * Rs[i][c];
+                }
+            if (!(rn2 == rn2)) {
+                status |= OZ_STATUS_NONFINITE;
+                break;
+            }
+            if (sqrt(rn2) < a.newton_tol) break;
+            if (it >= a.newton_max_iter) {
+                status |= OZ_STATUS_NOT_CONVERGED;
+                break;
+            }
+            T Ma[MA][MA], b[MA], Jq[S][R::DQ > 0 ? R::DQ : 1][DA];
+#pragma unroll
+            for (int j = 0; j < S; ++j) {
+                T J[D * D];
+                R::jac(Y[j], ps[j], th, J);
+#pragma unroll
+                for (int i = 0; i < S; ++i) {
+                    const T ha = h * tab.a(i, j);
+#pragma unroll
+                    for (int r = 0; r < DA; ++r)
+#pragma unroll
+                        for (int c = 0; c < DA; ++c)
+                            Ma[i * DA + r][j * DA + c] = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+                }
+#pragma unroll
+                for (int q = 0; q < R::DQ; ++q)
+#pragma unroll
+                    for (int c = 0; c < DA; ++c) Jq[j][q][c] = J[(DA + q) * D + c];
+            }
+#pragma unroll
+            for (int i = 0; i < S; ++i)
+#pragma unroll
+                for (int r = 0; r < DA; ++r) b[i * DA + r] = -Rs[i][r];
+            if (!reg_solve<T, MA>(Ma, b)) {
+                status |= OZ_STATUS_SINGULAR;
+                break;
+            }
+            if constexpr (R::DQ > 0) {
+                T wq[S][R::DQ];
+#pragma unroll
+                for (int j = 0; j < S; ++j)
+#pragma unroll
+                    for (int q = 0; q < R::DQ; ++q) {
+                        T acc = T(0);
+#pragma unroll
+                        for (int c = 0; c < DA; ++c) acc += Jq[j][q][c] * b[j * DA + c];
+                        wq[j][q] = acc;
+                    }
+#pragma unroll
+                for (int i = 0; i < S; ++i)
+#pragma unroll
+                    for (int q = 0; q < R::DQ; ++q) {
+                        T acc = T(0);
+#pragma unroll
+                        for (int j = 0; j < S; ++j) acc += tab.a(i, j) * wq[j][q];
+                        Y[i][DA + q] += -Rs[i][DA + q] + h * acc;
+                    }
+            }
+#pragma unroll
+            for (int i = 0; i < S; ++i)
+#pragma unroll
+                for (int r = 0; r < DA; ++r) Y[i][r] += b[i * DA + r];
+            ++iters;
         }
     } else {
         constexpr int M = S * D;
@@ -268,7 +364,41 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
     T Y[S][D], F[S][D], Yb[S][D];
     solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
 
-    if constexpr (IMPL) {
+    if constexpr (IMPL && use_reg_solve<R, S, T>()) {
+        // M^T = [M_aa^T M_qa^T; 0 I] and the quadrature columns of J are zero, so Ybar_q = 0 and
+        // M_aa^T Ybar_a = blk(J^T)(h b (x) lam) restricted to the active components.
+        constexpr int DA = D - R::DQ, MA = S * DA;
+        T Mt[MA][MA], b[MA];
+#pragma unroll
+        for (int j = 0; j < S; ++j) {
+            T J[D * D];
+            R::jac(Y[j], ps[j], th, J);
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
+                const T ha = h * tab.a(i, j);
+#pragma unroll
+                for (int r = 0; r < DA; ++r)
+#pragma unroll
+                    for (int c = 0; c < DA; ++c)
+                        Mt[j * DA + c][i * DA + r] = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+            }
+#pragma unroll
+            for (int c = 0; c < DA; ++c) {
+                T acc = T(0);
+#pragma unroll
+                for (int r = 0; r < D; ++r) acc += J[r * D + c] * lam[r];
+                b[j * DA + c] = h * tab.B[j] * acc;
+            }
+        }
+        if (!reg_solve<T, MA>(Mt, b)) status |= OZ_STATUS_SINGULAR;
+#pragma unroll
+        for (int i = 0; i < S; ++i) {
+#pragma unroll
+            for (int c = 0; c < DA; ++c) Yb[i][c] = b[i * DA + c];
+#pragma unroll
+            for (int c = DA; c < D; ++c) Yb[i][c] = T(0);
+        }
+    } else if constexpr (IMPL) {
         constexpr int M = S * D;
         using Sys = SmemSystem<T, M>;
         Sys sys = Sys::carve(smem, blockDim.x, threadIdx.x);
