@@ -121,6 +121,10 @@ typedef struct oz_problem {
     void* ws;
     size_t ws_bytes;
     void* stream;
+    /* ---- optional stage cache (implicit methods): [n][s][d][N].  oz_tm_forward stores the converged
+     * stage values Y here; oz_tm_adjoint, given the same buffer, reads them instead of repeating the
+     * Newton solve of every step (it then only factors the transposed system once per step). ---- */
+    void* stages;
 } oz_problem;
 
 /* Library / build identification. */

@@ -44,7 +44,7 @@ class OzProblem(C.Structure):
         ('field', C.c_void_p), ('status', C.c_void_p), ('iters', C.c_void_p),
         ('hist_bar', C.c_void_p), ('final_bar', C.c_void_p), ('prof_bar', C.c_void_p), ('field_bar', C.c_void_p),
         ('y0_bar', C.c_void_p), ('h_bar', C.c_void_p), ('p_bar', C.c_void_p), ('th_bar', C.c_void_p),
-        ('ws', C.c_void_p), ('ws_bytes', C.c_size_t), ('stream', C.c_void_p),
+        ('ws', C.c_void_p), ('ws_bytes', C.c_size_t), ('stream', C.c_void_p), ('stages', C.c_void_p),
     ]
 
 

@@ -86,6 +86,7 @@ struct TmArgs {
     T* h_bar;
     T* p_bar;
     T* th_bar;
+    T* stages;    // optional [n][s][d][N] cache of converged implicit stage values (forward writes, adjoint reads)
     T* ws;        // adjoint scratch (see tm_adjoint_ws_layout)
     long long W;  // number of warps in the grid = partial sums per reduced quantity
 };
@@ -121,6 +122,7 @@ inline TmArgs<T> make_tm_args(const oz_problem* pb) {
     a.h_bar = (T*)pb->h_bar;
     a.p_bar = (T*)pb->p_bar;
     a.th_bar = (T*)pb->th_bar;
+    a.stages = (T*)pb->stages;
     a.ws = (T*)pb->ws;
     a.W = 0;
     return a;

@@ -266,6 +266,13 @@ __global__ void __launch_bounds__(128) tm_forward_kernel(const TmArgs<T> a) {
         load_params<R>(a, k + 1, i, phi);
         stage_params<R, T, S>(a.tab, plo, phi, ps);
         solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
+        if constexpr (IMPL) {
+            if (a.stages)
+#pragma unroll
+                for (int s = 0; s < S; ++s)
+#pragma unroll
+                    for (int c = 0; c < D; ++c) a.stages[(((long long)k * S + s) * D + c) * N + i] = Y[s][c];
+        }
         advance<R, T, S>(a.tab, y, h, F);
         if (a.hist)
 #pragma unroll
@@ -357,12 +364,22 @@ __global__ void __launch_bounds__(256) reduce_rows_kernel(const T* __restrict__ 
 //   explicit: back-substitution i = S-1..0;  implicit: M^T Ybar = blk(J^T)(h b (x) lam), M the Newton matrix
 template <class R, typename T, int S, bool IMPL>
 OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R>::P1], const T* th, T* lam,
-                       T& hb, T* pb_lo, T* pb_hi, T* tb, unsigned char* smem, int& status, int& iters) {
+                       T& hb, T* pb_lo, T* pb_hi, T* tb, unsigned char* smem, int& status, int& iters,
+                       const T* cached_stages, long long N, long long i) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     const Tableau<T>& tab = a.tab;
     T Y[S][D], F[S][D], Yb[S][D];
-    solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
+    if (IMPL && cached_stages) {  // converged stages of this step, stored by the forward sweep
+#pragma unroll
+        for (int s = 0; s < S; ++s) {
+#pragma unroll
+            for (int c = 0; c < D; ++c) Y[s][c] = __ldg(cached_stages + ((long long)s * D + c) * N + i);
+            R::f(Y[s], ps[s], th, F[s]);
+        }
+    } else {
+        solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
+    }
 
     if constexpr (IMPL && use_reg_solve<R, S, T>()) {
         // M^T = [M_aa^T M_qa^T; 0 I] and the quadrature columns of J are zero, so Ybar_q = 0 and
@@ -600,7 +617,8 @@ __global__ void __launch_bounds__(128) tm_adjoint_kernel(const TmArgs<T> a, cons
             load_params<R>(a, k, i, plo);
             stage_params<R, T, S>(a.tab, plo, phi, ps);
             T hb;
-            adjoint_step<R, T, S, IMPL>(a, y, h, ps, th, lam, hb, pb_lo, pb_hi, tb, smem, status, iters);
+            adjoint_step<R, T, S, IMPL>(a, y, h, ps, th, lam, hb, pb_lo, pb_hi, tb, smem, status, iters,
+                                        (IMPL && a.stages && !use_seg) ? a.stages + (long long)k * S * D * N : nullptr, N, i);
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) pb_next[c] += pb_hi[c];
             emit_p(k + 1);

@@ -118,7 +118,7 @@ def _set_inputs(pb, spec, y0, h, p, th):
     return y0, h, p, th
 
 
-def tm_forward(spec: SolveSpec, y0, h, p=None, th=None, keep_history=None):
+def tm_forward(spec: SolveSpec, y0, h, p=None, th=None, keep_history=None, cache_stages=False):
     """oz_tm_forward.  Returns dict(hist, ckpt, final, prof, field, status, iters); absent outputs are None."""
     dev = y0.device
     pb = make_problem(spec)
@@ -141,6 +141,10 @@ def tm_forward(spec: SolveSpec, y0, h, p=None, th=None, keep_history=None):
     pb.hist, pb.ckpt, pb.yfinal = _ptr(out['hist']), _ptr(out['ckpt']), _ptr(out['final'])
     pb.prof, pb.field = _ptr(out['prof']), _ptr(out['field'])
     pb.status, pb.iters = _ptr(out['status']), _ptr(out['iters'])
+    out['stages'] = None
+    if cache_stages and not spec.method.explicit and spec.info['kind'] == 0:
+        out['stages'] = new(spec.n, spec.method.num_stages, d, N)
+        pb.stages = _ptr(out['stages'])
     ws = _forward_workspace(pb, dev)
     nat.check(nat.lib.oz_tm_forward(C.byref(pb)), 'oz_tm_forward')
     del keep, ws
@@ -160,7 +164,7 @@ def _forward_workspace(pb, dev):
 
 
 def tm_adjoint(spec: SolveSpec, y0, h, p, th, hist=None, ckpt=None, hist_bar=None, final_bar=None,
-               prof_bar=None, field_bar=None, need=('y0', 'h', 'p', 'th'), status=None):
+               prof_bar=None, field_bar=None, need=('y0', 'h', 'p', 'th'), status=None, stages=None):
     """oz_tm_adjoint.  Returns dict(y0, h, p, th) of gradients shaped like the inputs."""
     dev = y0.device
     pb = make_problem(spec)
@@ -174,6 +178,8 @@ def tm_adjoint(spec: SolveSpec, y0, h, p, th, hist=None, ckpt=None, hist_bar=Non
     prof_bar = _chk(prof_bar, spec, (nt, spec.info['nprof'], N), 'prof_bar') if spec.info['nprof'] else None
     field_bar = _chk(field_bar, spec, (spec.info['nfield'], N), 'field_bar') if spec.info['nfield'] else None
     pb.hist, pb.ckpt = _ptr(hist), _ptr(ckpt)
+    if stages is not None:
+        pb.stages = _ptr(_chk(stages, spec, (spec.n, spec.method.num_stages, d, N), 'stages'))
     pb.hist_bar, pb.final_bar, pb.prof_bar, pb.field_bar = map(_ptr, (hist_bar, final_bar, prof_bar, field_bar))
     grads = {}
     for k in ('y0', 'h', 'p', 'th'):
@@ -191,6 +197,9 @@ def tm_adjoint(spec: SolveSpec, y0, h, p, th, hist=None, ckpt=None, hist_bar=Non
     return grads
 
 
+STAGE_CACHE_LIMIT = 8 << 30      # bytes; beyond this the reverse sweep re-solves the stages instead
+
+
 class _TimeMarch(torch.autograd.Function):
     """Solve + reverse sweep on the autograd tape.  Inputs are packed; outputs are
     (hist | empty, final, prof | empty, field | empty, status, iters)."""
@@ -200,11 +209,14 @@ class _TimeMarch(torch.autograd.Function):
         needs = [t is not None and t.requires_grad for t in (y0, h, p, th)]
         any_grad = any(needs)
         keep_hist = spec.store_history or (any_grad and spec.num_inner == 0)
-        out = tm_forward(spec, y0, h, p, th, keep_history=keep_hist)
+        # implicit methods: keep the converged stages so the reverse sweep does not repeat the Newton solves
+        stage_bytes = spec.n * spec.method.num_stages * spec.d * spec.N * (8 if spec.dtype == torch.float64 else 4)
+        cache = any_grad and keep_hist and spec.num_inner == 0 and not spec.method.explicit and stage_bytes <= STAGE_CACHE_LIMIT
+        out = tm_forward(spec, y0, h, p, th, keep_history=keep_hist, cache_stages=cache)
         ctx.spec, ctx.needs = spec, needs
         ctx.has = dict(hist=out['hist'] is not None, prof=out['prof'] is not None, field=out['field'] is not None)
         ctx.status = out['status']
-        saved = [y0, h, p, th, out['hist'], out['ckpt']]
+        saved = [y0, h, p, th, out['hist'], out['ckpt'], out['stages']]
         ctx.present = [t is not None for t in saved]
         ctx.save_for_backward(*[t for t in saved if t is not None])
         e = lambda: torch.empty(0, dtype=spec.dtype, device=y0.device)
@@ -221,10 +233,10 @@ class _TimeMarch(torch.autograd.Function):
     def backward(ctx, g_hist, g_final, g_prof, g_field, _gs, _gi):
         spec = ctx.spec
         it = iter(ctx.saved_tensors)
-        y0, h, p, th, hist, ckpt = [next(it) if present else None for present in ctx.present]
+        y0, h, p, th, hist, ckpt, stages = [next(it) if present else None for present in ctx.present]
         need = tuple(k for k, flag in zip(('y0', 'h', 'p', 'th'), ctx.needs) if flag)
         fix = lambda g, ok: g.contiguous() if (ok and g is not None and g.numel() > 0) else None
-        grads = tm_adjoint(spec, y0, h, p, th, hist=hist, ckpt=ckpt,
+        grads = tm_adjoint(spec, y0, h, p, th, hist=hist, ckpt=ckpt, stages=stages,
                            hist_bar=fix(g_hist, ctx.hist_returned), final_bar=fix(g_final, True),
                            prof_bar=fix(g_prof, ctx.has['prof']), field_bar=fix(g_field, ctx.has['field']),
                            need=need, status=ctx.status)
@@ -262,7 +274,8 @@ class TmPlan:
     kernels (no allocation, no host sync).  This is what a caller inside an optimisation loop
     uses; ``bench.py`` times it."""
 
-    def __init__(self, spec: SolveSpec, device='cuda', grads=('y0', 'h', 'p', 'th'), cotangents=('final',)):
+    def __init__(self, spec: SolveSpec, device='cuda', grads=('y0', 'h', 'p', 'th'), cotangents=('final',),
+                 cache_stages=True):
         self.spec = spec
         dev = torch.device(device)
         d, N, n, nt = spec.d, spec.N, spec.n, spec.nt
@@ -293,6 +306,10 @@ class TmPlan:
         pb.hist_bar, pb.final_bar = _ptr(self.hist_bar), _ptr(self.final_bar)
         pb.prof_bar, pb.field_bar = _ptr(self.prof_bar), _ptr(self.field_bar)
         pb.y0_bar, pb.h_bar, pb.p_bar, pb.th_bar = (_ptr(self.grad[k]) for k in ('y0', 'h', 'p', 'th'))
+        self.stages = None
+        if cache_stages and not spec.method.explicit and info['kind'] == 0 and self.hist is not None:
+            self.stages = new(n, spec.method.num_stages, d, N)
+            pb.stages = _ptr(self.stages)
         ws_bytes = nat.lib.oz_tm_adjoint_workspace_bytes(C.byref(pb))
         if ws_bytes == C.c_size_t(-1).value:
             raise nat.OzError(f'oz_tm_adjoint_workspace_bytes: {nat.lib.oz_last_error().decode()}')

@@ -59,11 +59,11 @@ def unshare(g, ref):
     return g.reshape(ref.shape) if g.size == ref.size else g
 
 
-def run_pair(case, method, dtype=torch.float64, cot_seed=0, tol=1e-7, num_inner=0, store_history=True):
+def run_pair(case, method, dtype=torch.float64, cot_seed=0, tol=1e-7, num_inner=0, store_history=True, cache_stages=False):
     """Forward + adjoint through the engine and through the oracle with the same random cotangents."""
     spec = make_spec(case, method, dtype, num_inner=num_inner, store_history=store_history, tol=tol)
     y0, h, p, th = dev_inputs(case, spec)
-    fwd = engine.tm_forward(spec, y0, h, p, th, keep_history=store_history)
+    fwd = engine.tm_forward(spec, y0, h, p, th, keep_history=store_history, cache_stages=cache_stages)
     rhs = oracle_rhs(case)
     if num_inner:
         ref = I.time_marching_checkpoints(rhs, method, case['y0'], case['h'], case['p'], case['th'],
@@ -79,7 +79,7 @@ def run_pair(case, method, dtype=torch.float64, cot_seed=0, tol=1e-7, num_inner=
     dt = spec.dtype
     t = lambda a: None if a is None else torch.tensor(a, dtype=dt, device='cuda')
     g = engine.tm_adjoint(spec, y0, h, p, th, hist=fwd['hist'], ckpt=fwd['ckpt'], hist_bar=t(hb), final_bar=t(fb),
-                          prof_bar=t(pb), field_bar=t(qb), status=fwd['status'])
+                          prof_bar=t(pb), field_bar=t(qb), status=fwd['status'], stages=fwd.get('stages'))
     torch.cuda.synchronize()
     gref = Adj.tm_adjoint(rhs, method, case['y0'], case['h'], case['p'], case['th'], history=ref['history'],
                           hist_bar=hb, final_bar=fb, prof_bar=pb, field_bar=qb, tol=tol)

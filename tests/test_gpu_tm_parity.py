@@ -96,6 +96,16 @@ def test_config2_van_der_pol_reference_newton_tolerance():
     assert np.array_equal(np_(fwd['iters']), ref['newton_iters'].sum(axis=0))
 
 
+@pytest.mark.parametrize('method', ['GaussLegendre6', 'Trapezoidal', 'RadauII5'])
+def test_config2_adjoint_from_cached_stages_equals_resolve(method):
+    # the forward sweep can hand its converged stage values to the reverse sweep (no second Newton solve)
+    c = cases.van_der_pol_inputs(N=130)
+    _, _, _, g1, gref = _compare(c, method, tol=1e-12, cache_stages=True)
+    _, _, _, g2, _ = _compare(c, method, tol=1e-12, cache_stages=False)
+    for k in ('y0', 'h', 'p'):
+        assert relerr(np_(g1[k]), np_(g2[k])) < 1e-13, k      # same stage values; only FMA contraction may differ
+
+
 def test_config2_fp32():
     _compare(cases.van_der_pol_inputs(N=64), 'GaussLegendre4', torch.float32, tol=1e-5, fwd_tol=2e-5, grad_tol=2e-4)
 
