@@ -332,8 +332,11 @@ class Runner:
             fwd = w * (2 * n * s * d * N + 2 * n * d * N + (n + 1) * P * pN)          # read Y, y, p; write c1, c2
             adj = w * (3 * n * s * d * N + 3 * n * d * N + 2 * (n + 1) * P * pN)      # read mu1, mu2, Y, p; write Ybar, ybar, pbar
             return fwd, adj
-        fwd = w * (d * N + (n + 1) * P * pN + (n + 1) * d * N + d * N)                # y0, p | hist (incl. IC row), final
-        adj = w * (n * d * N + d * N + (n + 1) * P * pN + (n + 1) * P * pN)           # y_0..y_{n-1}, final_bar, p | p_bar
+        info = self.spec.info
+        S, tN = info['S'], (1 if self.spec.th_shared else N)
+        outs = ((n + 1) * info['nprof'] + info['nfield']) * N                         # profile rows + field sums the RHS declares
+        fwd = w * (d * N + (n + 1) * P * pN + S * tN + (n + 1) * d * N + d * N + outs)   # y0, p, th | hist (incl. IC row), final, outputs
+        adj = w * (n * d * N + d * N + (n + 1) * P * pN + S * tN + (n + 1) * P * pN + S * tN)   # y_0..y_{n-1}, final_bar, p, th | p_bar, th_bar
         return fwd, adj
 
 

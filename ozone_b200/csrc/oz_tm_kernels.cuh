@@ -25,6 +25,11 @@ constexpr bool use_reg_solve() {
     return S * (R::D - R::DQ) <= (sizeof(T) == 4 ? 8 : 6);
 }
 
+// Pull a line towards L1 ahead of its use.  The reverse sweep runs at 2-4 warps per scheduler (the
+// stage arrays take 120-255 registers), too few to hide a DRAM round trip behind other warps, and every
+// step starts with loads that nothing else depends on: their addresses are known one step ahead.
+OZ_D void prefetch_l1(const void* p) { asm volatile("prefetch.global.L1 [%0];" ::"l"(p)); }
+
 // row `row` of a [rows][N] (per trajectory) or [rows] (shared) array
 template <typename T>
 OZ_D T ld_in(const T* base, long long row, long long N, long long i, int shared) {
@@ -609,10 +614,51 @@ __global__ void __launch_bounds__(128) tm_adjoint_kernel(const TmArgs<T> a, cons
                 for (int c = 0; c < DM::P; ++c) qlo[c] = qhi[c];
             }
         }
-        for (int k = lo + ni - 1; k >= lo; --k) {
-            const T* src = state_ptr(k);
+        // y_k is fetched one iteration ahead so that its load latency overlaps the previous step's arithmetic:
+        // into registers for explicit methods, as an L1 prefetch for implicit ones (no registers to spare there)
+        constexpr bool PRELOAD = !IMPL;
+        T ynext[D];
+        if constexpr (PRELOAD) {
+            const T* src = state_ptr(lo + ni - 1);
 #pragma unroll
-            for (int c = 0; c < D; ++c) y[c] = use_seg ? src[c * N + i] : __ldg(src + c * N + i);
+            for (int c = 0; c < D; ++c) ynext[c] = use_seg ? src[c * N + i] : __ldg(src + c * N + i);
+        }
+        for (int k = lo + ni - 1; k >= lo; --k) {
+            if constexpr (PRELOAD) {
+#pragma unroll
+                for (int c = 0; c < D; ++c) y[c] = ynext[c];
+            } else {
+                const T* src = state_ptr(k);
+#pragma unroll
+                for (int c = 0; c < D; ++c) y[c] = use_seg ? src[c * N + i] : __ldg(src + c * N + i);
+            }
+            if (k > lo) {  // next iteration's inputs (step k-1)
+                const T* nsrc = state_ptr(k - 1);
+                if constexpr (PRELOAD) {
+#pragma unroll
+                    for (int c = 0; c < D; ++c) ynext[c] = use_seg ? nsrc[c * N + i] : __ldg(nsrc + c * N + i);
+                } else {
+#pragma unroll
+                    for (int c = 0; c < D; ++c) prefetch_l1(nsrc + c * N + i);
+                }
+                if (!a.p_shared)
+#pragma unroll
+                    for (int c = 0; c < DM::P; ++c) prefetch_l1(a.p + ((long long)(k - 1) * DM::P + c) * N + i);
+                if (!a.h_shared) prefetch_l1(a.h + (long long)(k - 1) * N + i);
+                if (a.hist_bar)
+#pragma unroll
+                    for (int c = 0; c < D; ++c) prefetch_l1(a.hist_bar + ((long long)(k - 1) * D + c) * N + i);
+                if constexpr (DM::NP > 0) {
+                    if (a.prof_bar)
+#pragma unroll
+                        for (int c = 0; c < DM::NP; ++c) prefetch_l1(a.prof_bar + ((long long)(k - 1) * DM::NP + c) * N + i);
+                }
+                if constexpr (IMPL) {
+                    if (a.stages && !use_seg)
+#pragma unroll
+                        for (int c = 0; c < S * D; ++c) prefetch_l1(a.stages + ((long long)(k - 1) * S * D + c) * N + i);
+                }
+            }
             const T h = ld_in(a.h, k, N, i, a.h_shared);
             load_params<R>(a, k, i, plo);
             stage_params<R, T, S>(a.tab, plo, phi, ps);
