@@ -63,6 +63,14 @@ enum {
     OZ_RHS_COUNT = 7
 };
 
+/* Slab mode runs a long solve as consecutive time segments (one call each).  The state at a segment
+ * boundary belongs to both segments; these flags keep its output terms from being counted twice. */
+enum {
+    OZ_GRID_SKIP_IC_FIELD = 1,        /* forward: the k = 0 term of the field sum was counted by the previous segment */
+    OZ_GRID_SKIP_TERMINAL_FIELD = 2,  /* adjoint: the k = n direct field cotangent is added by the next segment */
+    OZ_GRID_NO_CONTROL_COST = 4       /* this rank does not own the 20 u^2 term of J_space (one rank does) */
+};
+
 enum { OZ_STATUS_OK = 0, OZ_STATUS_NOT_CONVERGED = 1, OZ_STATUS_SINGULAR = 2, OZ_STATUS_NONFINITE = 4 };
 
 /* One descriptor for the forward solve and its adjoint.  Unused pointers are NULL. */
@@ -94,6 +102,7 @@ typedef struct oz_problem {
      * of a grid of grid_nx_global cells; only local cells [grid_own_lo, grid_own_hi) count in the grid-wide
      * sums (J_space, u_bar, h_bar).  Used by the spatial shard; 0 = the whole grid is local. */
     int64_t grid_x_off, grid_nx_global, grid_own_lo, grid_own_hi;
+    int64_t grid_flags;   /* OZ_GRID_* bits: how a time segment of a sharded solve joins its neighbours */
     /* ---- inputs ---- */
     const void* y0;
     const void* h;

@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_HERE, 'liboz_b200.so')
 OZ_MAX_STAGES = 7
 OZ_F64, OZ_F32 = 0, 1
 STATUS_NOT_CONVERGED, STATUS_SINGULAR, STATUS_NONFINITE = 1, 2, 4
+GRID_SKIP_IC_FIELD, GRID_SKIP_TERMINAL_FIELD, GRID_NO_CONTROL_COST = 1, 2, 4
 
 RHS_IDS = {
     'lotka_volterra': 0,
@@ -38,7 +39,7 @@ class OzProblem(C.Structure):
         ('newton_tol', C.c_double), ('newton_max_iter', C.c_int32), ('reserved0', C.c_int32),
         ('rhs_cfg', C.c_double * 8),
         ('num_state_blocks', C.c_int32), ('state_block_lo', C.c_int32 * 9),
-        ('grid_x_off', C.c_int64), ('grid_nx_global', C.c_int64), ('grid_own_lo', C.c_int64), ('grid_own_hi', C.c_int64),
+        ('grid_x_off', C.c_int64), ('grid_nx_global', C.c_int64), ('grid_own_lo', C.c_int64), ('grid_own_hi', C.c_int64), ('grid_flags', C.c_int64),
         ('y0', C.c_void_p), ('h', C.c_void_p), ('p', C.c_void_p), ('th', C.c_void_p),
         ('hist', C.c_void_p), ('ckpt', C.c_void_p), ('yfinal', C.c_void_p), ('prof', C.c_void_p),
         ('field', C.c_void_p), ('status', C.c_void_p), ('iters', C.c_void_p),

@@ -276,13 +276,13 @@ __global__ void pde_terminal_kernel(long long nx, const T* __restrict__ yn, cons
 
 // field = sum_k [ (100/nx) sum_cta part_sq[k][cta] + 20 u_k^2 ]   (one block, fixed order)
 template <typename T>
-__global__ void __launch_bounds__(256) pde_field_kernel(const T* __restrict__ part_sq, int nt, long long ncta,
+__global__ void __launch_bounds__(256) pde_field_kernel(const T* __restrict__ part_sq, int k0, int nt, long long ncta,
                                                         const T* __restrict__ u, T scale, T own_u, T* __restrict__ field) {
     __shared__ T red[32];
     T acc = T(0);
-    for (long long q = threadIdx.x; q < (long long)nt * ncta; q += blockDim.x) acc += part_sq[q];
+    for (long long q = (long long)k0 * ncta + threadIdx.x; q < (long long)nt * ncta; q += blockDim.x) acc += part_sq[q];
     acc *= scale;
-    for (int k = threadIdx.x; k < nt; k += blockDim.x) acc += own_u * T(20) * u[k] * u[k];
+    for (int k = k0 + threadIdx.x; k < nt; k += blockDim.x) acc += own_u * T(20) * u[k] * u[k];
     const T s = block_sum(acc, red);
     if (threadIdx.x == 0) field[0] = s;
 }
@@ -292,7 +292,7 @@ template <typename T>
 __global__ void __launch_bounds__(256) pde_grads_kernel(int n, long long ncta, const T* __restrict__ part_h,
                                                         const T* __restrict__ part_ulo, const T* __restrict__ part_uhi,
                                                         const T* __restrict__ u, const T* __restrict__ field_bar,
-                                                        T* __restrict__ h_bar, T* __restrict__ u_bar) {
+                                                        int k_cost_end, T* __restrict__ h_bar, T* __restrict__ u_bar) {
     __shared__ T red[32];
     const int k = blockIdx.x;  // 0..n
     T ah = T(0), au = T(0);
@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(256) pde_grads_kernel(int n, long long ncta, c
     T s = block_sum(ah, red);
     if (threadIdx.x == 0 && k < n && h_bar) h_bar[k] = s;
     s = block_sum(au, red);
-    if (threadIdx.x == 0 && u_bar) u_bar[k] = s + (field_bar ? T(40) * field_bar[0] * u[k] : T(0));
+    if (threadIdx.x == 0 && u_bar) u_bar[k] = s + ((field_bar && k < k_cost_end) ? T(40) * field_bar[0] * u[k] : T(0));
 }
 
 struct PdeLayout {
@@ -426,8 +426,9 @@ static int pde_forward(const oz_problem* pb) {
     if (pb->yfinal && cur != (const T*)pb->yfinal)
         OZ_CUDA_CHECK(cudaMemcpyAsync(pb->yfinal, cur, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
     if (pb->field) {
-        pde_field_kernel<T><<<1, 256, 0, st>>>(part_sq, n + 1, L.ncta_f, u, (T)(100.0 / (double)a.nx_global),
-                                               (T)((pb->grid_nx_global > 0 && pb->grid_x_off + pb->grid_own_lo != 0) ? 0.0 : 1.0), (T*)pb->field);
+        pde_field_kernel<T><<<1, 256, 0, st>>>(part_sq, (pb->grid_flags & OZ_GRID_SKIP_IC_FIELD) ? 1 : 0, n + 1, L.ncta_f, u,
+                                               (T)(100.0 / (double)a.nx_global),
+                                               (T)((pb->grid_flags & OZ_GRID_NO_CONTROL_COST) ? 0.0 : 1.0), (T*)pb->field);
         OZ_CUDA_CHECK(cudaGetLastError());
     }
     if (pb->status) OZ_CUDA_CHECK(cudaMemsetAsync(pb->status, 0, sizeof(int), st));
@@ -466,8 +467,8 @@ static int pde_adjoint(const oz_problem* pb) {
     const T* yn = use_seg ? (pb->num_inner > 0 ? ckpt + (size_t)(n / pb->num_inner) * nx : nullptr) : hist + (size_t)n * nx;
     OZ_REQUIRE(yn != nullptr || !pb->field_bar, "a field cotangent needs the final state (hist, or ckpt with num_inner > 0)");
     const unsigned gb = (unsigned)((nx + 255) / 256);
-    pde_terminal_kernel<T><<<gb, 256, 0, st>>>(nx, yn, (const T*)pb->final_bar,
-                                              hist_bar ? hist_bar + (size_t)n * nx : nullptr, a.field_bar, a.fb_scale, lam[0]);
+    pde_terminal_kernel<T><<<gb, 256, 0, st>>>(nx, yn, (const T*)pb->final_bar, hist_bar ? hist_bar + (size_t)n * nx : nullptr,
+                                              (pb->grid_flags & OZ_GRID_SKIP_TERMINAL_FIELD) ? nullptr : a.field_bar, a.fb_scale, lam[0]);
     int cur = 0;
     for (int o = nseg - 1; o >= 0; --o) {
         const int lo = o * ni;
@@ -504,7 +505,8 @@ static int pde_adjoint(const oz_problem* pb) {
     }
     OZ_CUDA_CHECK(cudaGetLastError());
     if (pb->h_bar || pb->p_bar) {
-        pde_grads_kernel<T><<<n + 1, 256, 0, st>>>(n, L.ncta_a, ph, pulo, puhi, u, a.field_bar, (T*)pb->h_bar, (T*)pb->p_bar);
+        const int k_cost_end = (pb->grid_flags & OZ_GRID_NO_CONTROL_COST) ? 0 : ((pb->grid_flags & OZ_GRID_SKIP_TERMINAL_FIELD) ? n : n + 1);
+        pde_grads_kernel<T><<<n + 1, 256, 0, st>>>(n, L.ncta_a, ph, pulo, puhi, u, a.field_bar, k_cost_end, (T*)pb->h_bar, (T*)pb->p_bar);
         OZ_CUDA_CHECK(cudaGetLastError());
     }
     return 0;

@@ -35,6 +35,7 @@ class SolveSpec:
     rhs_cfg: tuple = ()
     want_status: bool = True
     state_blocks: tuple = ()           # Picard: packed-component offsets of the states (block Gauss-Seidel order)
+    grid_slab: tuple = ()              # grid RHS slab mode: (x_off, nx_global, own_lo, own_hi, flags)
     info: dict = field(default_factory=dict)
 
     def __post_init__(self):
@@ -90,6 +91,8 @@ def make_problem(spec: SolveSpec) -> nat.OzProblem:
     pb.newton_tol, pb.newton_max_iter = float(spec.newton_tol), int(spec.newton_max_iter)
     for i, v in enumerate(spec.rhs_cfg):
         pb.rhs_cfg[i] = float(v)
+    if spec.grid_slab:
+        pb.grid_x_off, pb.grid_nx_global, pb.grid_own_lo, pb.grid_own_hi, pb.grid_flags = (int(v) for v in spec.grid_slab)
     if spec.state_blocks:
         pb.num_state_blocks = len(spec.state_blocks) - 1
         for i, v in enumerate(spec.state_blocks):

@@ -151,3 +151,27 @@ def test_config3_grid_fp32():
     c = cases.pde_inputs(nx=2000, n=10)
     # states to 1e-5; the step-size gradient sums O(1/dx^2) terms of both signs, fp32 keeps ~3 digits of it
     _compare(c, 'RK4', torch.float32, fwd_tol=1e-5, grad_tol=5e-3)
+
+
+def test_config3_spatial_slabs_match_the_single_slab_solve():
+    # the spatial shard of ozone_b200/parallel.py with 3 ranks emulated on one GPU: owned cells, the field
+    # output and every gradient must equal the undivided checkpointed solve (halo 2*s*n_inner, one exchange per segment)
+    from ozone_b200 import engine, parallel
+    from ozone_b200.glms import get_integration_method
+    nx, n, ni = 3000, 12, 3
+    c = cases.pde_inputs(nx=nx, n=n)
+    cfg = (np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx)))
+    m = get_integration_method('RK4')
+    t = lambda a: torch.tensor(np.ascontiguousarray(a), dtype=torch.float64, device='cuda')
+    y0, h, u = t(c['y0'][:, 0]), t(c['h']), t(c['p'][:, 0, 0])
+    res = parallel.solve_grid_emulated(m, nx, n, ni, 3, y0, h, u, cfg)
+    spec = engine.SolveSpec(rhs_name='diffusion_reaction', method=m, N=1, n=n, h_shared=True, p_shared=True,
+                            th_shared=True, num_inner=ni, store_history=False, d_override=nx, rhs_cfg=cfg)
+    fwd = engine.tm_forward(spec, y0.reshape(-1, 1), h, u.reshape(-1, 1), None, keep_history=False)
+    g = engine.tm_adjoint(spec, y0.reshape(-1, 1), h, u.reshape(-1, 1), None, ckpt=fwd['ckpt'],
+                          field_bar=torch.ones(1, 1, dtype=torch.float64, device='cuda'))
+    assert relerr(np_(res['final']), np_(fwd['final'][:, 0])) < 1e-13
+    assert relerr(np_(res['field']), np_(fwd['field'])) < 1e-13
+    assert relerr(np_(res['y0_bar']), np_(g['y0'][:, 0])) < 1e-12
+    assert relerr(np_(res['h_bar']), np_(g['h'])) < 1e-12
+    assert relerr(np_(res['u_bar']), np_(g['p'])) < 1e-12
