@@ -10,7 +10,7 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, 'liboz_b200.so')
+LIB_PATH = os.environ.get('OZONE_B200_LIB') or os.path.join(_HERE, 'liboz_b200.so')   # env override: A/B builds
 
 OZ_MAX_STAGES = 7
 OZ_F64, OZ_F32 = 0, 1

@@ -25,6 +25,28 @@ constexpr bool use_reg_solve() {
     return S * (R::D - R::DQ) <= (sizeof(T) == 4 ? 8 : 6);
 }
 
+// Occupancy targets (threads per block, minimum resident blocks per SM) per kernel flavour.  Implicit
+// kernels that solve in registers run 64-thread blocks; the second number caps registers per thread.
+#ifndef OZ_MB_IMPL_FWD
+#define OZ_MB_IMPL_FWD 4
+#endif
+#ifndef OZ_MB_IMPL_ADJ
+#define OZ_MB_IMPL_ADJ 4
+#endif
+#ifndef OZ_MB_EXPL_ADJ
+#define OZ_MB_EXPL_ADJ 5
+#endif
+template <class R, int S, typename T, bool IMPL>
+constexpr int lb_threads() {
+    return (IMPL && use_reg_solve<R, S, T>()) ? 64 : 128;
+}
+template <class R, int S, typename T, bool IMPL, bool ADJ>
+constexpr int lb_blocks() {
+    if (IMPL && use_reg_solve<R, S, T>()) return ADJ ? OZ_MB_IMPL_ADJ : OZ_MB_IMPL_FWD;
+    if (!IMPL && ADJ) return OZ_MB_EXPL_ADJ;
+    return 1;
+}
+
 // Pull a line towards L1 ahead of its use.  The reverse sweep runs at 2-4 warps per scheduler (the
 // stage arrays take 120-255 registers), too few to hide a DRAM round trip behind other warps, and every
 // step starts with loads that nothing else depends on: their addresses are known one step ahead.
@@ -235,7 +257,8 @@ OZ_D void advance(const Tableau<T>& tab, T* y, T h, const T (*F)[R::D]) {
 
 // =============================================================================================
 template <class R, typename T, int S, bool IMPL>
-__global__ void __launch_bounds__(128) tm_forward_kernel(const TmArgs<T> a) {
+__global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S, T, IMPL, false>()))
+    tm_forward_kernel(const TmArgs<T> a) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -522,7 +545,8 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
 }
 
 template <class R, typename T, int S, bool IMPL>
-__global__ void __launch_bounds__(128) tm_adjoint_kernel(const TmArgs<T> a, const AdjWsPtr<T> ws) {
+__global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S, T, IMPL, true>()))
+    tm_adjoint_kernel(const TmArgs<T> a, const AdjWsPtr<T> ws) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     constexpr bool HAS_OUT = (DM::NP + DM::NF) > 0;

@@ -42,7 +42,7 @@ class DeviceRHS:
         return self._rename.get(name, name)
 
     def names(self, which):
-        return [(self._n(n), tuple(s)) for n, s in getattr(self, which)]
+        return [(self._n(n), None if s is None else tuple(s)) for n, s in getattr(self, which)]
 
     @property
     def rhs_id(self):
