@@ -60,7 +60,8 @@ enum {
     OZ_RHS_QUAD_DECAY = 4,          /* ozone/tests/test_correctness/test_3_large/utils.py:23-30 */
     OZ_RHS_GENERAL3 = 5,            /* ozone/tests/test_correctness/test_2_general/utils.py:43-84 */
     OZ_RHS_DIFFUSION_REACTION = 6,  /* ozone/paper_examples/pde_control/pde_control.py:11-81 */
-    OZ_RHS_COUNT = 7
+    OZ_RHS_COUNT = 7,
+    OZ_RHS_PLUGIN_BASE = 1000       /* ids handed out by oz_register_rhs_plugin */
 };
 
 /* Slab mode runs a long solve as consecutive time segments (one call each).  The state at a segment
@@ -174,6 +175,12 @@ OZ_API int oz_colloc_residual(const oz_problem* pb, const void* Y, const void* y
 OZ_API size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb);
 OZ_API int oz_colloc_vjp(const oz_problem* pb, const void* Y, const void* y, const void* mu1, const void* mu2,
                   void* Y_bar, void* y_bar);
+
+/* Register a right-hand side compiled separately (ozone_b200/trace.py turns a Python callback into CUDA
+ * source and builds it against the same kernel templates).  `so_path` is a shared object exporting
+ * `oz_plugin_describe`; returns the rhs_id to put in oz_problem.rhs_id (>= OZ_RHS_PLUGIN_BASE) or < 0.
+ * This is what stands in for "any Python f" of ozone/func_wrapper.py:90-107. */
+OZ_API int oz_register_rhs_plugin(const char* so_path);
 
 /* No counterpart in the reference.  Same reverse sweep as oz_tm_adjoint, for callers that cannot
  * allocate device memory (plug-ins inside a host application that owns the GPU, real-time loops,

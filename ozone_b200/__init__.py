@@ -15,6 +15,7 @@ from . import timespan as timespans
 from . import approaches
 from . import methods
 from . import rhs
+from . import ops
 from .func_wrapper import ODEVars
 from .collections import IntegratorOutputs
 from .utils import set_default_dtype

@@ -1,5 +1,8 @@
 // extern "C" boundary of liboz_b200.so (declared in include/ozone_b200.h).
 #include <cstdarg>
+#include <dlfcn.h>
+#include <mutex>
+#include "oz_plugin.h"
 #include "oz_common.cuh"
 #include "oz_rhs.cuh"
 #include "oz_tm_launch.cuh"
@@ -54,9 +57,26 @@ static const RhsInfo kInfo[OZ_RHS_COUNT] = {
     {-1, 1, 0, 0, 1, 1},  // diffusion-reaction: d = nx comes from d_override
 };
 
+// ---- right-hand sides registered at run time (plugins built by ozone_b200/trace.py) -------------------
+constexpr int kMaxPlugins = 256;
+static oz_plugin_info g_plugins[kMaxPlugins];
+static int g_num_plugins = 0;
+static std::mutex g_plugin_mu;
+
+static const oz_plugin_info* plugin_of(int rhs_id) {
+    const int slot = rhs_id - OZ_RHS_PLUGIN_BASE;
+    if (slot < 0 || slot >= g_num_plugins) return nullptr;
+    return &g_plugins[slot];
+}
+static bool known_rhs(int rhs_id) { return (rhs_id >= 0 && rhs_id < OZ_RHS_COUNT) || plugin_of(rhs_id) != nullptr; }
+static int plugin_rc(const oz_plugin_info* pl, int rc) {
+    if (rc < 0 && pl->last_error) set_error("%s", pl->last_error());
+    return rc;
+}
+
 static int check_problem(const oz_problem* pb) {
     OZ_REQUIRE(pb != nullptr, "null problem descriptor");
-    OZ_REQUIRE(pb->rhs_id >= 0 && pb->rhs_id < OZ_RHS_COUNT, "unknown rhs_id %d", pb->rhs_id);
+    OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
     OZ_REQUIRE(pb->num_stages >= 1 && pb->num_stages <= OZ_MAX_STAGES, "num_stages %d out of range", pb->num_stages);
     OZ_REQUIRE(pb->N >= 1, "N must be >= 1 (got %lld)", (long long)pb->N);
@@ -67,6 +87,7 @@ static int check_problem(const oz_problem* pb) {
 }
 
 static int route(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    if (const oz_plugin_info* pl = plugin_of(pb->rhs_id)) return plugin_rc(pl, pl->tm(pb, mode, ws_bytes, ev));
     switch (pb->rhs_id) {
         case OZ_RHS_LOTKA_VOLTERRA: return tm_lotka_volterra(pb, mode, ws_bytes, ev);
         case OZ_RHS_VAN_DER_POL: return tm_van_der_pol(pb, mode, ws_bytes, ev);
@@ -90,9 +111,29 @@ int oz_version(void) { return 100; }
 
 const char* oz_last_error(void) { return g_err; }
 
+int oz_register_rhs_plugin(const char* so_path) {
+    OZ_REQUIRE(so_path != nullptr, "null plugin path");
+    std::lock_guard<std::mutex> lock(g_plugin_mu);
+    OZ_REQUIRE(g_num_plugins < kMaxPlugins, "too many right-hand side plugins (%d)", kMaxPlugins);
+    void* handle = dlopen(so_path, RTLD_NOW | RTLD_LOCAL);
+    OZ_REQUIRE(handle != nullptr, "cannot load plugin %s: %s", so_path, dlerror());
+    auto describe = (void (*)(oz_plugin_info*))dlsym(handle, "oz_plugin_describe");
+    OZ_REQUIRE(describe != nullptr, "%s does not export oz_plugin_describe", so_path);
+    oz_plugin_info info;
+    memset(&info, 0, sizeof(info));
+    describe(&info);
+    OZ_REQUIRE(info.abi == OZ_PLUGIN_ABI, "plugin %s was built for plugin ABI %d, this library speaks %d", so_path, info.abi,
+               OZ_PLUGIN_ABI);
+    OZ_REQUIRE(info.tm && info.d >= 1, "plugin %s is incomplete", so_path);
+    g_plugins[g_num_plugins] = info;
+    return OZ_RHS_PLUGIN_BASE + g_num_plugins++;
+}
+
 int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfield, int* kind) {
-    OZ_REQUIRE(rhs_id >= 0 && rhs_id < OZ_RHS_COUNT, "unknown rhs_id %d", rhs_id);
-    const RhsInfo& r = kInfo[rhs_id];
+    OZ_REQUIRE(known_rhs(rhs_id), "unknown rhs_id %d", rhs_id);
+    RhsInfo plug;
+    if (const oz_plugin_info* pl = plugin_of(rhs_id)) plug = RhsInfo{pl->d, pl->P, pl->S, pl->nprof, pl->nfield, 0};
+    const RhsInfo& r = plugin_of(rhs_id) ? plug : kInfo[rhs_id];
     if (d) *d = r.d;
     if (P) *P = r.P;
     if (S) *S = r.S;
@@ -104,7 +145,7 @@ int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfield, int
 
 int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* p, void* dy, void* prof, void* field) {
     OZ_REQUIRE(pb != nullptr, "null problem descriptor");
-    OZ_REQUIRE(pb->rhs_id >= 0 && pb->rhs_id < OZ_RHS_COUNT, "unknown rhs_id %d", pb->rhs_id);
+    OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(nodes >= 0, "negative node count");
     EvalArgs ev{nodes, y, p, dy, prof, field};
     return route(pb, TM_RHS_EVAL, nullptr, &ev);
@@ -112,7 +153,7 @@ int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* 
 
 size_t oz_tm_forward_workspace_bytes(const oz_problem* pb) {
     if (check_problem(pb)) return (size_t)-1;
-    if (kInfo[pb->rhs_id].kind == 0) return 0;
+    if (plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0) return 0;
     size_t bytes = 0;
     if (pde_dispatch(pb, 100, &bytes, nullptr)) return (size_t)-1;
     return bytes;
@@ -140,23 +181,41 @@ int oz_tm_adjoint(const oz_problem* pb) {
 size_t oz_picard_workspace_bytes(const oz_problem* pb) {
     if (check_problem(pb)) return (size_t)-1;
     size_t bytes = 0;
+    if (plugin_of(pb->rhs_id)) return 0;
     if (picard_dispatch(pb, 1, &bytes, nullptr, 0.0, 0)) return (size_t)-1;
     return bytes;
 }
 
 int oz_picard_forward(const oz_problem* pb, const void* guess, double tol, int max_sweeps) {
     if (int rc = check_problem(pb)) return rc;
+    if (const oz_plugin_info* pl = plugin_of(pb->rhs_id)) {
+        OZ_REQUIRE(pb->y0 && pb->h, "y0 and h are required");
+        OZ_REQUIRE(tol > 0.0 && max_sweeps >= 0, "tolerance must be positive and max_sweeps non-negative");
+        int blk[10] = {0, pl->d};
+        int nb = pb->num_state_blocks;
+        if (nb <= 0) nb = 1;
+        else {
+            OZ_REQUIRE(nb <= 8, "at most 8 state blocks");
+            for (int b = 0; b <= nb; ++b) blk[b] = pb->state_block_lo[b];
+        }
+        return plugin_rc(pl, pl->picard(pb, guess, tol, max_sweeps, blk, nb));
+    }
     return picard_dispatch(pb, 0, nullptr, guess, tol, max_sweeps);
 }
 
 int oz_colloc_residual(const oz_problem* pb, const void* Y, const void* y, void* c1, void* c2) {
     if (int rc = check_problem(pb)) return rc;
+    if (const oz_plugin_info* pl = plugin_of(pb->rhs_id)) return plugin_rc(pl, pl->colloc(pb, 0, nullptr, Y, y, nullptr, nullptr, c1, c2));
     return colloc_dispatch(pb, 0, nullptr, Y, y, nullptr, nullptr, c1, c2);
 }
 
 size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb) {
     if (check_problem(pb)) return (size_t)-1;
     size_t bytes = 0;
+    if (const oz_plugin_info* pl = plugin_of(pb->rhs_id)) {
+        if (pl->colloc(pb, 2, &bytes, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr)) return (size_t)-1;
+        return bytes;
+    }
     if (colloc_dispatch(pb, 2, &bytes, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr)) return (size_t)-1;
     return bytes;
 }
@@ -164,6 +223,7 @@ size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb) {
 int oz_colloc_vjp(const oz_problem* pb, const void* Y, const void* y, const void* mu1, const void* mu2, void* Y_bar,
                   void* y_bar) {
     if (int rc = check_problem(pb)) return rc;
+    if (const oz_plugin_info* pl = plugin_of(pb->rhs_id)) return plugin_rc(pl, pl->colloc(pb, 1, nullptr, Y, y, mu1, mu2, Y_bar, y_bar));
     return colloc_dispatch(pb, 1, nullptr, Y, y, mu1, mu2, Y_bar, y_bar);
 }
 

@@ -334,19 +334,22 @@ int run_colloc(const oz_problem* pb, int mode, size_t* ws_bytes, const void* Y, 
 template <class R>
 int dispatch_colloc(const oz_problem* pb, int mode, size_t* ws_bytes, const void* Y, const void* y, const void* mu1,
                     const void* mu2, void* o1, void* o2) {
-#define OZ_COL_CASE(SS)                                                                                      \
-    case SS:                                                                                                 \
-        return pb->dtype == OZ_F64 ? run_colloc<R, double, SS>(pb, mode, ws_bytes, Y, y, mu1, mu2, o1, o2)     \
-                                   : run_colloc<R, float, SS>(pb, mode, ws_bytes, Y, y, mu1, mu2, o1, o2);
-    switch (pb->num_stages) {
-        OZ_COL_CASE(1)
-        OZ_COL_CASE(2)
-        OZ_COL_CASE(3)
-        OZ_COL_CASE(4)
-        OZ_COL_CASE(7)
+#define OZ_COL_CASE(SS)                                                                                          \
+    if constexpr (OZ_WANT_S(SS) && OZ_WANT_KIND(2)) {                                                            \
+        if (pb->num_stages == SS) {                                                                              \
+            if constexpr (OZ_WANT_F64(true))                                                                     \
+                if (pb->dtype == OZ_F64) return run_colloc<R, double, SS>(pb, mode, ws_bytes, Y, y, mu1, mu2, o1, o2); \
+            if constexpr (OZ_WANT_F64(false))                                                                    \
+                if (pb->dtype == OZ_F32) return run_colloc<R, float, SS>(pb, mode, ws_bytes, Y, y, mu1, mu2, o1, o2);  \
+        }                                                                                                        \
     }
+    OZ_COL_CASE(1)
+    OZ_COL_CASE(2)
+    OZ_COL_CASE(3)
+    OZ_COL_CASE(4)
+    OZ_COL_CASE(7)
 #undef OZ_COL_CASE
-    set_error("no collocation kernel for %d stages", pb->num_stages);
+    set_error("no collocation kernel for %d stages / dtype %d in this build", pb->num_stages, pb->dtype);
     return -1;
 }
 

@@ -10,6 +10,28 @@
 #define OZ_HD __host__ __device__ __forceinline__
 #define OZ_D __device__ __forceinline__
 
+// A plugin build instantiates one combination only: -DOZ_ONLY_S=4 -DOZ_ONLY_IMPL=0 -DOZ_ONLY_F64=1
+#ifdef OZ_ONLY_S
+#define OZ_WANT_S(s) ((s) == OZ_ONLY_S)
+#else
+#define OZ_WANT_S(s) true
+#endif
+#ifdef OZ_ONLY_IMPL
+#define OZ_WANT_IMPL(b) ((b) == (OZ_ONLY_IMPL != 0))
+#else
+#define OZ_WANT_IMPL(b) true
+#endif
+#ifdef OZ_ONLY_F64
+#define OZ_WANT_F64(b) ((b) == (OZ_ONLY_F64 != 0))
+#else
+#define OZ_WANT_F64(b) true
+#endif
+#ifdef OZ_ONLY_KIND      /* 0 time marching, 1 picard, 2 collocation */
+#define OZ_WANT_KIND(k) ((k) == OZ_ONLY_KIND)
+#else
+#define OZ_WANT_KIND(k) true
+#endif
+
 namespace oz {
 
 // Thread-local error text behind oz_last_error().

@@ -310,19 +310,22 @@ template <class R>
 int dispatch_picard(const oz_problem* pb, const void* guess, double tol, int max_sweeps, const int* blk_lo, int nblocks) {
     OZ_REQUIRE(nblocks >= 1 && nblocks <= kMaxBlocks, "between 1 and %d state blocks are supported", kMaxBlocks);
     OZ_REQUIRE(blk_lo[0] == 0 && blk_lo[nblocks] == R::D, "state blocks must cover the %d packed components", R::D);
-#define OZ_PICARD_CASE(SS)                                                                               \
-    case SS:                                                                                             \
-        return pb->dtype == OZ_F64 ? run_picard<R, double, SS>(pb, guess, tol, max_sweeps, blk_lo, nblocks) \
-                                   : run_picard<R, float, SS>(pb, guess, tol, max_sweeps, blk_lo, nblocks);
-    switch (pb->num_stages) {
-        OZ_PICARD_CASE(1)
-        OZ_PICARD_CASE(2)
-        OZ_PICARD_CASE(3)
-        OZ_PICARD_CASE(4)
-        OZ_PICARD_CASE(7)
+#define OZ_PICARD_CASE(SS)                                                                                  \
+    if constexpr (OZ_WANT_S(SS) && OZ_WANT_KIND(1)) {                                                       \
+        if (pb->num_stages == SS) {                                                                         \
+            if constexpr (OZ_WANT_F64(true))                                                                \
+                if (pb->dtype == OZ_F64) return run_picard<R, double, SS>(pb, guess, tol, max_sweeps, blk_lo, nblocks); \
+            if constexpr (OZ_WANT_F64(false))                                                               \
+                if (pb->dtype == OZ_F32) return run_picard<R, float, SS>(pb, guess, tol, max_sweeps, blk_lo, nblocks);  \
+        }                                                                                                   \
     }
+    OZ_PICARD_CASE(1)
+    OZ_PICARD_CASE(2)
+    OZ_PICARD_CASE(3)
+    OZ_PICARD_CASE(4)
+    OZ_PICARD_CASE(7)
 #undef OZ_PICARD_CASE
-    set_error("no Picard kernel for %d stages", pb->num_stages);
+    set_error("no Picard kernel for %d stages / dtype %d in this build", pb->num_stages, pb->dtype);
     return -1;
 }
 

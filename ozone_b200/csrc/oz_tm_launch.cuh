@@ -80,21 +80,18 @@ int run_tm(const oz_problem* pb, int mode, size_t* ws_bytes) {
 template <class R, typename T>
 int dispatch_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
     const int s = pb->num_stages;
-    if (pb->is_explicit) {
-        switch (s) {
-            case 1: return run_tm<R, T, 1, false>(pb, mode, ws_bytes);
-            case 2: return run_tm<R, T, 2, false>(pb, mode, ws_bytes);
-            case 3: return run_tm<R, T, 3, false>(pb, mode, ws_bytes);
-            case 4: return run_tm<R, T, 4, false>(pb, mode, ws_bytes);
-            case 7: return run_tm<R, T, 7, false>(pb, mode, ws_bytes);
-        }
-    } else {
-        switch (s) {
-            case 1: return run_tm<R, T, 1, true>(pb, mode, ws_bytes);
-            case 2: return run_tm<R, T, 2, true>(pb, mode, ws_bytes);
-            case 3: return run_tm<R, T, 3, true>(pb, mode, ws_bytes);
-        }
-    }
+#define OZ_TM_CASE(SS, IM)                                                             \
+    if constexpr (OZ_WANT_S(SS) && OZ_WANT_IMPL(IM) && OZ_WANT_KIND(0))                \
+        if (s == SS && (pb->is_explicit != 0) == !(IM)) return run_tm<R, T, SS, IM>(pb, mode, ws_bytes);
+    OZ_TM_CASE(1, false)
+    OZ_TM_CASE(2, false)
+    OZ_TM_CASE(3, false)
+    OZ_TM_CASE(4, false)
+    OZ_TM_CASE(7, false)
+    OZ_TM_CASE(1, true)
+    OZ_TM_CASE(2, true)
+    OZ_TM_CASE(3, true)
+#undef OZ_TM_CASE
     set_error("no kernel for %s method with %d stages", pb->is_explicit ? "an explicit" : "an implicit", s);
     return -1;
 }
@@ -105,20 +102,26 @@ int dispatch_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs
         cudaStream_t stream = (cudaStream_t)pb->stream;
         const unsigned grid = (unsigned)((ev->nodes + 127) / 128);
         if (grid == 0) return 0;
-        if (pb->dtype == OZ_F64)
-            rhs_eval_kernel<R, double><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const double*)ev->y,
-                                                               (const double*)ev->p, (const double*)pb->th,
-                                                               (double*)ev->dy, (double*)ev->prof, (double*)ev->field);
-        else
-            rhs_eval_kernel<R, float><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const float*)ev->y,
-                                                              (const float*)ev->p, (const float*)pb->th, (float*)ev->dy,
-                                                              (float*)ev->prof, (float*)ev->field);
+        if constexpr (OZ_WANT_F64(true)) {
+            if (pb->dtype == OZ_F64)
+                rhs_eval_kernel<R, double><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const double*)ev->y,
+                                                                   (const double*)ev->p, (const double*)pb->th,
+                                                                   (double*)ev->dy, (double*)ev->prof, (double*)ev->field);
+        }
+        if constexpr (OZ_WANT_F64(false)) {
+            if (pb->dtype == OZ_F32)
+                rhs_eval_kernel<R, float><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const float*)ev->y,
+                                                                  (const float*)ev->p, (const float*)pb->th, (float*)ev->dy,
+                                                                  (float*)ev->prof, (float*)ev->field);
+        }
         OZ_CUDA_CHECK(cudaGetLastError());
         return 0;
     }
-    if (pb->dtype == OZ_F64) return dispatch_stage<R, double>(pb, mode, ws_bytes);
-    if (pb->dtype == OZ_F32) return dispatch_stage<R, float>(pb, mode, ws_bytes);
-    set_error("unknown dtype %d", pb->dtype);
+    if constexpr (OZ_WANT_F64(true))
+        if (pb->dtype == OZ_F64) return dispatch_stage<R, double>(pb, mode, ws_bytes);
+    if constexpr (OZ_WANT_F64(false))
+        if (pb->dtype == OZ_F32) return dispatch_stage<R, float>(pb, mode, ws_bytes);
+    set_error("no kernel for dtype %d in this build", pb->dtype);
     return -1;
 }
 

@@ -36,10 +36,16 @@ class SolveSpec:
     want_status: bool = True
     state_blocks: tuple = ()           # Picard: packed-component offsets of the states (block Gauss-Seidel order)
     grid_slab: tuple = ()              # grid RHS slab mode: (x_off, nx_global, own_lo, own_hi, flags)
+    traced: object = None              # trace.TracedRHS: a Python callback compiled to a plugin functor
     info: dict = field(default_factory=dict)
 
     def __post_init__(self):
-        self.rhs_id = nat.RHS_IDS[self.rhs_name]
+        if self.traced is not None:
+            t = self.traced
+            self.rhs_id = None          # resolved per (stages, implicit, dtype, approach) in make_problem
+            self.info = dict(d=t.D, P=t.P, S=t.S, nprof=len(t.prof_exprs), nfield=len(t.field_exprs), kind=0)
+        else:
+            self.rhs_id = nat.RHS_IDS[self.rhs_name]
         if not self.info:
             self.info = nat.rhs_info(self.rhs_id)
         if self.info['kind'] == 1:
@@ -72,13 +78,19 @@ def _chk(t: Optional[torch.Tensor], spec: SolveSpec, shape, name):
     return t.contiguous()
 
 
-def make_problem(spec: SolveSpec) -> nat.OzProblem:
+KIND_TM, KIND_PICARD, KIND_COLLOC = 0, 1, 2
+
+
+def make_problem(spec: SolveSpec, kind: int = KIND_TM) -> nat.OzProblem:
     pb = nat.OzProblem()
     m = spec.method
     s = m.num_stages
     if s > MAX_STAGES:
         raise ValueError(f'{s} stages exceed the device tableau storage ({MAX_STAGES})')
-    pb.rhs_id, pb.dtype = spec.rhs_id, (nat.OZ_F64 if spec.dtype == torch.float64 else nat.OZ_F32)
+    rhs_id = spec.rhs_id
+    if spec.traced is not None:         # compiled on first use for this (stages, implicit, dtype, approach)
+        rhs_id = spec.traced.plugin_id(s, not m.explicit if kind == KIND_TM else False, spec.dtype == torch.float64, kind)
+    pb.rhs_id, pb.dtype = rhs_id, (nat.OZ_F64 if spec.dtype == torch.float64 else nat.OZ_F32)
     pb.num_stages, pb.is_explicit = s, int(m.explicit)
     for i in range(s):
         for j in range(s):
@@ -345,7 +357,7 @@ class TmPlan:
 def picard_forward(spec: SolveSpec, y0, h, p=None, th=None, guess=None, tol=1e-10, max_sweeps=2000):
     """oz_picard_forward: all (step, stage) nodes relaxed at once; returns the same dict as tm_forward."""
     dev = y0.device
-    pb = make_problem(spec)
+    pb = make_problem(spec, KIND_PICARD)
     keep = _set_inputs(pb, spec, y0, h, p, th)
     d, N, nt = spec.d, spec.N, spec.nt
     guess = _chk(guess, spec, (spec.n, d, N), 'guess')
@@ -405,7 +417,7 @@ def picard(spec: SolveSpec, y0, h, p=None, th=None, guess=None, tol=1e-10, max_s
 # ------------------------------------------------------------------------------------------------
 def colloc_residual(spec: SolveSpec, y0, h, p, th, Y, y):
     dev = y0.device
-    pb = make_problem(spec)
+    pb = make_problem(spec, KIND_COLLOC)
     keep = _set_inputs(pb, spec, y0, h, p, th)
     n, s, d, N = spec.n, spec.method.num_stages, spec.d, spec.N
     Y = _chk(Y, spec, (n, s, d, N), 'stage design variables')
@@ -420,7 +432,7 @@ def colloc_residual(spec: SolveSpec, y0, h, p, th, Y, y):
 def colloc_vjp(spec: SolveSpec, y0, h, p, th, Y, y, mu1, mu2, need=('y0', 'h', 'p', 'th')):
     """oz_colloc_vjp: gradient of <mu1, c1> + <mu2, c2> w.r.t. (Y, y, y0, h, p, th)."""
     dev = y0.device
-    pb = make_problem(spec)
+    pb = make_problem(spec, KIND_COLLOC)
     keep = _set_inputs(pb, spec, y0, h, p, th)
     n, s, d, N = spec.n, spec.method.num_stages, spec.d, spec.N
     Y = _chk(Y, spec, (n, s, d, N), 'stage design variables')

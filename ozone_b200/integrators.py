@@ -68,13 +68,11 @@ class IntegratorBase(object):
     # ---- shared set-up -------------------------------------------------------------------
     def _prepare(self):
         f = self.ode_func
-        if not f.is_device:
-            self._probe_python_callback()
-            raise NotImplementedError(
-                'set_function received a Python callback.  It was called once and its keys/shapes are valid, but '
-                'Python code cannot run inside the CUDA kernels: pass one of the registered device right-hand sides '
-                '(ozone_b200.rhs.*).  Tracing arbitrary callbacks to device code is not built yet.')
-        rhs = f.f
+        if f.is_device:
+            rhs = f.f
+        else:
+            rhs = self._trace_python_callback()                          # KeyError / ValueError / TypeError like the reference
+        self.rhs = rhs
         static_values = rhs.bind_static(f.args, f.kwargs)               # TypeError like a wrong Python call
         self.packing = pk = Packing(rhs, self.states, self.dynamic_parameters, static_values, self.step_vector,
                                     self.num_times)
@@ -86,8 +84,10 @@ class IntegratorBase(object):
         self.p = pk.pack_params(self.dynamic_parameters)
         self.th = pk.pack_static()
         opts = self.options
+        traced = None if f.is_device else rhs
         self.spec = engine.SolveSpec(
-            rhs_name=rhs.kernel, method=self.method, N=pk.N, n=self.num_steps, dtype=pk.dtype,
+            rhs_name='traced' if traced is not None else rhs.kernel, traced=traced, method=self.method, N=pk.N,
+            n=self.num_steps, dtype=pk.dtype,
             h_shared=pk.h_shared, p_shared=pk.p_shared, th_shared=pk.th_shared,
             store_history=any(s.output for s in self.states.states.values()),
             newton_tol=opts.get('newton_tolerance', 1e-7), newton_max_iter=opts.get('newton_max_iter', 100),
@@ -95,23 +95,31 @@ class IntegratorBase(object):
             state_blocks=tuple(pk.state_offsets()))
         return rhs
 
-    def _probe_python_callback(self):
-        """One call shaped like the reference's first evaluate() -- num_nodes = 1 (explicit stage,
-        time_marching.py:176-180), s (implicit, :210-214) or n*s (Picard / Collocation,
-        picard_iteration.py:23-31) -- so malformed callbacks raise the same KeyError / ValueError /
-        TypeError (ozone/func_wrapper.py:28-53)."""
-        kind = self.approach.kind
-        if kind in ('picard', 'collocation'):
-            nn = self.num_steps * self.method.num_stages
-        else:
-            nn = 1 if self.method.explicit else self.method.num_stages
-        states = {n: s.initial_condition.reshape((1,) + s.shape).expand((nn,) + s.shape)
-                  for n, s in self.states.states.items()}
-        params = {n: d.parameter[:1].expand((nn,) + d.point_shape) for n, d in self.dynamic_parameters.d_params.items()}
-        self.ode_func.evaluate(states, params, nn)
+    def _trace_python_callback(self):
+        """Run the Python callback once on symbolic inputs (two nodes, so shapes are checked the way the
+        reference checks them with num_nodes > 1) and turn it into a device functor (trace.py).  Malformed
+        callbacks raise the reference's KeyError / ValueError / TypeError (ozone/func_wrapper.py:28-53)."""
+        from .trace import TracedRHS, _norm_shape
+        batched = bool(self.options.get('batched', False))
+        N = 1
+        state_shapes, param_shapes = {}, {}
+        for n, s in self.states.states.items():
+            shp = tuple(s.shape)
+            if batched:
+                if len(shp) == 0:
+                    raise ValueError(f'batched=True: state \'{n}\' needs a trailing trajectory axis')
+                N, shp = max(N, shp[-1]), shp[:-1]
+            state_shapes[n] = _norm_shape(shp)
+        for n, d in self.dynamic_parameters.d_params.items():
+            shp = tuple(d.point_shape)
+            if batched and N > 1 and len(shp) >= 1 and shp[-1] == N:
+                shp = shp[:-1]
+            param_shapes[n] = _norm_shape(shp)
+        f = self.ode_func
+        return TracedRHS(f.f, f.args, f.kwargs, state_shapes, param_shapes, batch_size=N)
 
     def _collect(self, out):
-        pk, rhs = self.packing, self.ode_func.f
+        pk, rhs = self.packing, self.rhs
         nt = self.num_times
         res = self.outputs
         if out.get('hist') is not None:

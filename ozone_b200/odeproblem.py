@@ -26,7 +26,8 @@ class ODEProblem(object):
     def __init__(self, method, approach, **options) -> None:
         """``ODEProblem(method, approach)`` as in the reference.  Optional keyword options of the
         device engine: ``newton_tolerance`` (default 1e-7, time_marching.py:220), ``newton_max_iter``,
-        ``verbose``."""
+        ``verbose``, ``batched`` (Python callbacks only: the trailing axis of every state is the
+        trajectory axis; registered ``rhs.*`` handles infer it from their declared shapes)."""
         check_if_method(method, 'method')
         self.method: GLMMethod = get_integration_method(method.name)
         if not isinstance(approach, _Approach):

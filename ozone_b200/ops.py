@@ -1,0 +1,57 @@
+"""Functions a right-hand side callback may apply to its variables (the csdl functions the reference's
+callbacks use: exp, sin, sum, expand, reshape, concatenate, ...).  They work on traced quantities
+(``trace.TVar``, while a Python callback is being compiled to a device functor) and on torch tensors."""
+import numpy as np
+import torch
+
+from .trace import TVar, _arr
+
+
+def _unary(name, tfn):
+    def fn(x):
+        if isinstance(x, TVar):
+            return x.map(name)
+        return tfn(torch.as_tensor(x))
+    fn.__name__ = name
+    return fn
+
+
+exp = _unary('exp', torch.exp)
+log = _unary('log', torch.log)
+sin = _unary('sin', torch.sin)
+cos = _unary('cos', torch.cos)
+tan = _unary('tan', torch.tan)
+tanh = _unary('tanh', torch.tanh)
+sqrt = _unary('sqrt', torch.sqrt)
+arctan = _unary('arctan', torch.atan)
+
+
+def sum(x, axes=None, axis=None):
+    ax = axes if axes is not None else axis
+    if isinstance(x, TVar):
+        return x.sum(axis=tuple(ax) if isinstance(ax, (list, tuple)) else ax)
+    return torch.sum(x) if ax is None else torch.sum(x, dim=ax)
+
+
+def expand(x, shape, action=None):
+    if isinstance(x, TVar):
+        return x.expand(shape, action)
+    if isinstance(x, torch.Tensor):
+        return TVar(_arr(x)).expand(shape, action)          # captured tensor used inside a trace
+    return TVar(np.asarray(x, dtype=object)).expand(shape, action)
+
+
+def reshape(x, shape):
+    return x.reshape(shape)
+
+
+def concatenate(xs, axis=0):
+    if any(isinstance(x, TVar) for x in xs):
+        return TVar(np.concatenate([_arr(x) for x in xs], axis=axis))
+    return torch.cat(list(xs), dim=axis)
+
+
+def norm(x):
+    if isinstance(x, TVar):
+        return (x * x).sum().map('sqrt')
+    return torch.linalg.norm(x)

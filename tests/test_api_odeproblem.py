@@ -108,19 +108,27 @@ def _problem_with(f, *args, **kwargs):
     return ode_problem
 
 
+def _expect_traced(problem):
+    """A well-formed Python callback is traced into a device functor; what happens next depends on the box:
+    with a GPU it solves, without one the solve is refused (no CPU fallback) -- never NotImplementedError."""
+    try:
+        problem.solve()
+    except RuntimeError as e:
+        assert not torch.cuda.is_available() and 'CUDA' in str(e)
+
+
 def test_ode_function_api_python_callbacks_are_validated_like_the_reference():
     a_static = torch.ones((1,), dtype=torch.float64)
 
     def rate(v):
-        return -v.states['x'] * v.dynamic_parameters['a_dynamic'].sum(dim=1).reshape(-1, 1, 1) * a_static
+        return -v.states['x'] * v.dynamic_parameters['a_dynamic'].sum(axis=1).reshape(-1, 1, 1) * a_static
 
-    # a well-formed callback passes validation; it cannot run on the device, which is said plainly  # :113-124
+    # a well-formed callback is accepted (traced to device code)                                   # :113-124
     def f(v: ozone.ODEVars):
         v.d_states['x'] = rate(v)
         v.field_outputs['x'] = v.states['x']
         v.profile_outputs['x'] = v.states['x']
-    with pytest.raises(NotImplementedError):
-        _problem_with(f).solve()
+    _expect_traced(_problem_with(f))
 
     def f(v):                                                        # :127-140 extra key
         v.d_states['x'] = rate(v)
@@ -140,8 +148,7 @@ def test_ode_function_api_python_callbacks_are_validated_like_the_reference():
 
     def f(v):                                                        # same size, different shape: reshaped (func_wrapper.py:32-34)
         v.d_states['x'] = rate(v).reshape(-1, 2)
-    with pytest.raises(NotImplementedError):
-        _problem_with(f).solve()
+    _expect_traced(_problem_with(f))
 
     def f(v):                                                        # :171-184 profile output shape wrong
         v.d_states['x'] = rate(v)
@@ -251,3 +258,45 @@ def test_methods_and_approaches_surface():
     assert ap.TimeMarchingCheckpoints().name == 'TimeMarching (Checkpointing)'
     assert ap.TimeMarchingCheckpoints(num_checkpoints=7).num_checkpoints == 7
     assert ap.PicardIteration().name == 'Picard Iteration' and ap.Collocation().name == 'Collocation'
+
+
+def test_python_callback_tracing_rules():
+    from ozone_b200 import trace, ops
+    sp = torch.linspace(0.1, 1.1, 3, dtype=torch.float64)
+
+    def f(v):                                   # test_3_large/utils.py:23-30 written for one trajectory
+        y, dp = v.states['y'], v.dynamic_parameters['dynamic_param']
+        v.d_states['y'] = -(y * (dp + sp[0])) ** 2
+    t = trace.TracedRHS(f, (), {}, {'y': ()}, {'dynamic_param': ()})
+    assert (t.D, t.P, t.S, t.DQ) == (1, 1, 1, 0) and 'struct RhsTraced' in t.cuda_source()
+
+    def vdp(v):                                 # van_der_pol/main_model.py:6-14: J is a pure quadrature
+        x0, x1, u = v.states['x0'], v.states['x1'], v.dynamic_parameters['u']
+        v.d_states['x0'] = ((1.0 + (-1.0) * (x1 ** 2.0)) * x0 + (-1 * x1) + u).reshape(-1, 1)
+        v.d_states['x1'] = (x0 * 1.0).reshape(-1, 1)
+        v.d_states['J'] = (x0 ** 2.0 + x1 ** 2.0 + u ** 2.0).reshape(-1, 1)
+    t = trace.TracedRHS(vdp, (), {}, {'x0': (), 'x1': (), 'J': ()}, {'u': ()})
+    assert (t.D, t.P, t.S, t.DQ) == (3, 1, 0, 1)
+
+    def couples_rows(v):                        # not node-wise: every row reads row 0
+        v.d_states['y'] = v.states['y'][0:1].expand(v.states['y'].shape)
+    with pytest.raises(ValueError):
+        trace.TracedRHS(couples_rows, (), {}, {'y': ()}, {})
+
+    def branches(v):                            # data-dependent Python control flow cannot be compiled
+        y = v.states['y']
+        v.d_states['y'] = y if y[0, 0] > 0 else -y
+    with pytest.raises(TypeError):
+        trace.TracedRHS(branches, (), {}, {'y': ()}, {})
+
+    def big(v):
+        v.d_states['y'] = -v.states['y']
+    with pytest.raises(ValueError):             # 500 components per trajectory do not fit one thread: batch them
+        trace.TracedRHS(big, (), {}, {'y': (500,)}, {})
+
+    def uses_ops(v):
+        y = v.states['y']
+        v.d_states['y'] = ops.exp(-y) * ops.sin(y) + np.cos(y) / ops.sqrt(1.0 + y * y) - abs(y) ** 1.5
+    t = trace.TracedRHS(uses_ops, (), {}, {'y': (2,)}, {})
+    src = t.cuda_source()
+    assert 'exp(' in src and 'sin(' in src and 'cos(' in src and 'sqrt(' in src and 'pow(' in src

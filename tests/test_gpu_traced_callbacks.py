@@ -1,0 +1,211 @@
+"""Python right-hand side callbacks, traced and compiled to device functors (ozone_b200/trace.py), on the
+reference's own problems: the callbacks below are the reference's (csdl ops spelled with ozone_b200.ops /
+array methods) and the answers are the reference's goldens."""
+import numpy as np
+import pytest
+import torch
+
+import ozone_b200 as ozone
+from ozone_b200 import ops
+from ozone_b200.approaches import TimeMarching, TimeMarchingCheckpoints, PicardIteration, Collocation
+from ozone_b200.methods import RK4, Trapezoidal, GaussLegendre6
+
+pytestmark = pytest.mark.gpu
+
+
+def var(value, requires_grad=True):
+    return torch.tensor(np.asarray(value, dtype=np.float64), device='cuda', requires_grad=requires_grad)
+
+
+def norms(out, inputs):
+    g = torch.autograd.grad(out.sum(), list(inputs.values()), retain_graph=True, allow_unused=True)
+    return {k: (0.0 if gi is None else float(torch.linalg.norm(gi))) for k, gi in zip(inputs, g)}
+
+
+@pytest.mark.parametrize('approach', [TimeMarching(), PicardIteration()], ids=['TimeMarching', 'Picard'])
+@pytest.mark.parametrize('method', [RK4(), Trapezoidal()], ids=['RK4', 'Trapezoidal'])
+def test_1_simple_python_callback(method, approach):
+    def f(ozone_vars: ozone.ODEVars):                       # test_1_simple/utils.py:6-7, verbatim
+        ozone_vars.d_states['y'] = -ozone_vars.states['y']
+
+    y_0, h_vec = var([0.5]), var(np.ones(29) * 0.01)
+    p = ozone.ODEProblem(method, approach, newton_tolerance=1e-12)
+    p.add_state('y', initial_condition=y_0, store_history=True)
+    p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h_vec))
+    p.set_function(f)
+    y_out = p.solve().states['y'].sum()
+    assert float(y_out) == pytest.approx(13.0239779, rel=1e-5)
+    d = norms(y_out, {'y_0': y_0, 'h': h_vec})
+    assert d['y_0'] == pytest.approx(26.047954954623957, rel=1e-4)
+    assert d['h'] == pytest.approx(38.575000915365756, rel=1e-4)
+
+
+def general_f(ozone_vars: ozone.ODEVars, d_arg):
+    """test_2_general/utils.py:43-84 with csdl.expand / csdl.reshape spelled ops.expand / ops.reshape."""
+    a = ozone_vars.dynamic_parameters['a']
+    b = ozone_vars.dynamic_parameters['b']
+    g = ozone_vars.dynamic_parameters['g']
+    e = ozone_vars.dynamic_parameters['e']
+    x, y, z = ozone_vars.states['x'], ozone_vars.states['y'], ozone_vars.states['z']
+    n = ozone_vars.num_nodes
+    z_adjust1 = ops.expand(ops.reshape(z[:, 0, 1], (n,)), (n, 2, 2), 'i->ijk')
+    dy_dt = a * y - b * y * x
+    dx_dt = g * x * y - d_arg * x
+    dz_dt = z * 0.0
+    for i in range(n):
+        temp_y = y[i] ** 2
+        val = -z[i, :, :] / 3.0 * z_adjust1[i, :, :] + temp_y / 2.0 + a[i] * e[i, :, :] + x[i] / 2.0
+        dz_dt = dz_dt.set((i, slice(None), slice(None)), val)
+    ozone_vars.d_states['y'] = dy_dt
+    ozone_vars.d_states['x'] = dx_dt
+    ozone_vars.d_states['z'] = dz_dt
+    z_adjust2 = ops.expand(ops.reshape(z[:, 1, 0], (n,)), (n, 2, 2), 'i->ijk')
+    ozone_vars.profile_outputs['z'] = ops.reshape(z[:, 1, 1], (n,))
+    ozone_vars.profile_outputs['x'] = x + (y / 4.0) * y
+    ozone_vars.profile_outputs['y'] = z * z_adjust1 * z_adjust2 + e ** 2 + ops.expand(a.flatten(), (n, 2, 2), 'i->ijk') \
+        + ops.expand(d_arg, (n, 2, 2))
+    coeffs = ozone_vars.dynamic_parameters['coefficients']
+    ozone_vars.field_outputs['y'] = coeffs * y
+    ozone_vars.field_outputs['z'] = coeffs[:, 0].expand(z.shape, action='i->ijk') * z
+
+
+@pytest.mark.parametrize('approach', [TimeMarching(), TimeMarchingCheckpoints(num_checkpoints=5)], ids=['TM', 'Checkpoints5'])
+def test_2_general_python_callback(approach):
+    nt = 31
+    t = np.arange(nt)
+    y_0, x_0, z_0 = var([2.0]), var([2.0]), var([[2.0, 1.0], [-1.0, -3.0]])
+    ai, bi, gi = var(1.0 + t / nt / 5.0), var(0.5 + t / nt / 5.0), var(2.0 + t / nt / 5.0)
+    ei = var(np.array([[0.3, 0.2], [0.1, -2.6]])[None] + (t / nt / 5.0)[:, None, None])
+    di, coeffs, h_vec = var([0.5]), var(np.ones(nt) / nt), var(np.ones(nt - 1) * 0.001)
+    p = ozone.ODEProblem(RK4(), approach, verbose=False)
+    p.add_state('y', initial_condition=y_0)
+    p.add_state('x', initial_condition=x_0)
+    p.add_state('z', initial_condition=z_0, store_history=True)
+    for name, v in (('a', ai), ('b', bi), ('g', gi), ('e', ei), ('coefficients', coeffs)):
+        p.add_dynamic_parameter(name, v)
+    p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h_vec))
+    p.set_function(general_f, di)
+    out = p.solve()
+    pox, poz, poy = out.profile_outputs['x'], out.profile_outputs['z'], out.profile_outputs['y']
+    total = pox[-1] + poz[-1] + out.field_outputs['y'][0] + out.states['z'][-1, 0, 1].reshape(1) / 2.0
+    total2 = torch.linalg.norm(poy[-1] + poy[0])
+    assert float(total) == pytest.approx(2.80611596, rel=2e-9)                       # utils.py:161-162 (RK4 goldens)
+    assert float(total2) == pytest.approx(22.27526371713729, rel=1e-13)
+    inputs = {'a': ai, 'x_0': x_0, 'h': h_vec, 'z_0': z_0, 'e': ei}
+    d1, d2 = norms(total, inputs), norms(total2, inputs)
+    assert d1['a'] == pytest.approx(0.00574943937426972, rel=1e-9)                   # :127-156
+    assert d1['x_0'] == pytest.approx(1.08155650643438, rel=1e-9)
+    assert d1['h'] == pytest.approx(57.652844215047104, rel=1e-9)
+    assert d2['a'] == pytest.approx(1.754553251836068, rel=1e-9)
+    assert d2['x_0'] == pytest.approx(0.027324051014, rel=1e-9)
+    assert d2['h'] == pytest.approx(33.7649223785, rel=1e-9)
+    assert d2['z_0'] == pytest.approx(9.09442575264, rel=1e-9)
+    assert d2['e'] == pytest.approx(6.880652370272789, rel=1e-9)
+
+
+def test_3_large_python_callback_with_captured_static_parameter():
+    # test_3_large/utils.py:6-74: 500 independent ODEs = a batch; `sp` is captured by the closure and differentiated
+    nt, size = 30, 500
+    y_0 = var(0.5 * np.ones(size))
+    sp = var(np.linspace(0.1, 1.1, size))
+    dp = var(np.linspace(0.5, 0.8, nt).reshape(nt, 1))
+    h_vec = var(np.ones(nt - 1) * 0.01)
+
+    def f(ozone_vars: ozone.ODEVars):
+        y = ozone_vars.states['y']
+        dpv = ozone_vars.dynamic_parameters['dynamic_param']
+        ozone_vars.d_states['y'] = -(y * (dpv + sp)) ** 2
+
+    p = ozone.ODEProblem(RK4(), TimeMarching(), batched=True)
+    p.add_state('y', initial_condition=y_0, store_history=True)
+    p.add_dynamic_parameter('dynamic_param', dp)
+    p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h_vec))
+    p.set_function(f)
+    y_out = p.solve().states['y'].sum()
+    assert float(y_out) == pytest.approx(6794.12754072, rel=1e-11)                   # utils.py:73-74, exact RK4 values
+    d = norms(y_out, {'y_0': y_0, 'h': h_vec, 'static_param': sp, 'dynamic_param': dp})
+    assert d['y_0'] == pytest.approx(555.6297961976778, rel=1e-12)
+    assert d['h'] == pytest.approx(12570.03729508261, rel=1e-12)
+    assert d['static_param'] == pytest.approx(43.805547522344185, rel=1e-12)
+    assert d['dynamic_param'] == pytest.approx(203.55862089571335, rel=1e-12)
+
+
+def test_van_der_pol_python_callback_equals_the_registered_functor():
+    # van_der_pol/main_model.py:6-14 verbatim; implicit GL6 -> Newton in registers, J detected as a quadrature state
+    def ode_func(ozone_vars: ozone.ODEVars):
+        x0, x1 = ozone_vars.states['x0'], ozone_vars.states['x1']
+        u = ozone_vars.dynamic_parameters['u']
+        ozone_vars.d_states['x0'] = ((1.0 + (- 1.0) * (x1**2.0))*x0 + (-1*x1) + u).reshape(-1, 1)
+        ozone_vars.d_states['x1'] = (x0*1.0).reshape(-1, 1)
+        ozone_vars.d_states['J'] = (x0**2.0 + x1**2.0 + u**2.0).reshape(-1, 1)
+
+    nt, N = 40, 256
+    rng = np.random.default_rng(4)
+    uval = rng.uniform(-0.75, 1.0, size=(nt, N))
+    res = []
+    for func, opts in ((ode_func, dict(batched=True)), (ozone.rhs.van_der_pol, {})):
+        u, h = var(uval), var(np.ones(nt - 1) * (15.0 / (nt - 1)))
+        p = ozone.ODEProblem(GaussLegendre6(), TimeMarching(), newton_tolerance=1e-12, **opts)
+        p.add_state('x0', var(np.ones(N), False), store_history=True)
+        p.add_state('x1', var(np.ones(N), False))
+        p.add_state('J', var(np.zeros(N), False), store_final=True)
+        p.set_timespan(ozone.timespan.StepVector(start=0.0, step_vector=h))
+        p.add_dynamic_parameter('u', u)
+        p.set_function(func)
+        out = p.solve()
+        J = out.final_states['J']
+        g = torch.autograd.grad(J.sum(), [u, h])
+        res.append((J.detach(), out.states['x0'].detach(), g[0], g[1], out.iterations))
+    if isinstance(ozone.rhs.van_der_pol, object):
+        assert p.integrator.spec.traced is None
+    for a, b in zip(res[0][:4], res[1][:4]):
+        assert float((a - b).abs().max() / b.abs().max()) < 1e-12
+    assert torch.equal(res[0][4], res[1][4])                                         # same Newton iteration counts
+
+
+def test_lotka_volterra_example_python_callback_and_collocation_constraints():
+    # examples/simple_examples/lotka_volterra.py:51-62 verbatim
+    def ode_function(ozone_vars: ozone.ODEVars, c):
+        a = ozone_vars.dynamic_parameters['a']
+        x = ozone_vars.states['x']
+        y = ozone_vars.states['y']
+        ozone_vars.d_states['y'] = a*y - 0.5*y*x
+        ozone_vars.d_states['x'] = 2.0*x*y - c*x
+        ozone_vars.field_outputs['field_x'] = x
+        ozone_vars.profile_outputs['x_plus_y'] = x + y
+
+    num_times = 10
+    outs = {}
+    for name, func in (('py', ode_function), ('dev', ozone.rhs.lotka_volterra)):
+        x_0, y_0, c = var([2.0]), var([2.0]), var([0.5])
+        a = var(1.0 + np.arange(num_times) / num_times / 5.0)
+        h = var(np.full(num_times - 1, 0.1))
+        p = ozone.ODEProblem(RK4(), TimeMarching())
+        p.add_state('y', y_0)
+        p.add_state('x', x_0)
+        p.add_dynamic_parameter('a', a)
+        p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+        p.set_function(func, c)
+        o = p.solve()
+        m = o.profile_outputs['x_plus_y'].max() + o.field_outputs['field_x'].sum()
+        outs[name] = (o.profile_outputs['x_plus_y'].detach(), torch.autograd.grad(m, [a, c, h, x_0]))
+    assert torch.allclose(outs['py'][0], outs['dev'][0], rtol=1e-13, atol=0)
+    for g1, g2 in zip(outs['py'][1], outs['dev'][1]):
+        assert torch.allclose(g1, g2, rtol=1e-11, atol=1e-14)
+
+    # the same callback under Collocation: constraints vanish at the time-marching solution of a traced RHS too
+    x_0, y_0, c = var([2.0]), var([2.0]), var([0.5])
+    a = var(1.0 + np.arange(num_times) / num_times / 5.0)
+    h = var(np.full(num_times - 1, 0.1))
+    p = ozone.ODEProblem(RK4(), Collocation())
+    p.add_state('y', y_0, store_history=True)
+    p.add_state('x', x_0, store_history=True)
+    p.add_dynamic_parameter('a', a)
+    p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    p.set_function(ode_function, c)
+    o = p.solve()
+    integ = p.integrator
+    assert set(integ.constraints) == {'y_stage_c', 'y_state_c', 'x_stage_c', 'x_state_c'}   # collocation.py:53-54
+    assert tuple(o.states['x'].shape) == (num_times, 1)
+    gY, = torch.autograd.grad((integ.c1 ** 2).sum() + (integ.c2 ** 2).sum(), [integ.stage_dv])
+    assert torch.isfinite(gY).all() and float(gY.abs().max()) > 0
