@@ -37,7 +37,9 @@ WORKLOADS = {
     'lotka_volterra_rk4_tm_adjoint_N1M_nt101_fp32': dict(kind='tm', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, fp32=True),
     'lotka_volterra_rk4_picard_adjoint_N1M_nt101': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9),
     'lotka_volterra_rk4_picard_adjoint_N1M_nt101_fp32': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, fp32=True),
+    'lotka_volterra_rk4_picard_jacobi_adjoint_N1M_nt101': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, jacobi=True),
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32),
+    'diffusion_reaction_rk4_checkpoints_nx1M_n1024_fp32': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, fp32=True),
     'lunar_ascent_rk4_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='RK4', N=16384, nt=101, T=0.1),
     'lunar_ascent_gl6_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='GaussLegendre6', N=16384, nt=101, T=0.1),
 }
@@ -231,7 +233,7 @@ class Runner:
             extra = dict(d_override=nx, rhs_cfg=(np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx))),
                          num_inner=self.n // wl['nc'], store_history=False)
         if self.kind == 'picard':
-            extra = dict(state_blocks=(0, 1, 2))
+            extra = dict(state_blocks=(0, 2) if wl.get('jacobi') else (0, 1, 2))
         self.spec = spec = engine.SolveSpec(
             rhs_name=wl['rhs'], method=get_integration_method(wl['method']), N=N, n=self.n, dtype=self.dtype,
             h_shared=True, p_shared=self.p_shared, th_shared=False, newton_tol=args.newton_tol,
@@ -260,6 +262,18 @@ class Runner:
         self.h2d = sum(self.host[k].numel() * self.w for k in self.e2e_inputs)
         self.d2h = sum(v.numel() * self.w for v in self.host_out.values()) + self.host_obj.numel() * self.w
         self.launches = plan.launches_forward + plan.launches_adjoint
+        self.pipe = None
+        if self.kind == 'tm':      # e2e leg: host-resident batch in sub-batches on their own streams (copy / compute overlap)
+            self.pipe = engine.PipelinedTmSolve(spec, slices=args.e2e_slices, device=dev, grads=want, cotangents=cot,
+                                                upload=self.e2e_inputs)
+            self.pipe.set_host_inputs(**self.host)
+            if args.world > 1:
+                import torch.distributed as dist
+                self.pipe.reduce_shared = dist.all_reduce
+            for pl in self.pipe.plans:
+                pl.final_bar.copy_(plan.final_bar[:, :pl.spec.N])
+            self.h2d, self.d2h = self.pipe.bytes_per_run()
+            self.e2e_launches = self.pipe.launches
         if self.kind == 'picard':
             self.launches = 1 + plan.launches_adjoint
         if self.kind == 'colloc':
@@ -302,6 +316,9 @@ class Runner:
         return self.plan.grad['h']
 
     def e2e(self):
+        if self.pipe is not None:
+            self.pipe.run()
+            return
         pl = self.plan
         for k in self.e2e_inputs:
             getattr(pl, k).copy_(self.host[k], non_blocking=True)
@@ -309,6 +326,8 @@ class Runner:
         self.adjoint()
 
     def e2e_readback(self):
+        if self.pipe is not None:
+            return                  # downloads are part of every slice's stream
         if self.kind in ('picard', 'colloc'):
             src = self.pic['final'][-1] if self.kind == 'picard' else self.c[1][-1, 0]
             self.host_obj.copy_(src, non_blocking=True)
@@ -351,11 +370,13 @@ def main():
                     help='CPU sample size per core (defaults: CPU_SAMPLE / CPU_SAMPLE_REF tables)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--newton-tol', type=float, default=1e-7)
+    ap.add_argument('--e2e-slices', type=int, default=6, help='sub-batches (streams) of the end-to-end leg')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
 
     rank = int(os.environ.get('RANK', '0'))
     world = int(os.environ.get('WORLD_SIZE', '1'))
+    args.world = world
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
     if args.impl == 'reference':
         run_reference(args, rank, world)
@@ -381,9 +402,13 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def allreduce_shared():
+    def allreduce_shared(e2e=False):
+        if world == 1:
+            return
+        if e2e and run.pipe is not None:      # PipelinedTmSolve all-reduces its summed shared gradients itself
+            return
         g = run.shared_grad()
-        if world > 1 and g is not None:
+        if g is not None:
             dist.all_reduce(g)
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
@@ -399,7 +424,7 @@ def main():
         e0, e1 = ev(), ev()
         e0.record()
         run.e2e()
-        allreduce_shared()
+        allreduce_shared(e2e=True)
         run.e2e_readback()
         e1.record()
         times.append((e0, e1))
@@ -502,7 +527,9 @@ def main():
                             'parallelism': f'trajectory-batch x{world}' if run.kind != 'grid' else 'replicas only (bench); '
                             'spatial shard: see ozone_b200/parallel.py'}, **extra_cfg),
             'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
-                    'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps},
+                    'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps,
+                    'how': (f'engine.PipelinedTmSolve: {args.e2e_slices} sub-batches on their own streams, pinned host buffers'
+                            if run.pipe is not None else 'engine plan API, pinned host buffers, one stream')},
             'gpu_launches': args.steps * run.launches,
             'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
             'wall_ms_timed_loop': t_wall * 1e3,

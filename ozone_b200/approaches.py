@@ -29,11 +29,16 @@ class PicardIteration(_Approach):
     name = 'Picard Iteration'
     kind = 'picard'
 
-    def __init__(self, tolerance: Optional[float] = None, max_iter: int = 2000) -> None:
+    def __init__(self, tolerance: Optional[float] = None, max_iter: int = 2000, relaxation: str = 'gauss_seidel') -> None:
         # max_iter: ozone/integrators/picard_iteration.py:35.  The tolerance is a csdl default the
         # reference does not set; here it defaults to 1e-10 (fp64) / 1e-4 (fp32).
+        # relaxation: 'gauss_seidel' relaxes the states one after another, re-evaluating f for each (what csdl's
+        # GaussSeidel solver does, :35); 'jacobi' relaxes all states from one evaluation of f -- same fixed point,
+        # one RHS pass per sweep instead of one per state.
         super().__init__()
-        self.tolerance, self.max_iter = tolerance, max_iter
+        if relaxation not in ('gauss_seidel', 'jacobi'):
+            raise ValueError("relaxation must be 'gauss_seidel' or 'jacobi'")
+        self.tolerance, self.max_iter, self.relaxation = tolerance, max_iter, relaxation
 
 
 class Collocation(_Approach):

@@ -501,3 +501,89 @@ def outputs_on_history(spec: SolveSpec, hist, p, th):
     prof = prof.reshape(info['nprof'], nt, N).permute(1, 0, 2).contiguous() if prof is not None else None
     fld = fld.reshape(info['nfield'], nt, N).sum(dim=1) if fld is not None else None
     return prof, fld
+
+
+class PipelinedTmSolve:
+    """Solve + reverse sweep of a HOST-resident trajectory batch, cut into `slices` sub-batches that each run
+    on their own stream: while one slice integrates, the next one's inputs cross PCIe and the previous one's
+    gradients flow back (copies in both directions overlap each other and the kernels).  Trajectories are
+    independent, so slicing changes nothing but the order of the sums of batch-shared gradients, which are
+    added up over the slices at the end (fixed order)."""
+
+    def __init__(self, spec: SolveSpec, slices=4, device='cuda', grads=('h', 'p'), cotangents=('final',),
+                 upload=('h', 'p')):
+        from .parallel import shard_bounds
+        self.spec, self.upload = spec, tuple(upload)
+        dev = torch.device(device)
+        slices = max(1, min(slices, spec.N))
+        self.bounds = [shard_bounds(spec.N, i, slices) for i in range(slices)]
+        self.plans = [TmPlan(replace(spec, N=hi - lo), device=dev, grads=grads, cotangents=cotangents)
+                      for lo, hi in self.bounds]
+        self.streams = [torch.cuda.Stream(device=dev) for _ in self.plans]
+        self.shared = dict(y0=False, h=spec.h_shared, p=spec.p_shared, th=spec.th_shared)
+        pin = lambda t: torch.empty(t.shape, dtype=t.dtype).pin_memory()
+        self.host_in = [{k: pin(getattr(pl, k)) for k in ('y0', 'h', 'p', 'th') if getattr(pl, k) is not None}
+                        for pl in self.plans]
+        self.host_grad = [{k: pin(g) for k, g in pl.grad.items() if g is not None} for pl in self.plans]
+        self.host_final = [pin(pl.final) for pl in self.plans]
+        self._start, self._done = torch.cuda.Event(), [torch.cuda.Event() for _ in self.plans]
+        self.host_shared = {k: pin(g) for k, g in self.plans[0].grad.items() if g is not None and self.shared[k]}
+        self.reduce_shared = None      # e.g. torch.distributed.all_reduce under torchrun
+
+    def set_host_inputs(self, **arrays):
+        """arrays in the packed layout of the whole batch (torch CPU tensors); per-trajectory ones are split
+        into contiguous per-slice pinned buffers once, inputs that are not re-uploaded go to the device now."""
+        for (lo, hi), pl, hin in zip(self.bounds, self.plans, self.host_in):
+            for k, a in arrays.items():
+                if k not in hin:
+                    continue
+                hin[k].copy_(a if self.shared[k] else a[..., lo:hi])
+                if k not in self.upload:
+                    getattr(pl, k).copy_(hin[k])
+
+    def run(self):
+        """Enqueue upload -> forward -> reverse -> download for every slice; returns immediately."""
+        cur = torch.cuda.current_stream()
+        self._start.record(cur)
+        for pl, st, hin, hg, hf, done in zip(self.plans, self.streams, self.host_in, self.host_grad, self.host_final,
+                                             self._done):
+            st.wait_event(self._start)
+            with torch.cuda.stream(st):
+                for k in self.upload:
+                    if k in hin:
+                        getattr(pl, k).copy_(hin[k], non_blocking=True)
+                pl.forward()
+                pl.adjoint()
+                hf.copy_(pl.final, non_blocking=True)
+                for k, v in hg.items():
+                    if not self.shared[k]:
+                        v.copy_(pl.grad[k], non_blocking=True)
+                done.record(st)
+        for done in self._done:
+            cur.wait_event(done)
+        # gradients of batch-shared inputs: sum over the slices (fixed order), optional all-reduce over ranks, download
+        for k in self.host_grad[0]:
+            if self.shared[k]:
+                total = torch.stack([pl.grad[k] for pl in self.plans]).sum(0)
+                if self.reduce_shared is not None:
+                    self.reduce_shared(total)
+                self.host_shared[k].copy_(total, non_blocking=True)
+
+    def bytes_per_run(self):
+        w = 8 if self.spec.dtype == torch.float64 else 4
+        h2d = sum(hin[k].numel() * w for hin in self.host_in for k in self.upload if k in hin)
+        d2h = sum(v.numel() * w for hg in self.host_grad for k, v in hg.items() if not self.shared[k]) \
+            + sum(v.numel() * w for v in self.host_shared.values()) + sum(f.numel() * w for f in self.host_final)
+        return h2d, d2h
+
+    def gather(self):
+        """After a synchronisation: (final (d, N), grads) assembled on the host; shared gradients summed over slices."""
+        final = torch.cat(self.host_final, dim=-1)
+        grads = {}
+        for k in self.host_grad[0]:
+            grads[k] = self.host_shared[k] if self.shared[k] else torch.cat([hg[k] for hg in self.host_grad], dim=-1)
+        return final, grads
+
+    @property
+    def launches(self):
+        return sum(pl.launches_forward + pl.launches_adjoint for pl in self.plans)

@@ -185,6 +185,9 @@ class PicardIteration(IntegratorBase):
         if tol is None:
             tol = 1e-10 if self.spec.dtype == torch.float64 else 1e-4   # fp32 round-off floor of the residual 2-norm is ~1e-5
         guess = self.packing.pack_guess(self.states)
+        if self.approach.relaxation == 'jacobi':
+            from dataclasses import replace
+            self.spec = replace(self.spec, state_blocks=(0, self.spec.d))
         self._collect(engine.picard(self.spec, self.y0, self.h, self.p, self.th, guess=guess, tol=tol,
                                     max_sweeps=self.approach.max_iter))
 

@@ -235,3 +235,10 @@ def test_van_der_pol_paper_model_gauss_legendre_batch():
     g = Adj.tm_adjoint(rhs, 'GaussLegendre6', y0, hh, p, None, history=ref['history'], final_bar=fb, tol=1e-12)
     assert np.abs(g_u.cpu().numpy() - g['p'][:, 0]).max() / np.abs(g['p']).max() < 1e-10
     assert np.abs(g_h.cpu().numpy() - g['h']).max() / np.abs(g['h']).max() < 1e-10
+
+
+def test_picard_jacobi_relaxation_reaches_the_same_fixed_point():
+    inputs, outputs = build_test2(RK4(), PicardIteration(relaxation='jacobi'))
+    assert float(outputs['total2']) == pytest.approx(22.27526371713729, rel=1e-10)
+    with pytest.raises(ValueError):
+        PicardIteration(relaxation='sor')

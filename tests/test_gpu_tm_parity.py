@@ -175,3 +175,27 @@ def test_config3_spatial_slabs_match_the_single_slab_solve():
     assert relerr(np_(res['y0_bar']), np_(g['y0'][:, 0])) < 1e-12
     assert relerr(np_(res['h_bar']), np_(g['h'])) < 1e-12
     assert relerr(np_(res['u_bar']), np_(g['p'])) < 1e-12
+
+
+def test_pipelined_host_batch_equals_the_single_launch_solve():
+    # engine.PipelinedTmSolve: sub-batches on their own streams with pinned host buffers (the bench's e2e leg)
+    from ozone_b200 import engine
+    from tests.gpu_util import make_spec, dev_inputs
+    c = cases.van_der_pol_inputs(N=1000, nt=21)
+    spec = make_spec(c, 'GaussLegendre4', tol=1e-12)
+    y0, h, p, th = dev_inputs(c, spec)
+    plan = engine.TmPlan(spec, grads=('h', 'p'), cotangents=('final',))
+    plan.y0.copy_(y0); plan.h.copy_(h); plan.p.copy_(p)
+    plan.final_bar.zero_(); plan.final_bar[-1].fill_(1.0)
+    plan.forward(); plan.adjoint()
+    pipe = engine.PipelinedTmSolve(spec, slices=3, grads=('h', 'p'), cotangents=('final',), upload=('h', 'p'))
+    pipe.set_host_inputs(y0=y0.cpu(), h=h.cpu(), p=p.cpu())
+    for pl in pipe.plans:
+        pl.final_bar.zero_(); pl.final_bar[-1].fill_(1.0)
+    for _ in range(2):
+        pipe.run()
+        torch.cuda.synchronize()
+        final, grads = pipe.gather()
+        assert torch.equal(final, plan.final.cpu())
+        assert torch.equal(grads['p'], plan.grad['p'].cpu())
+        assert relerr(np_(grads['h']), np_(plan.grad['h'])) < 1e-13      # same terms, different summation order
