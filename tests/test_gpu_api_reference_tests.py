@@ -242,3 +242,30 @@ def test_picard_jacobi_relaxation_reaches_the_same_fixed_point():
     assert float(outputs['total2']) == pytest.approx(22.27526371713729, rel=1e-10)
     with pytest.raises(ValueError):
         PicardIteration(relaxation='sor')
+
+
+def test_picard_with_user_initial_guess_like_the_van_der_pol_model():
+    # van_der_pol/main_model.py:37-39 passes initial_guess=np.linspace(...).reshape(-1, 1) per state (collections.py:125-128)
+    nt, tf = 12, 1.5
+    u = var(np.full(nt, -0.75))
+    h = var(np.ones(nt - 1) * (tf / (nt - 1)))
+    sols = []
+    for guess in (True, False):
+        kw = (lambda a, b: dict(initial_guess=np.linspace(a, b, nt - 1).reshape(-1, 1))) if guess else (lambda a, b: {})
+        p = ozone.ODEProblem(RK4(), PicardIteration(tolerance=1e-13))
+        p.add_state('x0', var([1.0], False), store_history=True, **kw(1.0, 0.0))
+        p.add_state('x1', var([1.0], False), store_history=True, **kw(1.0, 0.0))
+        p.add_state('J', var([0.0], False), store_final=True, **kw(0.0, 1.0))
+        p.set_timespan(ozone.timespan.StepVector(start=0.0, step_vector=h))
+        p.add_dynamic_parameter('u', u)
+        p.set_function(ozone.rhs.van_der_pol)
+        out = p.solve()
+        assert int(out.status.max()) == 0
+        sols.append((out.states['x0'].detach(), out.final_states['J'].detach(), int(out.iterations.max())))
+    assert torch.allclose(sols[0][0], sols[1][0], rtol=1e-11, atol=0) and torch.allclose(sols[0][1], sols[1][1], rtol=1e-11)
+    with pytest.raises(ValueError):                                     # collections.py:92-95: wrong guess shape
+        p = ozone.ODEProblem(RK4(), PicardIteration())
+        p.add_state('x0', var([1.0], False), initial_guess=np.ones((3, 1)))
+        p.set_timespan(ozone.timespan.StepVector(start=0.0, step_vector=h))
+        p.set_function(ozone.rhs.affine, -1.0)
+        p.solve()
