@@ -68,9 +68,11 @@ OZ_D void load_params(const TmArgs<T>& a, int k, long long i, T* p) {
 template <class R, typename T, int S>
 OZ_D void stage_params(const Tableau<T>& tab, const T* plo, const T* phi, T (*ps)[Dims<R>::P1]) {
 #pragma unroll
-    for (int s = 0; s < S; ++s)
+    for (int c = 0; c < R::P; ++c) {
+        const T dp = phi[c] - plo[c];         // p[k](1 - c_s) + p[k+1] c_s = p[k] + c_s (p[k+1] - p[k]): one FMA per stage
 #pragma unroll
-        for (int c = 0; c < R::P; ++c) ps[s][c] = plo[c] * (T(1) - tab.C[s]) + phi[c] * tab.C[s];
+        for (int s = 0; s < S; ++s) ps[s][c] = plo[c] + tab.C[s] * dp;
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -498,6 +500,7 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
 #pragma unroll
                 for (int j = i + 1; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
             }
+            hb += acc * F[i][c];  // h_bar = sum_i (G_i / h) . F_i without dividing by h (h = 0 is legal)
             G[c] = h * acc;
         }
         if constexpr (IMPL) {
@@ -512,29 +515,14 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
         }
 #pragma unroll
         for (int c = 0; c < DM::P; ++c) {
-            pb_lo[c] += (T(1) - tab.C[i]) * pbi[c];
+            pb_lo[c] += pbi[c];               // running total; the (1 - c_i) part is total - c_i part, taken below
             pb_hi[c] += tab.C[i] * pbi[c];
         }
     }
-    // h_bar = sum_i b_i F_i . lam + sum_i Ybar_i . sum_j a_ij F_j   (no division by h: h = 0 is legal)
 #pragma unroll
-    for (int c = 0; c < D; ++c) {
-        T accb = T(0);
-#pragma unroll
-        for (int i = 0; i < S; ++i) {
-            accb += tab.B[i] * F[i][c];
-            T af = T(0);
-            if constexpr (IMPL) {
-#pragma unroll
-                for (int j = 0; j < S; ++j) af += tab.a(i, j) * F[j][c];
-            } else {
-#pragma unroll
-                for (int j = 0; j < i; ++j) af += tab.a(i, j) * F[j][c];
-            }
-            hb += Yb[i][c] * af;
-        }
-        hb += accb * lam[c];
-    }
+    for (int c = 0; c < DM::P; ++c) pb_lo[c] -= pb_hi[c];
+    // (h_bar: sum_i G_i . F_i = h [sum_i b_i F_i . lam + sum_j Ybar_j . sum_i a_ji F_i], accumulated above as
+    //  sum_i (G_i / h) . F_i from the not-yet-scaled cotangent)
 #pragma unroll
     for (int c = 0; c < D; ++c) {
         T acc = T(0);
