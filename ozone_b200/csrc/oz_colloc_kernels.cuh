@@ -35,8 +35,11 @@ OZ_D void col_load_p(const ColArgs<T>& a, int k, long long i, T* p) {
     for (int c = 0; c < R::P; ++c) p[c] = ld_in(a.p, (long long)k * R::P + c, a.N, i, a.p_shared);
 }
 
+#ifndef OZ_MB_COLLOC
+#define OZ_MB_COLLOC 3
+#endif
 template <class R, typename T, int S>
-__global__ void __launch_bounds__(128) colloc_residual_kernel(const ColArgs<T> a) {
+__global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_residual_kernel(const ColArgs<T> a) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -132,7 +135,7 @@ OZ_D void col_step_vjp(const ColArgs<T>& a, int k, long long i, const T* th, con
 }
 
 template <class R, typename T, int S>
-__global__ void __launch_bounds__(128) colloc_vjp_kernel(const ColArgs<T> a) {
+__global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_vjp_kernel(const ColArgs<T> a) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     const long long gi = (long long)blockIdx.x * blockDim.x + threadIdx.x;

@@ -24,6 +24,7 @@ namespace oz {
 constexpr int kPdeBlock = 256;
 constexpr int kPdeCpt = 4;                        // cells per thread
 constexpr int kPdeExt = kPdeBlock * kPdeCpt;      // cells per CTA including halos
+constexpr int kPdeLine = kPdeExt + 2;             // one shared-memory line: the tile plus a zero cell at either end
 
 template <typename T>
 struct PdeRhs {
@@ -90,10 +91,13 @@ OZ_D T block_sum(T v, T* sm) {
 // stages of one explicit step on the CTA's extended tile: F[i][m] for the cells this thread owns
 template <typename T, int S, bool WITH_DIAG>
 OZ_D void pde_stages(const PdeArgs<T>& a, T h, T ulo, T uhi, const T* yv, const bool* inside, const bool* in_h,
-                     T (*F)[kPdeCpt], T (*Dg)[kPdeCpt], T* line) {
+                     T (*F)[kPdeCpt], T (*Dg)[kPdeCpt], T* line2) {
+    // `line2` holds two lines used alternately: stage i+1 may overwrite its line while slower warps still read
+    // stage i's, so one barrier per stencil application is enough
     const Tableau<T>& tab = a.tab;
 #pragma unroll
     for (int i = 0; i < S; ++i) {
+        T* line = line2 + (i & 1) * kPdeLine;
         T Yi[kPdeCpt];
         const T ui = ulo * (T(1) - tab.C[i]) + uhi * tab.C[i];
 #pragma unroll
@@ -116,20 +120,22 @@ OZ_D void pde_stages(const PdeArgs<T>& a, T h, T ulo, T uhi, const T* yv, const 
                 F[i][m] = inside[m] ? a.rhs.f(line[e], Yi[m], line[e + 2], ui, in_h[m]) : T(0);
             }
         }
-        __syncthreads();
     }
 }
 
+#ifndef OZ_MB_PDE
+#define OZ_MB_PDE 3
+#endif
 template <typename T, int S>
-__global__ void __launch_bounds__(kPdeBlock, 3) pde_step_kernel(const PdeArgs<T> a) {
-    __shared__ T line[kPdeExt + 2];
+__global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE) pde_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line[2 * kPdeLine];
     __shared__ T red[32];
     constexpr int HALO = S;
     const int interior = a.tile;
     const long long base = (long long)blockIdx.x * interior - HALO;
     if (threadIdx.x == 0) {
-        line[0] = T(0);
-        line[kPdeExt + 1] = T(0);
+        line[0] = line[kPdeLine] = T(0);
+        line[kPdeExt + 1] = line[kPdeLine + kPdeExt + 1] = T(0);
     }
     T yv[kPdeCpt], F[S][kPdeCpt];
     bool inside[kPdeCpt], in_h[kPdeCpt];
@@ -178,15 +184,15 @@ __global__ void __launch_bounds__(kPdeBlock) pde_sumsq_kernel(const T* __restric
 
 template <typename T, int S>
 __global__ void __launch_bounds__(kPdeBlock, 2) pde_adjoint_step_kernel(const PdeArgs<T> a) {
-    __shared__ T line[kPdeExt + 2];
+    __shared__ T line2[2 * kPdeLine];
     __shared__ T red[32];
     constexpr int HALO = 2 * S;
     const Tableau<T>& tab = a.tab;
     const int interior = a.tile;
     const long long base = (long long)blockIdx.x * interior - HALO;
     if (threadIdx.x == 0) {
-        line[0] = T(0);
-        line[kPdeExt + 1] = T(0);
+        line2[0] = line2[kPdeLine] = T(0);
+        line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
     }
     T yv[kPdeCpt], lam[kPdeCpt], F[S][kPdeCpt], Yb[S][kPdeCpt], Dg[S][kPdeCpt];
     bool inside[kPdeCpt], in_h[kPdeCpt];
@@ -201,12 +207,13 @@ __global__ void __launch_bounds__(kPdeBlock, 2) pde_adjoint_step_kernel(const Pd
     }
     const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
     const T fbs = a.field_bar ? __ldg(a.field_bar) * a.fb_scale : T(0);
-    pde_stages<T, S, true>(a, h, ulo, uhi, yv, inside, in_h, F, Dg, line);
+    pde_stages<T, S, true>(a, h, ulo, uhi, yv, inside, in_h, F, Dg, line2);
 
     // transposed stage chain:  G_i = h (b_i lam + sum_{j>i} a_ji Ybar_j),  Ybar_i = J(Y_i)^T G_i
     T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
 #pragma unroll
     for (int i = S - 1; i >= 0; --i) {
+        T* line = line2 + ((S + (S - 1 - i)) & 1) * kPdeLine;   // keeps alternating after the S forward stages
         T G[kPdeCpt];
 #pragma unroll
         for (int m = 0; m < kPdeCpt; ++m) {
@@ -234,7 +241,6 @@ __global__ void __launch_bounds__(kPdeBlock, 2) pde_adjoint_step_kernel(const Pd
         }
         u_lo_acc += (T(1) - tab.C[i]) * usum;
         u_hi_acc += tab.C[i] * usum;
-        __syncthreads();
     }
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) {
