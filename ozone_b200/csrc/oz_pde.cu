@@ -21,8 +21,17 @@
 
 namespace oz {
 
-constexpr int kPdeBlock = 256;
-constexpr int kPdeCpt = 4;                        // cells per thread
+#ifndef OZ_PDE_BLOCK
+#define OZ_PDE_BLOCK 256
+#endif
+#ifndef OZ_PDE_CPT
+#define OZ_PDE_CPT 4
+#endif
+#ifndef OZ_MB_PDE_ADJ
+#define OZ_MB_PDE_ADJ 2
+#endif
+constexpr int kPdeBlock = OZ_PDE_BLOCK;
+constexpr int kPdeCpt = OZ_PDE_CPT;                // cells per thread
 constexpr int kPdeExt = kPdeBlock * kPdeCpt;      // cells per CTA including halos
 constexpr int kPdeLine = kPdeExt + 2;             // one shared-memory line: the tile plus a zero cell at either end
 
@@ -88,73 +97,101 @@ OZ_D T block_sum(T v, T* sm) {
     return r;  // valid in warp 0
 }
 
-// stages of one explicit step on the CTA's extended tile: F[i][m] for the cells this thread owns
-template <typename T, int S, bool WITH_DIAG>
-OZ_D void pde_stages(const PdeArgs<T>& a, T h, T ulo, T uhi, const T* yv, const bool* inside, const bool* in_h,
+// Per-CTA view of the tile.  EDGE = false is the fast path taken by CTAs whose extended tile lies inside the
+// domain and does not straddle an end of the control window: no per-cell predicates at all.
+template <typename T, bool EDGE>
+struct PdeTile {
+    bool inside[kPdeCpt];
+    T uh[kPdeCpt];     // 1 where the control acts on the cell, else 0 (EDGE only)
+    T uh_all;          // the same for the whole tile (fast path)
+    OZ_D bool in(int m) const { return EDGE ? inside[m] : true; }
+    OZ_D T mask(int m) const { return EDGE ? uh[m] : uh_all; }
+};
+
+// stages of one explicit step on the CTA's extended tile: F[i][m] for the cells this thread owns.
+// `line2` holds two lines used alternately: stage i+1 may overwrite its line while slower warps still read
+// stage i's, so one barrier per stencil application is enough.
+template <typename T, int S, bool WITH_DIAG, bool EDGE>
+OZ_D void pde_stages(const PdeArgs<T>& a, const PdeTile<T, EDGE>& tl, T h, T ulo, T uhi, const T* yv,
                      T (*F)[kPdeCpt], T (*Dg)[kPdeCpt], T* line2) {
-    // `line2` holds two lines used alternately: stage i+1 may overwrite its line while slower warps still read
-    // stage i's, so one barrier per stencil application is enough
     const Tableau<T>& tab = a.tab;
+    const T du = uhi - ulo;
 #pragma unroll
     for (int i = 0; i < S; ++i) {
         T* line = line2 + (i & 1) * kPdeLine;
         T Yi[kPdeCpt];
-        const T ui = ulo * (T(1) - tab.C[i]) + uhi * tab.C[i];
+        const T bu_ui = a.rhs.beta_u * (ulo + tab.C[i] * du);   // beta_U * u at the stage abscissa
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) Yi[m] = yv[m];
+#pragma unroll
+        for (int j = 0; j < i; ++j) {
+            const T haij = h * tab.a(i, j);          // CTA-uniform; the zero entries of a sparse tableau (RK4: 3 of 6)
+            if (haij != T(0)) {                      // skip their kPdeCpt FMAs with one uniform branch
+#pragma unroll
+                for (int m = 0; m < kPdeCpt; ++m) Yi[m] += haij * F[j][m];
+            }
+        }
 #pragma unroll
         for (int m = 0; m < kPdeCpt; ++m) {
-            T acc = T(0);
-#pragma unroll
-            for (int j = 0; j < i; ++j) acc += tab.a(i, j) * F[j][m];
-            Yi[m] = inside[m] ? yv[m] + h * acc : T(0);
+            if (EDGE && !tl.inside[m]) Yi[m] = T(0);
             line[1 + threadIdx.x + m * kPdeBlock] = Yi[m];
         }
         __syncthreads();
 #pragma unroll
         for (int m = 0; m < kPdeCpt; ++m) {
             const int e = threadIdx.x + m * kPdeBlock;
-            if constexpr (WITH_DIAG) {
-                T dg = T(0);
-                F[i][m] = inside[m] ? a.rhs.f_and_diag(line[e], Yi[m], line[e + 2], ui, in_h[m], dg) : T(0);
-                Dg[i][m] = dg;
-            } else {
-                F[i][m] = inside[m] ? a.rhs.f(line[e], Yi[m], line[e + 2], ui, in_h[m]) : T(0);
-            }
+            const T x = Yi[m];
+            const T q = T(1) / (T(1) + x);
+            const T ex = a.rhs.beta_t * exp(-a.rhs.gamma * q);
+            T f = (line[e] - T(2) * x + line[e + 2]) * a.rhs.inv_dx2 + ex - a.rhs.bt_emg + (tl.mask(m) * bu_ui - a.rhs.beta_u * x);
+            if (EDGE && !tl.inside[m]) f = T(0);
+            F[i][m] = f;
+            if constexpr (WITH_DIAG) Dg[i][m] = ex * a.rhs.gamma * q * q - a.rhs.beta_u;   // d(reaction + transfer)/dx, same exp
         }
     }
 }
 
-#ifndef OZ_MB_PDE
-#define OZ_MB_PDE 3
-#endif
-template <typename T, int S>
-__global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE) pde_step_kernel(const PdeArgs<T> a) {
-    __shared__ T line[2 * kPdeLine];
-    __shared__ T red[32];
+template <typename T, bool EDGE>
+OZ_D void pde_tile_setup(const PdeArgs<T>& a, long long base, PdeTile<T, EDGE>& tl) {
+    if constexpr (EDGE) {
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) {
+            const long long j = base + threadIdx.x + m * kPdeBlock;
+            tl.inside[m] = j >= 0 && j < a.nx;
+            const long long g = j + a.x_off;
+            tl.uh[m] = (g >= a.rhs.h_lo && g < a.rhs.h_hi) ? T(1) : T(0);
+        }
+    } else {
+        const long long g = base + a.x_off;
+        tl.uh_all = (g >= a.rhs.h_lo && g < a.rhs.h_hi) ? T(1) : T(0);
+    }
+}
+
+// true when the CTA needs the predicated path: it touches an end of the domain or of the control window
+template <typename T>
+OZ_D bool pde_is_edge(const PdeArgs<T>& a, long long base) {
+    const long long g0 = base + a.x_off, g1 = g0 + kPdeExt;   // global range of the extended tile
+    const bool cut_lo = g0 < a.rhs.h_lo && g1 > a.rhs.h_lo, cut_hi = g0 < a.rhs.h_hi && g1 > a.rhs.h_hi;
+    return base < 0 || base + kPdeExt > a.nx || cut_lo || cut_hi;
+}
+
+template <typename T, int S, bool EDGE>
+OZ_D void pde_step_body(const PdeArgs<T>& a, long long base, T* line2, T* red) {
     constexpr int HALO = S;
     const int interior = a.tile;
-    const long long base = (long long)blockIdx.x * interior - HALO;
-    if (threadIdx.x == 0) {
-        line[0] = line[kPdeLine] = T(0);
-        line[kPdeExt + 1] = line[kPdeLine + kPdeExt + 1] = T(0);
-    }
+    PdeTile<T, EDGE> tl;
+    pde_tile_setup<T, EDGE>(a, base, tl);
     T yv[kPdeCpt], F[S][kPdeCpt];
-    bool inside[kPdeCpt], in_h[kPdeCpt];
 #pragma unroll
-    for (int m = 0; m < kPdeCpt; ++m) {
-        const long long j = base + threadIdx.x + m * kPdeBlock;
-        inside[m] = j >= 0 && j < a.nx;
-        yv[m] = inside[m] ? __ldg(a.y_in + j) : T(0);
-        const long long g = j + a.x_off;
-        in_h[m] = g >= a.rhs.h_lo && g < a.rhs.h_hi;
-    }
+    for (int m = 0; m < kPdeCpt; ++m) yv[m] = tl.in(m) ? __ldg(a.y_in + base + threadIdx.x + m * kPdeBlock) : T(0);
     const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
-    pde_stages<T, S, false>(a, h, ulo, uhi, yv, inside, in_h, F, nullptr, line);
+    pde_stages<T, S, false, EDGE>(a, tl, h, ulo, uhi, yv, F, nullptr, line2);
     T acc2 = T(0);
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) {
         const int e = threadIdx.x + m * kPdeBlock;
         const long long j = base + e;
-        if (e >= HALO && e < HALO + interior && inside[m]) {
+        if (e >= HALO && e < HALO + interior && tl.in(m)) {
             T acc = T(0);
 #pragma unroll
             for (int i = 0; i < S; ++i) acc += a.tab.B[i] * F[i][m];
@@ -167,6 +204,24 @@ __global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE) pde_step_kernel(const Pd
         const T s = block_sum(acc2, red);
         if (threadIdx.x == 0) a.part_sq[blockIdx.x] = s;
     }
+}
+
+#ifndef OZ_MB_PDE
+#define OZ_MB_PDE 3
+#endif
+template <typename T, int S>
+__global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE) pde_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line2[2 * kPdeLine];
+    __shared__ T red[32];
+    const long long base = (long long)blockIdx.x * a.tile - S;
+    if (threadIdx.x == 0) {
+        line2[0] = line2[kPdeLine] = T(0);
+        line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
+    }
+    if (pde_is_edge(a, base))
+        pde_step_body<T, S, true>(a, base, line2, red);
+    else
+        pde_step_body<T, S, false>(a, base, line2, red);
 }
 
 // sum of squares of a vector over the owned cells (J_space of the initial condition)
@@ -182,81 +237,74 @@ __global__ void __launch_bounds__(kPdeBlock) pde_sumsq_kernel(const T* __restric
     if (threadIdx.x == 0) part[blockIdx.x] = s;
 }
 
-template <typename T, int S>
-__global__ void __launch_bounds__(kPdeBlock, 2) pde_adjoint_step_kernel(const PdeArgs<T> a) {
-    __shared__ T line2[2 * kPdeLine];
-    __shared__ T red[32];
+template <typename T, int S, bool EDGE>
+OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red) {
     constexpr int HALO = 2 * S;
     const Tableau<T>& tab = a.tab;
     const int interior = a.tile;
-    const long long base = (long long)blockIdx.x * interior - HALO;
-    if (threadIdx.x == 0) {
-        line2[0] = line2[kPdeLine] = T(0);
-        line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
-    }
+    PdeTile<T, EDGE> tl;
+    pde_tile_setup<T, EDGE>(a, base, tl);
     T yv[kPdeCpt], lam[kPdeCpt], F[S][kPdeCpt], Yb[S][kPdeCpt], Dg[S][kPdeCpt];
-    bool inside[kPdeCpt], in_h[kPdeCpt];
+    bool owned[kPdeCpt];
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) {
-        const long long j = base + threadIdx.x + m * kPdeBlock;
-        inside[m] = j >= 0 && j < a.nx;
-        yv[m] = inside[m] ? __ldg(a.y_in + j) : T(0);
-        lam[m] = inside[m] ? __ldg(a.lam_in + j) : T(0);
-        const long long g = j + a.x_off;
-        in_h[m] = g >= a.rhs.h_lo && g < a.rhs.h_hi;
+        const int e = threadIdx.x + m * kPdeBlock;
+        const long long j = base + e;
+        yv[m] = tl.in(m) ? __ldg(a.y_in + j) : T(0);
+        lam[m] = tl.in(m) ? __ldg(a.lam_in + j) : T(0);
+        owned[m] = e >= HALO && e < HALO + interior && tl.in(m) && j >= a.own_lo && j < a.own_hi;
     }
     const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
     const T fbs = a.field_bar ? __ldg(a.field_bar) * a.fb_scale : T(0);
-    pde_stages<T, S, true>(a, h, ulo, uhi, yv, inside, in_h, F, Dg, line2);
+    pde_stages<T, S, true, EDGE>(a, tl, h, ulo, uhi, yv, F, Dg, line2);
 
-    // transposed stage chain:  G_i = h (b_i lam + sum_{j>i} a_ji Ybar_j),  Ybar_i = J(Y_i)^T G_i
+    // transposed stage chain:  W_i = b_i lam + sum_{j>i} a_ji Ybar_j,  G_i = h W_i,  Ybar_i = J(Y_i)^T G_i
+    // h_bar = sum_i W_i . F_i (no division by h);  u_bar parts from beta_U H . G_i
     T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
 #pragma unroll
     for (int i = S - 1; i >= 0; --i) {
         T* line = line2 + ((S + (S - 1 - i)) & 1) * kPdeLine;   // keeps alternating after the S forward stages
         T G[kPdeCpt];
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
-            T acc = tab.B[i] * lam[m];
+        for (int m = 0; m < kPdeCpt; ++m) G[m] = tab.B[i] * lam[m];
 #pragma unroll
-            for (int j = i + 1; j < S; ++j) acc += tab.a(j, i) * Yb[j][m];
-            G[m] = inside[m] ? h * acc : T(0);
-            line[1 + threadIdx.x + m * kPdeBlock] = G[m];
+        for (int j = i + 1; j < S; ++j) {
+            const T aji = tab.a(j, i);
+            if (aji != T(0)) {
+#pragma unroll
+                for (int m = 0; m < kPdeCpt; ++m) G[m] += aji * Yb[j][m];
+            }
         }
-        __syncthreads();
         T usum = T(0);
 #pragma unroll
         for (int m = 0; m < kPdeCpt; ++m) {
-            const int e = threadIdx.x + m * kPdeBlock;
-            const long long j = base + e;
-            T af = T(0);  // sum_j a_ij F_j  -> Y_i and the h_bar term
-#pragma unroll
-            for (int jj = 0; jj < i; ++jj) af += tab.a(i, jj) * F[jj][m];
-            Yb[i][m] = inside[m] ? (line[e] - T(2) * G[m] + line[e + 2]) * a.rhs.inv_dx2 + Dg[i][m] * G[m] : T(0);
-            const bool owned = e >= HALO && e < HALO + interior && inside[m] && j >= a.own_lo && j < a.own_hi;
-            if (owned) {
-                if (in_h[m]) usum += a.rhs.beta_u * G[m];
-                h_acc += Yb[i][m] * af;
-            }
+            if (owned[m]) h_acc += G[m] * F[i][m];
+            G[m] = (EDGE && !tl.inside[m]) ? T(0) : h * G[m];
+            if (owned[m]) usum += tl.mask(m) * G[m];
+            line[1 + threadIdx.x + m * kPdeBlock] = G[m];
         }
-        u_lo_acc += (T(1) - tab.C[i]) * usum;
+        __syncthreads();
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) {
+            const int e = threadIdx.x + m * kPdeBlock;
+            const T v = (line[e] - T(2) * G[m] + line[e + 2]) * a.rhs.inv_dx2 + Dg[i][m] * G[m];
+            Yb[i][m] = (EDGE && !tl.inside[m]) ? T(0) : v;
+        }
+        usum *= a.rhs.beta_u;
         u_hi_acc += tab.C[i] * usum;
+        u_lo_acc += usum - tab.C[i] * usum;
     }
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) {
         const int e = threadIdx.x + m * kPdeBlock;
         const long long j = base + e;
-        if (e >= HALO && e < HALO + interior && inside[m]) {
-            T bf = T(0), yb = T(0);
+        if (e >= HALO && e < HALO + interior && tl.in(m)) {
+            T yb = T(0);
 #pragma unroll
-            for (int i = 0; i < S; ++i) {
-                bf += tab.B[i] * F[i][m];
-                yb += Yb[i][m];
-            }
+            for (int i = 0; i < S; ++i) yb += Yb[i][m];
             T out = lam[m] + yb + fbs * yv[m];
             if (a.hist_bar_k) out += __ldg(a.hist_bar_k + j);
             a.lam_out[j] = out;
-            if (j >= a.own_lo && j < a.own_hi) h_acc += bf * lam[m];
         }
     }
     T s = block_sum(h_acc, red);
@@ -265,6 +313,21 @@ __global__ void __launch_bounds__(kPdeBlock, 2) pde_adjoint_step_kernel(const Pd
     if (threadIdx.x == 0) a.part_ulo[blockIdx.x] = s;
     s = block_sum(u_hi_acc, red);
     if (threadIdx.x == 0) a.part_uhi[blockIdx.x] = s;
+}
+
+template <typename T, int S>
+__global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE_ADJ) pde_adjoint_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line2[2 * kPdeLine];
+    __shared__ T red[32];
+    const long long base = (long long)blockIdx.x * a.tile - 2 * S;
+    if (threadIdx.x == 0) {
+        line2[0] = line2[kPdeLine] = T(0);
+        line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
+    }
+    if (pde_is_edge(a, base))
+        pde_adjoint_body<T, S, true>(a, base, line2, red);
+    else
+        pde_adjoint_body<T, S, false>(a, base, line2, red);
 }
 
 // lam_n = final_bar + hist_bar[n] + field_bar * (200/nx) * y_n
