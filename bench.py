@@ -510,13 +510,22 @@ def main():
         else:
             note = 'HBM / FP64 co-limited explicit path (DESIGN.md section 5)'
         roof = dict({'bound': 'hbm'}, **dominant)
+        roof['frac_of_nominal_8000'] = dominant['achieved'] / 8000.0       # the north star's denominator
+        try:
+            roof['fma_peak_measured_tflops'] = {'f64': run.engine.measure_fma_peak(torch.float64, dev),
+                                                'f32': run.engine.measure_fma_peak(torch.float32, dev)}
+        except Exception as exc:                                            # never let the probe break the bench line
+            roof['fma_peak_measured_tflops'] = {'error': str(exc)}
         roof.update({'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6650 GB/s',
                      'traffic_source': traffic.get('source'), 'other_kernel': other, 'note': note})
         cpu = None
         if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
-            v, sample, _ = cpu_port_throughput(wl, cores, args.cpu_traj_per_core or CPU_SAMPLE[run.kind])
-            cpu = {'value': v, 'unit': 'state-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample}
+            per_core = args.cpu_traj_per_core or CPU_SAMPLE[run.kind]
+            v, sample, _ = cpu_port_throughput(wl, cores, per_core)
+            v1, _, _ = cpu_port_throughput(wl, 1, max(per_core // 4, 8))       # the reference's scripts pin one thread
+            cpu = {'value': v, 'unit': 'state-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample,
+                   'single_core_value': v1}
         line = {
             'metric': 'state-steps/sec (fwd+adjoint)', 'value': value, 'unit': 'state-steps/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': step_ms / args.steps, 'higher_is_better': True,

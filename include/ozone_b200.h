@@ -176,6 +176,11 @@ OZ_API size_t oz_colloc_vjp_workspace_bytes(const oz_problem* pb);
 OZ_API int oz_colloc_vjp(const oz_problem* pb, const void* Y, const void* y, const void* mu1, const void* mu2,
                   void* Y_bar, void* y_bar);
 
+/* Measurement aid (no counterpart in the reference): enqueue a register-resident FMA loop and return its
+ * flop count, so the caller can time the FP64 (or FP32) vector peak of the box with events.  bench.py reports it
+ * beside the HBM roofline because the implicit path is FP64-bound.  `out`: one device scalar. */
+OZ_API double oz_fma_probe(int dtype, int iters, void* out, void* stream);
+
 /* Register a right-hand side compiled separately (ozone_b200/trace.py turns a Python callback into CUDA
  * source and builds it against the same kernel templates).  `so_path` is a shared object exporting
  * `oz_plugin_describe`; returns the rhs_id to put in oz_problem.rhs_id (>= OZ_RHS_PLUGIN_BASE) or < 0.

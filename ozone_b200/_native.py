@@ -57,6 +57,7 @@ SYMBOLS = {
     'oz_last_error': (C.c_char_p, []),
     'oz_rhs_info': (C.c_int, [C.c_int, _IP, _IP, _IP, _IP, _IP, _IP]),
     'oz_register_rhs_plugin': (C.c_int, [C.c_char_p]),
+    'oz_fma_probe': (C.c_double, [C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'oz_rhs_eval': (C.c_int, [_PB, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'oz_tm_forward_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_forward': (C.c_int, [_PB]),

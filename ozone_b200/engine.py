@@ -587,3 +587,20 @@ class PipelinedTmSolve:
     @property
     def launches(self):
         return sum(pl.launches_forward + pl.launches_adjoint for pl in self.plans)
+
+
+def measure_fma_peak(dtype=torch.float64, device='cuda', iters=20000, repeats=3):
+    """Measured vector FMA peak of this GPU in TFLOP/s (oz_fma_probe timed with CUDA events, best of `repeats`)."""
+    out = torch.zeros(1, dtype=dtype, device=device)
+    code = nat.OZ_F64 if dtype == torch.float64 else nat.OZ_F32
+    stream = torch.cuda.current_stream().cuda_stream
+    nat.lib.oz_fma_probe(code, 200, out.data_ptr(), stream)           # warm-up
+    best = 0.0
+    for _ in range(repeats):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        flops = nat.lib.oz_fma_probe(code, iters, out.data_ptr(), stream)
+        e1.record()
+        torch.cuda.synchronize()
+        best = max(best, flops / (e0.elapsed_time(e1) * 1e-3) / 1e12)
+    return best

@@ -84,10 +84,14 @@ def test_picard_gradients_via_time_marching_adjoint():
 
 
 @pytest.mark.parametrize('method', ['RK4', 'GaussLegendre6', 'ForwardEuler'])
-@pytest.mark.parametrize('name', ['lunar_ascent', 'van_der_pol', 'lotka_volterra_shared'])
+@pytest.mark.parametrize('name', ['lunar_ascent', 'lunar_ascent_tf_per_design', 'van_der_pol', 'lotka_volterra_shared'])
 def test_config5_collocation_residual_and_vjp(name, method):
     if name == 'lunar_ascent':
         c = cases.ascent_inputs(N=70, nt=21)
+    elif name == 'lunar_ascent_tf_per_design':       # tf ~ U(0.08, 0.12) per design -> per-trajectory steps
+        c = cases.ascent_inputs(N=45, nt=15)
+        tf = np.random.default_rng(9).uniform(0.08, 0.12, size=45)
+        c['h'] = np.tile(tf / 14.0, (14, 1))
     elif name == 'van_der_pol':
         c = cases.van_der_pol_inputs(N=45, nt=12)
     else:
