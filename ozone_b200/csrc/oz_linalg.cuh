@@ -125,6 +125,17 @@ struct SmemSystem {
 // register shuffling; the exchange itself is a chain of statically indexed, predicated row swaps.
 // The decision depends only on the thread's own data, so a trajectory's result does not depend on
 // its warp neighbours.  On return b holds the solution; false = a zero / non-finite pivot was met.
+// Reciprocal of a pivot: hardware seed (rcp.approx, ~2^-23) + two Newton steps -> full double precision without the
+// special-case branches of an IEEE division (pivots here are O(1); a zero / non-finite pivot is flagged by the caller).
+OZ_D double fast_rcp(double x) {
+    double r;
+    asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
+    r = fma(fma(-x, r, 1.0), r, r);
+    r = fma(fma(-x, r, 1.0), r, r);
+    return r;
+}
+OZ_D float fast_rcp(float x) { return 1.0f / x; }
+
 // (column K is a template parameter: plain "#pragma unroll" on the column loop is not honoured by nvcc
 // beyond M = 4, which turns every index dynamic and sends the matrix to local memory)
 template <typename T, int M, int K>
@@ -145,7 +156,7 @@ struct RegElim {
         }
         const T piv = a[K][K];
         if (!(fabs(piv) > T(0)) || !isfinite(piv)) ok = false;
-        const T inv = T(1) / piv;
+        const T inv = fast_rcp(piv);
         a[K][K] = inv;
 #pragma unroll
         for (int r = K + 1; r < M; ++r) {

@@ -125,7 +125,7 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 status |= OZ_STATUS_NONFINITE;
                 break;
             }
-            if (sqrt(rn2) < a.newton_tol) break;
+            if (rn2 < a.newton_tol * a.newton_tol) break;   // ||R||_2 < tol without the square root
             if (it >= a.newton_max_iter) {
                 status |= OZ_STATUS_NOT_CONVERGED;
                 break;
@@ -211,7 +211,7 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 status |= OZ_STATUS_NONFINITE;
                 break;
             }
-            if (sqrt(rn2) < a.newton_tol) break;
+            if (rn2 < a.newton_tol * a.newton_tol) break;   // ||R||_2 < tol without the square root
             if (it >= a.newton_max_iter) {
                 status |= OZ_STATUS_NOT_CONVERGED;
                 break;
@@ -291,9 +291,19 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
             for (int c = 0; c < DM::NP; ++c) a.prof[c * N + i] = prof[c];
     }
 
+    // p[k+1] and h[k] are fetched one step ahead: at 2-4 warps per scheduler a load issued at the top of the step
+    // that needs it is a fully exposed DRAM round trip (ncu: the first use was the kernel's top stall)
+    T pnext[DM::P1], hnext;
+    load_params<R>(a, 1, i, pnext);
+    hnext = ld_in(a.h, 0, N, i, a.h_shared);
     for (int k = 0; k < a.n; ++k) {
-        const T h = ld_in(a.h, k, N, i, a.h_shared);
-        load_params<R>(a, k + 1, i, phi);
+        const T h = hnext;
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) phi[c] = pnext[c];
+        if (k + 1 < a.n) {
+            load_params<R>(a, k + 2, i, pnext);
+            hnext = ld_in(a.h, k + 1, N, i, a.h_shared);
+        }
         stage_params<R, T, S>(a.tab, plo, phi, ps);
         solve_stages<R, T, S, IMPL>(a, y, h, ps, th, Y, F, smem, status, iters);
         if constexpr (IMPL) {
