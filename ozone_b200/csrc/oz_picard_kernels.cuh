@@ -37,13 +37,16 @@ struct PicardArgs {
     int *status, *iters;
 };
 
+// C > 0: the lane's `chunk` of steps is the compile-time constant C and A.hF stays in REGISTERS (half the shared
+// memory per trajectory -> twice the resident warps, no LDS/STS for it); C = 0: any chunk, A.hF in shared memory.
 template <class R, int S>
-inline size_t picard_elems_per_lane(int chunk) {
-    return (size_t)2 * chunk * S * R::D + (size_t)chunk * R::D + (size_t)(chunk + 1) * AtLeast1<R::P>::value + chunk;
+inline size_t picard_elems_per_lane(int chunk, bool af_in_regs) {
+    return (size_t)(af_in_regs ? 1 : 2) * chunk * S * R::D + (size_t)chunk * R::D +
+           (size_t)(chunk + 1) * AtLeast1<R::P>::value + chunk;
 }
 
-template <class R, typename T, int S>
-__global__ void __launch_bounds__(256) picard_kernel(const PicardArgs<T> a) {
+template <class R, typename T, int S, int C>
+__global__ void __launch_bounds__(C > 0 ? 512 : 256) picard_kernel(const PicardArgs<T> a) {
     using DM = Dims<R>;
     constexpr int D = DM::D, P = DM::P;
     extern __shared__ __align__(16) unsigned char smem[];
@@ -51,13 +54,20 @@ __global__ void __launch_bounds__(256) picard_kernel(const PicardArgs<T> a) {
     const long long traj = (long long)blockIdx.x * (blockDim.x >> 5) + (tid >> 5);
     if (traj >= a.N) return;  // whole warp leaves together; only warp-level sync below
     const long long N = a.N, i = traj;
-    const int n = a.n, c = a.chunk;
+    const int n = a.n, c = C > 0 ? C : a.chunk;
     const int k0 = lane * c;
     const Tableau<T>& tab = a.tab;
 
     T* Yb = reinterpret_cast<T*>(smem) + tid;     // [c][S][D]
-    T* AF = Yb + (size_t)c * S * D * stride;      // [c][S][D]
-    T* inc = AF + (size_t)c * S * D * stride;     // [c][D]   lane-local inclusive prefix of h sum_i b_i F_i
+    T* AF = Yb + (size_t)c * S * D * stride;      // [c][S][D]  (C = 0 only)
+    T* inc = AF + (C > 0 ? (size_t)0 : (size_t)c * S * D * stride);   // [c][D]   lane-local inclusive prefix of h sum_i b_i F_i
+    T AFr[C > 0 ? C : 1][S][D];
+    auto af_set = [&](int q, int s, int cc, T v) {
+        if constexpr (C > 0) AFr[q][s][cc] = v; else AF[(size_t)((q * S + s) * D + cc) * stride] = v;
+    };
+    auto af_get = [&](int q, int s, int cc) -> T {
+        if constexpr (C > 0) return AFr[q][s][cc]; else return AF[(size_t)((q * S + s) * D + cc) * stride];
+    };
     T* pp = inc + (size_t)c * D * stride;         // [c+1][P] raw parameters at this lane's grid points
     T* hh = pp + (size_t)(c + 1) * DM::P1 * stride;  // [c]
 #define LP(buf, j) (buf)[(size_t)(j) * stride]
@@ -95,8 +105,9 @@ __global__ void __launch_bounds__(256) picard_kernel(const PicardArgs<T> a) {
             T run[D];
 #pragma unroll
             for (int cc = 0; cc < D; ++cc) run[cc] = T(0);
+#pragma unroll
             for (int q = 0; q < c; ++q) {
-                if (k0 + q >= n) break;
+                if (k0 + q >= n) continue;
                 T Y[S][D], F[S][D], ps[S][DM::P1], plo[DM::P1], phi[DM::P1];
                 const T h = LP(hh, q);
 #pragma unroll
@@ -120,7 +131,7 @@ __global__ void __launch_bounds__(256) picard_kernel(const PicardArgs<T> a) {
                         T acca = T(0);
 #pragma unroll
                         for (int j = 0; j < S; ++j) acca += tab.a(s, j) * F[j][cc];
-                        LP(AF, (q * S + s) * D + cc) = h * acca;
+                        af_set(q, s, cc, h * acca);
                     }
                     run[cc] += h * accb;
                     LP(inc, q * D + cc) = run[cc];
@@ -139,13 +150,16 @@ __global__ void __launch_bounds__(256) picard_kernel(const PicardArgs<T> a) {
             }
             // ---- pass 2: stages = A.hF + S_k ; residual and update for the components of this block
             T rn2 = T(0);
+#pragma unroll
             for (int q = 0; q < c; ++q) {
-                if (k0 + q >= n) break;
-                for (int cc = lo; cc < hi; ++cc) {
+                if (k0 + q >= n) continue;
+#pragma unroll
+                for (int cc = 0; cc < D; ++cc) {
+                    if (cc < lo || cc >= hi) continue;
                     const T Sk = y0[cc] + off[cc] + (q > 0 ? LP(inc, (q - 1) * D + cc) : T(0));
 #pragma unroll
                     for (int s = 0; s < S; ++s) {
-                        const T ynew = LP(AF, (q * S + s) * D + cc) + Sk;
+                        const T ynew = af_get(q, s, cc) + Sk;
                         const T r = LP(Yb, (q * S + s) * D + cc) - ynew;
                         rn2 += r * r;
                         LP(Yb, (q * S + s) * D + cc) = ynew;
@@ -291,19 +305,28 @@ int run_picard(const oz_problem* pb, const void* guess, double tol, int max_swee
     a.field = (T*)pb->field;
     a.status = pb->status;
     a.iters = pb->iters;
-    const size_t per_lane = picard_elems_per_lane<R, S>(a.chunk) * sizeof(T);
-    int warps = 8;
+    // register variant when the lane's chunk is small and C * S * D doubles fit the register file comfortably
+    const int creg = a.chunk <= 1 ? 1 : (a.chunk <= 2 ? 2 : (a.chunk <= 4 ? 4 : 0));
+    const bool regs = creg > 0 && (size_t)creg * S * R::D * sizeof(T) <= 256;
+    if (regs) a.chunk = creg;
+    const size_t per_lane = picard_elems_per_lane<R, S>(a.chunk, regs) * sizeof(T);
+    int warps = regs ? 16 : 8;
     while (warps > 1 && per_lane * 32 * warps > kSmemBudget) warps >>= 1;
     const size_t smem = per_lane * 32 * warps;
     OZ_REQUIRE(smem <= 227 * 1024,
                "Picard iterate of one trajectory (%zu bytes) does not fit in shared memory; use TimeMarching", smem);
-    auto kern = picard_kernel<R, T, S>;
-    if (smem > 48 * 1024) OZ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long nblk = (pb->N + warps - 1) / warps;
     OZ_REQUIRE(nblk < (1ll << 31), "batch too large for one launch");
-    kern<<<(unsigned)nblk, warps * 32, smem, (cudaStream_t)pb->stream>>>(a);
-    OZ_CUDA_CHECK(cudaGetLastError());
-    return 0;
+    auto launch = [&](auto kern) -> int {
+        if (smem > 48 * 1024) OZ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)nblk, warps * 32, smem, (cudaStream_t)pb->stream>>>(a);
+        OZ_CUDA_CHECK(cudaGetLastError());
+        return 0;
+    };
+    if (regs && creg == 1) return launch(picard_kernel<R, T, S, 1>);
+    if (regs && creg == 2) return launch(picard_kernel<R, T, S, 2>);
+    if (regs && creg == 4) return launch(picard_kernel<R, T, S, 4>);
+    return launch(picard_kernel<R, T, S, 0>);
 }
 
 template <class R>
