@@ -37,6 +37,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 PLUGIN_DIR = os.environ.get('OZONE_B200_PLUGIN_DIR') or os.path.join(os.path.dirname(_HERE), 'build', 'plugins')
 MAX_STATE = 32
 MAX_STATIC = 64
+_REGISTERED: dict = {}     # plugin path -> rhs_id (the library keeps a fixed table of registrations)
 
 
 # ================================================================================================
@@ -650,9 +651,12 @@ struct RhsTraced {{
             if res.returncode != 0:
                 raise RuntimeError(f'nvcc failed on the traced right-hand side:\n{res.stderr[-4000:]}')
             os.replace(so + '.tmp', so)
-        rid = nat.lib.oz_register_rhs_plugin(so.encode())
-        if rid < 0:
-            raise nat.OzError(f'oz_register_rhs_plugin: {nat.lib.oz_last_error().decode()}')
+        rid = _REGISTERED.get(so)                 # one registration per shared object and process
+        if rid is None:
+            rid = nat.lib.oz_register_rhs_plugin(so.encode())
+            if rid < 0:
+                raise nat.OzError(f'oz_register_rhs_plugin: {nat.lib.oz_last_error().decode()}')
+            _REGISTERED[so] = rid
         self._plugins[key] = rid
         return rid
 

@@ -209,3 +209,20 @@ def test_lotka_volterra_example_python_callback_and_collocation_constraints():
     assert tuple(o.states['x'].shape) == (num_times, 1)
     gY, = torch.autograd.grad((integ.c1 ** 2).sum() + (integ.c2 ** 2).sum(), [integ.stage_dv])
     assert torch.isfinite(gY).all() and float(gY.abs().max()) > 0
+
+
+def test_repeated_solves_reuse_one_plugin_registration():
+    from ozone_b200 import trace
+
+    def f(v):
+        v.d_states['y'] = -2.0 * v.states['y']
+    ids = set()
+    for _ in range(5):
+        p = ozone.ODEProblem(RK4(), TimeMarching())
+        p.add_state('y', var([1.0]), store_final=True)
+        p.set_timespan(ozone.timespans.StepVector(0.0, var(np.full(10, 0.05))))
+        p.set_function(f)
+        out = p.solve()
+        ids.add(p.integrator.spec.traced.plugin_id(4, False, True, 0))
+        assert float(out.final_states['y']) == pytest.approx(np.exp(-1.0), rel=1e-6)
+    assert len(ids) == 1
