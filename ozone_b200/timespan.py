@@ -5,15 +5,16 @@ from .utils import variablize, check_if_int
 
 
 def check_if_scalar(value, argname):
-    if value.numel() != 1:
-        raise ValueError(f'expected scalar for argument \'{argname}\' but got shape {tuple(value.shape)}')
-    return value.reshape((1,))
+    """one element of any shape -> shape (1,); anything else is a ValueError"""
+    if value.numel() == 1:
+        return value.reshape((1,))
+    raise ValueError(f"argument '{argname}' must hold exactly one value, its shape is {tuple(value.shape)}")
 
 
 def check_if_vector(value, argname):
-    if value.dim() == 1:
-        return value
-    raise ValueError(f'expected 1D vector for argument \'{argname}\' but got shape {tuple(value.shape)}')
+    if value.dim() != 1:
+        raise ValueError(f"argument '{argname}' must be one-dimensional, its shape is {tuple(value.shape)}")
+    return value
 
 
 class TimeSpan(object):
@@ -23,11 +24,10 @@ class TimeSpan(object):
 
     def finalize(self):
         """ozone/timespan.py:25-33."""
-        step_vector = self.step_vector
-        num_times = step_vector.shape[0] + 1
-        if num_times == 1:
-            raise ValueError('Atleast two time points are required to define a time span.')
-        return self.time_vector, step_vector, num_times
+        steps = self.step_vector
+        if steps.shape[0] < 1:
+            raise ValueError('a time span needs at least one step (two time points)')
+        return self.time_vector, steps, steps.shape[0] + 1
 
 
 class StepVector(TimeSpan):

@@ -1,4 +1,5 @@
-"""Argument checks with the reference's error types (``ozone/utils/general.py:2-39``)."""
+"""Argument checks (TypeError naming the offending argument, as ``ozone/utils/general.py`` does) and the
+conversion of user values to the engine's variable type."""
 import numpy as np
 import torch
 
@@ -20,28 +21,26 @@ def set_default_dtype(dtype):
 
 
 def get_type_string(value):
-    return f'\'{type(value).__name__}\''
+    return repr(type(value).__name__)
 
 
-def check_if_string(value, argname):
-    if not isinstance(value, str):
-        raise TypeError(f'expected type \'string\' for argument \'{argname}\' but got {get_type_string(value)}')
+def _type_check(expected_label, accept):
+    """Build a checker that raises TypeError naming the argument (the reference's convention, general.py:5-26)."""
+    def check(value, argname):
+        if not accept(value):
+            raise TypeError(f"argument '{argname}' must be {expected_label}, got {get_type_string(value)}")
+    return check
 
 
-def check_if_method(value, argname):
+def _is_method(v):
     from .methods import _Method
-    if not isinstance(value, _Method):
-        raise TypeError(f'expected type \'ozone.methods._Method\' for argument \'{argname}\' but got {get_type_string(value)}')
+    return isinstance(v, _Method)
 
 
-def check_if_bool(value, argname):
-    if not isinstance(value, bool):
-        raise TypeError(f'expected type \'bool\' for argument \'{argname}\' but got {get_type_string(value)}')
-
-
-def check_if_int(value, argname):
-    if isinstance(value, bool) or not isinstance(value, (int, np.int32, np.int64)):
-        raise TypeError(f'expected type \'int\' for argument \'{argname}\' but got {get_type_string(value)}')
+check_if_string = _type_check('a string', lambda v: isinstance(v, str))
+check_if_bool = _type_check('a bool', lambda v: isinstance(v, bool))
+check_if_int = _type_check('an int', lambda v: isinstance(v, (int, np.int32, np.int64)) and not isinstance(v, bool))
+check_if_method = _type_check('an instance of ozone.methods._Method', _is_method)
 
 
 def variablize(value, argname='value'):
