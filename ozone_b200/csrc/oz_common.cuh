@@ -87,6 +87,7 @@ struct TmArgs {
     int n;
     int num_inner;  // 0: full history available; > 0: checkpoints every num_inner steps
     int h_shared, p_shared, th_shared;
+    int chain;      // explicit tableau whose only nonzero A entries are a(i, i-1) (RK4, midpoint, Euler): one FMA per stage
     T newton_tol;
     int newton_max_iter;
     const T* y0;
@@ -120,6 +121,10 @@ inline TmArgs<T> make_tm_args(const oz_problem* pb) {
     a.N = pb->N;
     a.n = pb->n;
     a.num_inner = pb->num_inner;
+    a.chain = pb->is_explicit ? 1 : 0;
+    for (int i = 0; i < pb->num_stages; ++i)
+        for (int j = 0; j < pb->num_stages; ++j)
+            if (j != i - 1 && pb->A[i * kMaxS + j] != 0.0) a.chain = 0;
     a.h_shared = pb->h_shared;
     a.p_shared = pb->p_shared;
     a.th_shared = pb->th_shared;

@@ -47,6 +47,11 @@ constexpr int lb_blocks() {
     return 1;
 }
 
+template <bool B>
+struct BoolTag {
+    static constexpr bool value = B;
+};
+
 // Pull a line towards L1 ahead of its use.  The reverse sweep runs at 2-4 warps per scheduler (the
 // stage arrays take 120-255 registers), too few to hide a DRAM round trip behind other warps, and every
 // step starts with loads that nothing else depends on: their addresses are known one step ahead.
@@ -85,16 +90,32 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
     constexpr int D = R::D;
     const Tableau<T>& tab = a.tab;
     if constexpr (!IMPL) {
+        // The first stage of an explicit method is y itself (row 0 of A is empty).  Tableaux whose A has only the
+        // first subdiagonal (a.chain: RK4 is the one that matters) skip the structurally zero products.
+        if (S >= 3 && a.chain) {
 #pragma unroll
-        for (int i = 0; i < S; ++i) {
+            for (int i = 0; i < S; ++i) {
+                const T ha = i > 0 ? h * tab.a(i, i - 1) : T(0);
 #pragma unroll
-            for (int c = 0; c < D; ++c) {
-                T acc = T(0);
-#pragma unroll
-                for (int j = 0; j < i; ++j) acc += tab.a(i, j) * F[j][c];
-                Y[i][c] = y[c] + h * acc;
+                for (int c = 0; c < D; ++c) Y[i][c] = i > 0 ? y[c] + ha * F[i - 1][c] : y[c];
+                R::f(Y[i], ps[i], th, F[i]);
             }
-            R::f(Y[i], ps[i], th, F[i]);
+        } else {
+#pragma unroll
+            for (int i = 0; i < S; ++i) {
+#pragma unroll
+                for (int c = 0; c < D; ++c) {
+                    if (i == 0) {
+                        Y[i][c] = y[c];
+                        continue;
+                    }
+                    T acc = tab.a(i, 0) * F[0][c];
+#pragma unroll
+                    for (int j = 1; j < i; ++j) acc += tab.a(i, j) * F[j][c];
+                    Y[i][c] = y[c] + h * acc;
+                }
+                R::f(Y[i], ps[i], th, F[i]);
+            }
         }
     } else if constexpr (use_reg_solve<R, S, T>()) {
         // Register path.  States are split into DA active and DQ trailing quadrature states (zero Jacobian
@@ -489,46 +510,55 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
             for (int c = 0; c < D; ++c) Yb[i][c] = sys.v(i * D + c);
     }
 
-    hb = T(0);
+    hb = -T(0);
 #pragma unroll
     for (int c = 0; c < DM::P; ++c) {
-        pb_lo[c] = T(0);
-        pb_hi[c] = T(0);
+        pb_lo[c] = -T(0);
+        pb_hi[c] = -T(0);
     }
-#pragma unroll
-    for (int i = S - 1; i >= 0; --i) {
-        T G[D], pbi[DM::P1];
-#pragma unroll
-        for (int c = 0; c < DM::P1; ++c) pbi[c] = T(0);
-#pragma unroll
-        for (int c = 0; c < D; ++c) {
-            T acc = tab.B[i] * lam[c];
-            if constexpr (IMPL) {
-#pragma unroll
-                for (int j = 0; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
-            } else {
-#pragma unroll
-                for (int j = i + 1; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
+    auto stage_sweep = [&](auto chain_tag) {
+        [[maybe_unused]] constexpr bool CHAIN = decltype(chain_tag)::value;
+    #pragma unroll
+        for (int i = S - 1; i >= 0; --i) {
+            T G[D], pbi[DM::P1];
+    #pragma unroll
+            for (int c = 0; c < DM::P1; ++c) pbi[c] = -T(0);  // -0 is the exact additive identity: the first += folds away
+    #pragma unroll
+            for (int c = 0; c < D; ++c) {
+                T acc = tab.B[i] * lam[c];
+                if constexpr (IMPL) {
+    #pragma unroll
+                    for (int j = 0; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
+                } else if constexpr (CHAIN) {
+                    if (i + 1 < S) acc += tab.a(i + 1, i) * Yb[i + 1][c];
+                } else {
+    #pragma unroll
+                    for (int j = i + 1; j < S; ++j) acc += tab.a(j, i) * Yb[j][c];
+                }
+                hb += acc * F[i][c];  // h_bar = sum_i (G_i / h) . F_i without dividing by h (h = 0 is legal)
+                G[c] = h * acc;
             }
-            hb += acc * F[i][c];  // h_bar = sum_i (G_i / h) . F_i without dividing by h (h = 0 is legal)
-            G[c] = h * acc;
+            if constexpr (IMPL) {
+                T dummy[D];
+    #pragma unroll
+                for (int c = 0; c < D; ++c) dummy[c] = T(0);
+                R::vjp(Y[i], ps[i], th, G, dummy, pbi, tb);
+            } else {
+    #pragma unroll
+                for (int c = 0; c < D; ++c) Yb[i][c] = -T(0);
+                R::vjp(Y[i], ps[i], th, G, Yb[i], pbi, tb);
+            }
+    #pragma unroll
+            for (int c = 0; c < DM::P; ++c) {
+                pb_lo[c] += pbi[c];               // running total; the (1 - c_i) part is total - c_i part, taken below
+                pb_hi[c] += tab.C[i] * pbi[c];
+            }
         }
-        if constexpr (IMPL) {
-            T dummy[D];
-#pragma unroll
-            for (int c = 0; c < D; ++c) dummy[c] = T(0);
-            R::vjp(Y[i], ps[i], th, G, dummy, pbi, tb);
-        } else {
-#pragma unroll
-            for (int c = 0; c < D; ++c) Yb[i][c] = T(0);
-            R::vjp(Y[i], ps[i], th, G, Yb[i], pbi, tb);
-        }
-#pragma unroll
-        for (int c = 0; c < DM::P; ++c) {
-            pb_lo[c] += pbi[c];               // running total; the (1 - c_i) part is total - c_i part, taken below
-            pb_hi[c] += tab.C[i] * pbi[c];
-        }
-    }
+    };
+    if (!IMPL && S >= 3 && a.chain)
+        stage_sweep(BoolTag<true>{});
+    else
+        stage_sweep(BoolTag<false>{});
 #pragma unroll
     for (int c = 0; c < DM::P; ++c) pb_lo[c] -= pb_hi[c];
     // (h_bar: sum_i G_i . F_i = h [sum_i b_i F_i . lam + sum_j Ybar_j . sum_i a_ji F_i], accumulated above as
@@ -570,48 +600,97 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
     for (int c = 0; c < DM::NF; ++c) vf[c] = a.field_bar ? __ldg(a.field_bar + c * N + i) : T(0);
 
     const bool use_seg = (a.num_inner > 0) && (a.hist == nullptr);
-    auto state_ptr = [&](int k) -> const T* {  // where y_k lives
-        if (!use_seg) return a.hist + (long long)k * D * N;
-        return ws.seg + (long long)(k % a.num_inner) * D * N;
-    };
-    auto emit_p = [&](int k) {  // p_bar[k] is complete
+    // Row offsets are carried from step to step (one 64-bit subtraction each) instead of being rebuilt from k:
+    // the reverse sweep of a cheap right-hand side is otherwise issue-bound on address arithmetic.
+    const long long DN = (long long)D * N, PN = (long long)DM::P * N, NPN = (long long)DM::NP * N;
+    const long long PW = (long long)DM::P * ws.W;
+    auto emit_p = [&](int k, long long wrow) {  // p_bar[k] is complete; wrow = k * P * W + warp
         if (!a.p_bar) return;
 #pragma unroll
         for (int c = 0; c < DM::P; ++c) {
             if (a.p_shared) {
                 const T s = warp_sum(valid ? pb_next[c] : T(0));
-                if (lane == 0) ws.p[((long long)k * DM::P + c) * ws.W + warp] = s;
+                if (lane == 0) ws.p[wrow + c * ws.W] = s;
             } else if (valid) {
                 a.p_bar[((long long)k * DM::P + c) * N + i] = pb_next[c];
             }
         }
     };
-    // direct cotangents of y_k: history row, profile/field outputs evaluated at (y_k, p[k])
-    auto direct = [&](int k, const T* yk, const T* pk) {
+    // direct cotangents of y_k: history row (hb, already loaded), profile/field outputs evaluated at (y_k, p[k])
+    auto direct = [&](const T* hb, long long oprof, const T* yk, const T* pk) {
         if (a.hist_bar)
 #pragma unroll
-            for (int c = 0; c < D; ++c) lam[c] += __ldg(a.hist_bar + ((long long)k * D + c) * N + i);
+            for (int c = 0; c < D; ++c) lam[c] += hb[c];
         if constexpr (HAS_OUT) {
 #pragma unroll
-            for (int c = 0; c < DM::NP; ++c)
-                vp[c] = a.prof_bar ? __ldg(a.prof_bar + ((long long)k * DM::NP + c) * N + i) : T(0);
+            for (int c = 0; c < DM::NP; ++c) vp[c] = a.prof_bar ? __ldg(a.prof_bar + oprof + c * N) : T(0);
             R::out_vjp(yk, pk, th, vp, vf, lam, pb_next, tb);
         }
     };
+    auto load_hist_bar = [&](long long oy, T* hb) {
+        if (a.hist_bar)
+#pragma unroll
+            for (int c = 0; c < D; ++c) hb[c] = __ldg(a.hist_bar + oy + c * N);
+    };
+    auto params_at = [&](int k, long long op, T* p) {  // p[k]: row k of [nt][P] (shared) or [nt][P][N]
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) p[c] = a.p_shared ? __ldg(a.p + k * DM::P + c) : __ldg(a.p + op + c * N);
+    };
+
+    // Sums over the batch (cotangents of shared h and shared p).  Explicit sweeps, whose steps are a few hundred
+    // instructions, do not reduce with shuffles every step (5 shuffle pairs + 5 adds per quantity): each warp parks
+    // its lanes' values in a shared-memory tile, one row per (step, quantity), and once the tile holds 32 rows lane r
+    // adds up row r and writes that warp partial.  Same partial-sum layout as the shuffle path, fixed order, no atomics.
+    constexpr bool STAGED = !IMPL;
+    constexpr int kRow = 33;  // row pitch: lane r reading row r at a fixed column touches distinct banks
+    __shared__ T red_tile[STAGED ? (lb_threads<R, S, T, IMPL>() / 32) * 32 * kRow : 1];
+    T* tile = red_tile + (STAGED ? (threadIdx.x >> 5) * 32 * kRow : 0);
+    const bool h_red = a.h_bar && a.h_shared, p_red = a.p_bar && a.p_shared && DM::P > 0;
+    const int nq = (h_red ? 1 : 0) + (p_red ? DM::P : 0);   // rows per step
+    const int kc = nq ? 32 / nq : 0;                        // steps per tile
+    int fill = 0, kstart = 0;
+    auto flush = [&]() {  // rows 0 .. fill * nq - 1 hold steps kstart, kstart - 1, ...
+        __syncwarp();
+        if (lane < fill * nq) {
+            const T* row = tile + lane * kRow;
+            T s0 = row[0], s1 = row[1];
+#pragma unroll
+            for (int j = 2; j < 32; j += 2) {
+                s0 += row[j];
+                s1 += row[j + 1];
+            }
+            const int kk = lane / nq, q = lane - kk * nq, k = kstart - kk;
+            if (h_red && q == 0)
+                ws.h[(long long)k * ws.W + warp] = s0 + s1;
+            else
+                ws.p[((long long)(k + 1) * DM::P + (q - (h_red ? 1 : 0))) * ws.W + warp] = s0 + s1;
+        }
+        __syncwarp();
+        fill = 0;
+    };
 
     // ---- terminal condition: lam = dL/dy_n
+    T hbv[D];
 #pragma unroll
     for (int c = 0; c < D; ++c) lam[c] = a.final_bar ? __ldg(a.final_bar + c * N + i) : T(0);
-    load_params<R>(a, n, i, phi);
+    params_at(n, (long long)n * PN + i, phi);
     if constexpr (HAS_OUT) {
-        const T* src = use_seg ? a.ckpt + (long long)(n / a.num_inner) * D * N : a.hist + (long long)n * D * N;
+        const T* src = use_seg ? a.ckpt + (long long)(n / a.num_inner) * DN : a.hist + (long long)n * DN;
 #pragma unroll
         for (int c = 0; c < D; ++c) y[c] = __ldg(src + c * N + i);
     }
-    direct(n, y, phi);
+    load_hist_bar((long long)n * DN + i, hbv);
+    direct(hbv, (long long)n * NPN + i, y, phi);
 
     const int ni = use_seg ? a.num_inner : n;
     const int nseg = use_seg ? n / a.num_inner : 1;
+    // offsets of row k = n - 1, the first step of the sweep; every iteration moves them one row down
+    long long oy = (long long)(n - 1) * DN + i;      // hist / hist_bar row
+    long long op = (long long)(n - 1) * PN + i;      // p row
+    long long oprof = (long long)(n - 1) * NPN + i;  // prof_bar row
+    long long oh = (long long)(n - 1) * N + i;       // h row (per trajectory)
+    long long wrow_p = (long long)n * PW + warp;     // ws.p row of p_bar[k + 1]
+    long long wrow_h = (long long)(n - 1) * ws.W + warp;
     for (int o = nseg - 1; o >= 0; --o) {
         const int lo = o * ni;
         if (use_seg) {
@@ -640,40 +719,52 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         // into registers for explicit methods, as an L1 prefetch for implicit ones (no registers to spare there)
         constexpr bool PRELOAD = !IMPL;
         T ynext[D];
+        // row of y_k: the stored history, or this segment's recomputed rows (row k - lo of ws.seg)
+        const T* yrow = (use_seg ? ws.seg + (long long)(ni - 1) * DN : a.hist + (long long)(lo + ni - 1) * DN) + i;
         if constexpr (PRELOAD) {
-            const T* src = state_ptr(lo + ni - 1);
 #pragma unroll
-            for (int c = 0; c < D; ++c) ynext[c] = use_seg ? src[c * N + i] : __ldg(src + c * N + i);
+            for (int c = 0; c < D; ++c) ynext[c] = use_seg ? yrow[c * N] : __ldg(yrow + c * N);
         }
         for (int k = lo + ni - 1; k >= lo; --k) {
+            if constexpr (IMPL) {
+                // implicit steps are long and register-starved: rebuild the offsets here rather than keep seven
+                // 64-bit values alive across the Newton solve and the elimination
+                yrow = (use_seg ? ws.seg + (long long)(k - lo) * DN : a.hist + (long long)k * DN) + i;
+                oy = (long long)k * DN + i;
+                op = (long long)k * PN + i;
+                oprof = (long long)k * NPN + i;
+                oh = (long long)k * N + i;
+                wrow_p = (long long)(k + 1) * PW + warp;
+                wrow_h = (long long)k * ws.W + warp;
+            }
             if constexpr (PRELOAD) {
 #pragma unroll
                 for (int c = 0; c < D; ++c) y[c] = ynext[c];
+                load_hist_bar(oy, hbv);  // consumed at the end of this iteration
             } else {
-                const T* src = state_ptr(k);
 #pragma unroll
-                for (int c = 0; c < D; ++c) y[c] = use_seg ? src[c * N + i] : __ldg(src + c * N + i);
+                for (int c = 0; c < D; ++c) y[c] = use_seg ? yrow[c * N] : __ldg(yrow + c * N);
             }
             if (k > lo) {  // next iteration's inputs (step k-1)
-                const T* nsrc = state_ptr(k - 1);
+                const T* nrow = yrow - DN;
                 if constexpr (PRELOAD) {
 #pragma unroll
-                    for (int c = 0; c < D; ++c) ynext[c] = use_seg ? nsrc[c * N + i] : __ldg(nsrc + c * N + i);
+                    for (int c = 0; c < D; ++c) ynext[c] = use_seg ? nrow[c * N] : __ldg(nrow + c * N);
                 } else {
 #pragma unroll
-                    for (int c = 0; c < D; ++c) prefetch_l1(nsrc + c * N + i);
+                    for (int c = 0; c < D; ++c) prefetch_l1(nrow + c * N);
+                    if (a.hist_bar)
+#pragma unroll
+                        for (int c = 0; c < D; ++c) prefetch_l1(a.hist_bar + (oy - DN) + c * N);
                 }
                 if (!a.p_shared)
 #pragma unroll
-                    for (int c = 0; c < DM::P; ++c) prefetch_l1(a.p + ((long long)(k - 1) * DM::P + c) * N + i);
-                if (!a.h_shared) prefetch_l1(a.h + (long long)(k - 1) * N + i);
-                if (a.hist_bar)
-#pragma unroll
-                    for (int c = 0; c < D; ++c) prefetch_l1(a.hist_bar + ((long long)(k - 1) * D + c) * N + i);
+                    for (int c = 0; c < DM::P; ++c) prefetch_l1(a.p + (op - PN) + c * N);
+                if (!a.h_shared) prefetch_l1(a.h + (oh - N));
                 if constexpr (DM::NP > 0) {
                     if (a.prof_bar)
 #pragma unroll
-                        for (int c = 0; c < DM::NP; ++c) prefetch_l1(a.prof_bar + ((long long)(k - 1) * DM::NP + c) * N + i);
+                        for (int c = 0; c < DM::NP; ++c) prefetch_l1(a.prof_bar + (oprof - NPN) + c * N);
                 }
                 if constexpr (IMPL) {
                     if (a.stages && !use_seg)
@@ -681,31 +772,64 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
                         for (int c = 0; c < S * D; ++c) prefetch_l1(a.stages + ((long long)(k - 1) * S * D + c) * N + i);
                 }
             }
-            const T h = ld_in(a.h, k, N, i, a.h_shared);
-            load_params<R>(a, k, i, plo);
+            const T h = a.h_shared ? __ldg(a.h + k) : __ldg(a.h + oh);
+            params_at(k, op, plo);
             stage_params<R, T, S>(a.tab, plo, phi, ps);
             T hb;
             adjoint_step<R, T, S, IMPL>(a, y, h, ps, th, lam, hb, pb_lo, pb_hi, tb, smem, status, iters,
                                         (IMPL && a.stages && !use_seg) ? a.stages + (long long)k * S * D * N : nullptr, N, i);
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) pb_next[c] += pb_hi[c];
-            emit_p(k + 1);
+            if constexpr (STAGED) {
+                // shared-input cotangents of this step go to the warp's tile, one row per quantity; per-trajectory
+                // ones are stored directly
+                if (fill == 0) kstart = k;
+                T* row = tile + fill * nq * kRow + lane;
+                if (h_red) {
+                    *row = valid ? hb : T(0);
+                    row += kRow;
+                } else if (a.h_bar && valid) {
+                    a.h_bar[oh] = hb;
+                }
+                if (p_red) {
 #pragma unroll
-            for (int c = 0; c < DM::P; ++c) pb_next[c] = pb_lo[c];
-            if (a.h_bar) {
-                if (a.h_shared) {
-                    const T s = warp_sum(valid ? hb : T(0));
-                    if (lane == 0) ws.h[(long long)k * ws.W + warp] = s;
-                } else if (valid) {
-                    a.h_bar[(long long)k * N + i] = hb;
+                    for (int c = 0; c < DM::P; ++c) row[c * kRow] = valid ? pb_next[c] : T(0);
+                } else {
+                    emit_p(k + 1, wrow_p);
+                }
+                if (++fill == kc) flush();
+            } else {
+                emit_p(k + 1, wrow_p);
+                if (a.h_bar) {
+                    if (a.h_shared) {
+                        const T s = warp_sum(valid ? hb : T(0));
+                        if (lane == 0) ws.h[wrow_h] = s;
+                    } else if (valid) {
+                        a.h_bar[oh] = hb;
+                    }
                 }
             }
-            direct(k, y, plo);
+#pragma unroll
+            for (int c = 0; c < DM::P; ++c) pb_next[c] = pb_lo[c];
+            if constexpr (!PRELOAD) load_hist_bar(oy, hbv);
+            direct(hbv, oprof, y, plo);
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) phi[c] = plo[c];
+            if constexpr (!IMPL) {
+                yrow -= DN;
+                oy -= DN;
+                op -= PN;
+                oprof -= NPN;
+                oh -= N;
+                wrow_p -= PW;
+                wrow_h -= ws.W;
+            }
         }
     }
-    emit_p(0);
+    if constexpr (STAGED) {
+        if (fill > 0) flush();
+    }
+    emit_p(0, warp);
     if (a.y0_bar && valid)
 #pragma unroll
         for (int c = 0; c < D; ++c) a.y0_bar[c * N + i] = lam[c];
