@@ -33,8 +33,11 @@ constexpr bool use_reg_solve() {
 #ifndef OZ_MB_IMPL_ADJ
 #define OZ_MB_IMPL_ADJ 4
 #endif
-#ifndef OZ_MB_EXPL_ADJ
-#define OZ_MB_EXPL_ADJ 5
+#ifndef OZ_MB_EXPL_ADJ_F64   /* explicit reverse sweep, fp64: 128 registers (5 blocks = 96 registers spills the preloads) */
+#define OZ_MB_EXPL_ADJ_F64 4
+#endif
+#ifndef OZ_MB_EXPL_ADJ_F32
+#define OZ_MB_EXPL_ADJ_F32 6
 #endif
 template <class R, int S, typename T, bool IMPL>
 constexpr int lb_threads() {
@@ -43,7 +46,7 @@ constexpr int lb_threads() {
 template <class R, int S, typename T, bool IMPL, bool ADJ>
 constexpr int lb_blocks() {
     if (IMPL && use_reg_solve<R, S, T>()) return ADJ ? OZ_MB_IMPL_ADJ : OZ_MB_IMPL_FWD;
-    if (!IMPL && ADJ) return OZ_MB_EXPL_ADJ;
+    if (!IMPL && ADJ) return sizeof(T) == 8 ? OZ_MB_EXPL_ADJ_F64 : OZ_MB_EXPL_ADJ_F32;
     return 1;
 }
 
@@ -617,15 +620,15 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         }
     };
     // direct cotangents of y_k: history row (hb, already loaded), profile/field outputs evaluated at (y_k, p[k])
-    auto direct = [&](const T* hb, long long oprof, const T* yk, const T* pk) {
+    auto load_prof_bar = [&](long long oprof, T* v) {
+#pragma unroll
+        for (int c = 0; c < DM::NP; ++c) v[c] = a.prof_bar ? __ldg(a.prof_bar + oprof + c * N) : T(0);
+    };
+    auto direct = [&](const T* hb, const T* yk, const T* pk) {  // vp holds prof_bar[k]
         if (a.hist_bar)
 #pragma unroll
             for (int c = 0; c < D; ++c) lam[c] += hb[c];
-        if constexpr (HAS_OUT) {
-#pragma unroll
-            for (int c = 0; c < DM::NP; ++c) vp[c] = a.prof_bar ? __ldg(a.prof_bar + oprof + c * N) : T(0);
-            R::out_vjp(yk, pk, th, vp, vf, lam, pb_next, tb);
-        }
+        if constexpr (HAS_OUT) R::out_vjp(yk, pk, th, vp, vf, lam, pb_next, tb);
     };
     auto load_hist_bar = [&](long long oy, T* hb) {
         if (a.hist_bar)
@@ -680,7 +683,8 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         for (int c = 0; c < D; ++c) y[c] = __ldg(src + c * N + i);
     }
     load_hist_bar((long long)n * DN + i, hbv);
-    direct(hbv, (long long)n * NPN + i, y, phi);
+    load_prof_bar((long long)n * NPN + i, vp);
+    direct(hbv, y, phi);
 
     const int ni = use_seg ? a.num_inner : n;
     const int nseg = use_seg ? n / a.num_inner : 1;
@@ -691,6 +695,17 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
     long long oh = (long long)(n - 1) * N + i;       // h row (per trajectory)
     long long wrow_p = (long long)n * PW + warp;     // ws.p row of p_bar[k + 1]
     long long wrow_h = (long long)(n - 1) * ws.W + warp;
+    // Explicit sweeps load every per-step input one iteration before it is used (registers to spare, and a step is
+    // too short for five warps per scheduler to cover an L2 round trip): y_k, h_k, p_k here, the cotangent rows
+    // of step k at the top of iteration k for use at its end.
+    constexpr bool PRELOAD = !IMPL;
+    T hnx = T(0), pnx[DM::P1];
+    if constexpr (PRELOAD) {
+        if (n > 0) {
+            hnx = a.h_shared ? __ldg(a.h + (n - 1)) : __ldg(a.h + oh);
+            params_at(n - 1, op, pnx);
+        }
+    }
     for (int o = nseg - 1; o >= 0; --o) {
         const int lo = o * ni;
         if (use_seg) {
@@ -717,7 +732,6 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         }
         // y_k is fetched one iteration ahead so that its load latency overlaps the previous step's arithmetic:
         // into registers for explicit methods, as an L1 prefetch for implicit ones (no registers to spare there)
-        constexpr bool PRELOAD = !IMPL;
         T ynext[D];
         // row of y_k: the stored history, or this segment's recomputed rows (row k - lo of ws.seg)
         const T* yrow = (use_seg ? ws.seg + (long long)(ni - 1) * DN : a.hist + (long long)(lo + ni - 1) * DN) + i;
@@ -740,7 +754,8 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
             if constexpr (PRELOAD) {
 #pragma unroll
                 for (int c = 0; c < D; ++c) y[c] = ynext[c];
-                load_hist_bar(oy, hbv);  // consumed at the end of this iteration
+                load_hist_bar(oy, hbv);  // both consumed at the end of this iteration
+                if constexpr (DM::NP > 0) load_prof_bar(oprof, vp);
             } else {
 #pragma unroll
                 for (int c = 0; c < D; ++c) y[c] = use_seg ? yrow[c * N] : __ldg(yrow + c * N);
@@ -757,14 +772,16 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
 #pragma unroll
                         for (int c = 0; c < D; ++c) prefetch_l1(a.hist_bar + (oy - DN) + c * N);
                 }
-                if (!a.p_shared)
+                if constexpr (!PRELOAD) {
+                    if (!a.p_shared)
 #pragma unroll
-                    for (int c = 0; c < DM::P; ++c) prefetch_l1(a.p + (op - PN) + c * N);
-                if (!a.h_shared) prefetch_l1(a.h + (oh - N));
-                if constexpr (DM::NP > 0) {
-                    if (a.prof_bar)
+                        for (int c = 0; c < DM::P; ++c) prefetch_l1(a.p + (op - PN) + c * N);
+                    if (!a.h_shared) prefetch_l1(a.h + (oh - N));
+                    if constexpr (DM::NP > 0) {
+                        if (a.prof_bar)
 #pragma unroll
-                        for (int c = 0; c < DM::NP; ++c) prefetch_l1(a.prof_bar + (oprof - NPN) + c * N);
+                            for (int c = 0; c < DM::NP; ++c) prefetch_l1(a.prof_bar + (oprof - NPN) + c * N);
+                    }
                 }
                 if constexpr (IMPL) {
                     if (a.stages && !use_seg)
@@ -772,8 +789,19 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
                         for (int c = 0; c < S * D; ++c) prefetch_l1(a.stages + ((long long)(k - 1) * S * D + c) * N + i);
                 }
             }
-            const T h = a.h_shared ? __ldg(a.h + k) : __ldg(a.h + oh);
-            params_at(k, op, plo);
+            T h;
+            if constexpr (PRELOAD) {
+                h = hnx;
+#pragma unroll
+                for (int c = 0; c < DM::P; ++c) plo[c] = pnx[c];
+                if (k > 0) {  // rows of step k - 1 (also across a segment boundary: h and p are global rows)
+                    hnx = a.h_shared ? __ldg(a.h + (k - 1)) : __ldg(a.h + (oh - N));
+                    params_at(k - 1, op - PN, pnx);
+                }
+            } else {
+                h = a.h_shared ? __ldg(a.h + k) : __ldg(a.h + oh);
+                params_at(k, op, plo);
+            }
             stage_params<R, T, S>(a.tab, plo, phi, ps);
             T hb;
             adjoint_step<R, T, S, IMPL>(a, y, h, ps, th, lam, hb, pb_lo, pb_hi, tb, smem, status, iters,
@@ -811,8 +839,11 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
             }
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) pb_next[c] = pb_lo[c];
-            if constexpr (!PRELOAD) load_hist_bar(oy, hbv);
-            direct(hbv, oprof, y, plo);
+            if constexpr (!PRELOAD) {
+                load_hist_bar(oy, hbv);
+                if constexpr (DM::NP > 0) load_prof_bar(oprof, vp);
+            }
+            direct(hbv, y, plo);
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) phi[c] = plo[c];
             if constexpr (!IMPL) {

@@ -1,5 +1,8 @@
+#!/bin/bash
+# A/B of library builds on one workload:  tools/ab_libs.sh <workload> lib1.so lib2.so ...   (each run twice, interleaved)
+wl=$1; shift
 for i in 1 2; do
-for lib in build/liboz_old.so ozone_b200/liboz_b200.so; do
-  OZONE_B200_LIB=$PWD/$lib python bench.py --steps 20 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); r=d['roofline']; print('$lib', d['value'], r['kernel'], r['avg_launch_ms'], r['other_kernel']['kernel'], r['other_kernel']['avg_launch_ms'])"
+for lib in "$@"; do
+  OZONE_B200_LIB=$PWD/$lib python bench.py --workload $wl --steps 20 --warmup 3 --no-cpu-baseline 2>&1 | tail -1 | python -c "
+import json,sys; d=json.loads(sys.stdin.read()); r=d['roofline']; print('$lib', '%.4g' % d['value'], r['kernel'], '%.4f' % r['avg_launch_ms'], r['other_kernel']['kernel'], '%.4f' % r['other_kernel']['avg_launch_ms'])"
 done; done
