@@ -119,12 +119,18 @@ struct SmemSystem {
 // ---------------------------------------------------------------------------------------------
 // Register-resident dense solve for small systems (M <= ~9): Gaussian elimination of the augmented
 // system [a | b] with every index static, so the matrix never leaves the register file (the shared-
-// memory LU above is bound by LDS/STS traffic: 3 shared accesses per DFMA).  Threshold partial
-// pivoting: rows are exchanged only when |a_kk| < 0.1 max_r |a_rk| (growth then stays bounded by
-// 11^(M-1) in theory, ~O(10) in practice), which keeps the common path free of data-dependent
-// register shuffling; the exchange itself is a chain of statically indexed, predicated row swaps.
-// The decision depends only on the thread's own data, so a trajectory's result does not depend on
-// its warp neighbours.  On return b holds the solution; false = a zero / non-finite pivot was met.
+// memory LU above is bound by LDS/STS traffic: 3 shared accesses per DFMA).
+//
+// Threshold partial pivoting: rows are exchanged only when |a_kk| < 0.1 max_r |a_rk| (growth then stays
+// bounded by 11^(M-1) in theory, ~O(10) in practice).  The Newton matrices I - h A (x) J almost never need
+// an exchange, so the register path contains none: per column it only TESTS the diagonal (one compare per
+// candidate row, no selects, no row copies -- an in-register exchange made the compiler pre-copy rows on
+// the common path, 21 % of all issued instructions in the Gauss-Legendre forward sweep).  The first column
+// that fails the test hands the partly eliminated system to finish_with_pivoting(), a cold out-of-line
+// routine working in local memory with the same pivot rule.  The decision depends only on the thread's own
+// data, so a trajectory's result does not depend on its warp neighbours.  On return b holds the solution;
+// false = a zero / non-finite pivot was met.
+
 // Reciprocal of a pivot: hardware seed (rcp.approx, ~2^-23) + two Newton steps -> full double precision without the
 // special-case branches of an IEEE division (pivots here are O(1); a zero / non-finite pivot is flagged by the caller).
 OZ_D double fast_rcp(double x) {
@@ -136,23 +142,66 @@ OZ_D double fast_rcp(double x) {
 }
 OZ_D float fast_rcp(float x) { return 1.0f / x; }
 
-// (column K is a template parameter: plain "#pragma unroll" on the column loop is not honoured by nvcc
-// beyond M = 4, which turns every index dynamic and sends the matrix to local memory)
-template <typename T, int M, int K>
-struct RegElim {
-    OZ_D static void run(T (&a)[M][M], T (&b)[M], bool& ok) {
-        if constexpr (K < M - 1) {
-            T best = fabs(a[K][K]);
-            int pr = K;
-#pragma unroll
-            for (int r = K + 1; r < M; ++r) {
-                const T cand = fabs(a[r][K]);
+// Columns 0 .. k0-1 of the row-major M x M system are already eliminated (their diagonals hold reciprocals).
+// Finishes the elimination from column k0 with threshold partial pivoting and back-substitutes.
+template <typename T, int M>
+__device__ __noinline__ bool finish_with_pivoting(T* a, T* b, int k0) {
+    bool ok = true;
+    for (int k = k0; k < M; ++k) {
+        if (k < M - 1) {
+            int pr = k;
+            T best = fabs(a[k * M + k]);
+            for (int r = k + 1; r < M; ++r) {
+                const T cand = fabs(a[r * M + k]);
                 if (cand > best) {
                     best = cand;
                     pr = r;
                 }
             }
-            if (fabs(a[K][K]) < T(0.1) * best) swap_rows<K + 1>(a, b, pr);
+            if (pr != k && T(10) * fabs(a[k * M + k]) < best) {
+                for (int c = k; c < M; ++c) {
+                    const T t = a[k * M + c];
+                    a[k * M + c] = a[pr * M + c];
+                    a[pr * M + c] = t;
+                }
+                const T t = b[k];
+                b[k] = b[pr];
+                b[pr] = t;
+            }
+        }
+        const T piv = a[k * M + k];
+        if (!(fabs(piv) > T(0)) || !isfinite(piv)) ok = false;
+        const T inv = fast_rcp(piv);
+        a[k * M + k] = inv;
+        for (int r = k + 1; r < M; ++r) {
+            const T l = a[r * M + k] * inv;
+            for (int c = k + 1; c < M; ++c) a[r * M + c] -= l * a[k * M + c];
+            b[r] -= l * b[k];
+        }
+    }
+    for (int r = M - 1; r >= 0; --r) {
+        T acc = b[r];
+        for (int c = r + 1; c < M; ++c) acc -= a[r * M + c] * b[c];
+        b[r] = acc * a[r * M + r];
+    }
+    return ok;
+}
+
+// (column K is a template parameter: plain "#pragma unroll" on the column loop is not honoured by nvcc
+// beyond M = 4, which turns every index dynamic and sends the matrix to local memory)
+template <typename T, int M, int K>
+struct RegElim {
+    // bad: first column whose diagonal is below a tenth of an entry under it (elimination stops there), else -1
+    OZ_D static void run(T (&a)[M][M], T (&b)[M], bool& ok, int& bad) {
+        if constexpr (K < M - 1) {
+            const T lim = T(10) * fabs(a[K][K]);
+            bool small = false;
+#pragma unroll
+            for (int r = K + 1; r < M; ++r) small = small || (fabs(a[r][K]) > lim);
+            if (small) {
+                bad = K;
+                return;
+            }
         }
         const T piv = a[K][K];
         if (!(fabs(piv) > T(0)) || !isfinite(piv)) ok = false;
@@ -165,24 +214,7 @@ struct RegElim {
             for (int c = K + 1; c < M; ++c) a[r][c] -= l * a[K][c];
             b[r] -= l * b[K];
         }
-        if constexpr (K + 1 < M) RegElim<T, M, K + 1>::run(a, b, ok);
-    }
-    template <int R>
-    OZ_D static void swap_rows(T (&a)[M][M], T (&b)[M], int pr) {
-        if constexpr (R < M) {
-            if (pr == R) {
-#pragma unroll
-                for (int c = K; c < M; ++c) {
-                    const T t = a[K][c];
-                    a[K][c] = a[R][c];
-                    a[R][c] = t;
-                }
-                const T t = b[K];
-                b[K] = b[R];
-                b[R] = t;
-            }
-            swap_rows<R + 1>(a, b, pr);
-        }
+        if constexpr (K + 1 < M) RegElim<T, M, K + 1>::run(a, b, ok, bad);
     }
 };
 
@@ -200,7 +232,21 @@ struct RegBack {
 template <typename T, int M>
 OZ_D bool reg_solve(T (&a)[M][M], T (&b)[M]) {
     bool ok = true;
-    RegElim<T, M, 0>::run(a, b, ok);
+    int bad = -1;
+    RegElim<T, M, 0>::run(a, b, ok, bad);
+    if (bad >= 0) {  // rare: continue in local memory with row exchanges
+        T ta[M * M], tb[M];
+#pragma unroll
+        for (int r = 0; r < M; ++r) {
+#pragma unroll
+            for (int c = 0; c < M; ++c) ta[r * M + c] = a[r][c];
+            tb[r] = b[r];
+        }
+        ok = finish_with_pivoting<T, M>(ta, tb, bad) && ok;
+#pragma unroll
+        for (int r = 0; r < M; ++r) b[r] = tb[r];
+        return ok;
+    }
     RegBack<T, M, M - 1>::run(a, b);
     return ok;
 }

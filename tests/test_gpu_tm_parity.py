@@ -106,6 +106,25 @@ def test_config2_adjoint_from_cached_stages_equals_resolve(method):
         assert relerr(np_(g1[k]), np_(g2[k])) < 1e-13, k      # same stage values; only FMA contraction may differ
 
 
+@pytest.mark.parametrize('method,h', [('GaussLegendre2', 2.0), ('BackwardEuler', 1.0)])
+def test_newton_matrix_that_needs_a_row_exchange(method, h):
+    """With x1 = 0 and h a_11 = 1 the first Newton matrix I - h A (x) J has an exactly zero leading diagonal entry:
+    the register elimination must hand over to its pivoting routine (the oracle solves with LAPACK's partial
+    pivoting).  Neighbouring trajectories start elsewhere and stay on the exchange-free path.  (Larger stage
+    counts would need h >= 4 here, where Newton no longer converges on either side; their 4 x 4 and 6 x 6 systems
+    are exercised by the linear problem in test_gpu_traced_callbacks.py.)"""
+    N = 37
+    y0 = np.zeros((3, N))
+    y0[0] = 0.5
+    y0[1, 1::2] = np.linspace(0.2, 0.9, len(y0[1, 1::2]))           # every other trajectory: no exchange needed
+    c = dict(rhs='van_der_pol', y0=y0, h=np.full(3, h), p=np.full((4, 1, N), 0.1) + np.linspace(0, 0.2, N), th=None)
+    spec, fwd, ref, g, gref = run_pair(c, method, tol=1e-13)
+    assert int(fwd['status'].max()) == 0
+    assert relerr(np_(fwd['hist']), ref['history']) < 1e-10
+    for k in ('y0', 'h', 'p'):
+        assert relerr(np_(g[k]).reshape(gref[k].shape), gref[k]) < 1e-9, k
+
+
 def test_config2_fp32():
     _compare(cases.van_der_pol_inputs(N=64), 'GaussLegendre4', torch.float32, tol=1e-5, fwd_tol=2e-5, grad_tol=2e-4)
 

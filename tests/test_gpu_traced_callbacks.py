@@ -226,3 +226,41 @@ def test_repeated_solves_reuse_one_plugin_registration():
         ids.add(p.integrator.spec.traced.plugin_id(4, False, True, 0))
         assert float(out.final_states['y']) == pytest.approx(np.exp(-1.0), rel=1e-6)
     assert len(ids) == 1
+
+
+@pytest.mark.parametrize('method_name', ['BackwardEuler', 'GaussLegendre4', 'GaussLegendre6'])
+def test_linear_system_whose_newton_matrix_needs_row_exchanges(method_name):
+    """y' = J y with J_00 = 1 / (h a_11): the leading entry of the Newton matrix I - h A (x) J vanishes while the
+    entries under it are O(1), so the register elimination has to leave its exchange-free path.  The answer is
+    the stability function applied n times, computed here with LAPACK (np.linalg.solve)."""
+    from ozone_b200 import methods
+    from ozone_b200.glms import get_integration_method
+    m = get_integration_method(method_name)
+    A, B = np.asarray(m.A, dtype=np.float64), np.asarray(m.B, dtype=np.float64).reshape(-1)
+    s, h, n = A.shape[0], 0.1, 3
+    J = np.array([[1.0 / (h * A[0, 0]), 1.0], [1.0, 0.0]])
+
+    def f(v: ozone.ODEVars):
+        a, b = v.states['a'], v.states['b']
+        v.d_states['a'] = J[0, 0] * a + J[0, 1] * b
+        v.d_states['b'] = J[1, 0] * a + J[1, 1] * b
+
+    a_0, b_0, h_vec = var([1.0]), var([0.5]), var(np.full(n, h))
+    p = ozone.ODEProblem(getattr(methods, method_name)(), TimeMarching())
+    p.add_state('a', initial_condition=a_0, store_final=True)
+    p.add_state('b', initial_condition=b_0, store_final=True)
+    p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h_vec))
+    p.set_function(f)
+    out = p.solve()
+    total = out.final_states['a'].sum() + 2.0 * out.final_states['b'].sum()
+    # one step: (I - h A (x) J) Y = 1 (x) y ;  y+ = y + h (B (x) J) Y  =>  y+ = R y
+    M = np.eye(2 * s) - h * np.kron(A, J)
+    R = np.eye(2) + h * np.kron(B[None, :], J) @ np.linalg.solve(M, np.kron(np.ones((s, 1)), np.eye(2)))
+    assert abs(M[0, 0]) < 1e-12 < 0.1 * np.abs(M[1:, 0]).max()        # the situation this test is about
+    Rn = np.linalg.matrix_power(R, n)
+    yn = Rn @ np.array([1.0, 0.5])
+    assert float(out.final_states['a']) == pytest.approx(yn[0], rel=1e-10)
+    assert float(out.final_states['b']) == pytest.approx(yn[1], rel=1e-10)
+    ga, gb = torch.autograd.grad(total, [a_0, b_0])
+    gref = Rn.T @ np.array([1.0, 2.0])
+    assert float(ga) == pytest.approx(gref[0], rel=1e-9) and float(gb) == pytest.approx(gref[1], rel=1e-9)
