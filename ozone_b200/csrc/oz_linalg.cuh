@@ -125,9 +125,9 @@ struct SmemSystem {
 // bounded by 11^(M-1) in theory, ~O(10) in practice).  The Newton matrices I - h A (x) J almost never need
 // an exchange, so the register path contains none: per column it only TESTS the diagonal (one compare per
 // candidate row, no selects, no row copies -- an in-register exchange made the compiler pre-copy rows on
-// the common path, 21 % of all issued instructions in the Gauss-Legendre forward sweep).  The first column
-// that fails the test hands the partly eliminated system to finish_with_pivoting(), a cold out-of-line
-// routine working in local memory with the same pivot rule.  The decision depends only on the thread's own
+// the common path, 21 % of all issued instructions in the Gauss-Legendre forward sweep).  When a column
+// fails the test the caller assembles the system again in local memory and solves it there with
+// finish_with_pivoting(), a cold out-of-line routine with the same pivot rule.  The decision depends only on the thread's own
 // data, so a trajectory's result does not depend on its warp neighbours.  On return b holds the solution;
 // false = a zero / non-finite pivot was met.
 
@@ -141,6 +141,9 @@ OZ_D double fast_rcp(double x) {
     return r;
 }
 OZ_D float fast_rcp(float x) { return 1.0f / x; }
+
+OZ_D int mag_bits(double x) { return __double2hiint(x) & 0x7fffffff; }
+OZ_D int mag_bits(float x) { return __float_as_int(x) & 0x7fffffff; }
 
 // Columns 0 .. k0-1 of the row-major M x M system are already eliminated (their diagonals hold reciprocals).
 // Finishes the elimination from column k0 with threshold partial pivoting and back-substitutes.
@@ -194,10 +197,12 @@ struct RegElim {
     // bad: first column whose diagonal is below a tenth of an entry under it (elimination stops there), else -1
     OZ_D static void run(T (&a)[M][M], T (&b)[M], bool& ok, int& bad) {
         if constexpr (K < M - 1) {
-            const T lim = T(10) * fabs(a[K][K]);
+            // magnitudes are compared through their leading 32 bits (monotone for non-negative IEEE numbers, NaN
+            // and infinity rank highest): integer compares off the fp64 pipe; the threshold is a heuristic anyway
+            const int lim = mag_bits(T(10) * fabs(a[K][K]));
             bool small = false;
 #pragma unroll
-            for (int r = K + 1; r < M; ++r) small = small || (fabs(a[r][K]) > lim);
+            for (int r = K + 1; r < M; ++r) small = small || (mag_bits(a[r][K]) > lim);
             if (small) {
                 bad = K;
                 return;
@@ -229,26 +234,19 @@ struct RegBack {
     }
 };
 
+// Returns 0 (solved, b = solution), 1 (a zero / non-finite pivot was met) or 2: some column failed the threshold
+// test and nothing useful is left in a / b.  On 2 the caller builds the system again into row-major local arrays
+// and calls finish_with_pivoting(ta, tb, 0).  (Rebuilding, rather than handing over the partly eliminated
+// registers, keeps the cold path from needing any register state of the hot one: with a hand-over the compiler
+// hoisted the row copies for it above the branch.)
 template <typename T, int M>
-OZ_D bool reg_solve(T (&a)[M][M], T (&b)[M]) {
+OZ_D int reg_solve(T (&a)[M][M], T (&b)[M]) {
     bool ok = true;
     int bad = -1;
     RegElim<T, M, 0>::run(a, b, ok, bad);
-    if (bad >= 0) {  // rare: continue in local memory with row exchanges
-        T ta[M * M], tb[M];
-#pragma unroll
-        for (int r = 0; r < M; ++r) {
-#pragma unroll
-            for (int c = 0; c < M; ++c) ta[r * M + c] = a[r][c];
-            tb[r] = b[r];
-        }
-        ok = finish_with_pivoting<T, M>(ta, tb, bad) && ok;
-#pragma unroll
-        for (int r = 0; r < M; ++r) b[r] = tb[r];
-        return ok;
-    }
+    if (bad >= 0) return 2;
     RegBack<T, M, M - 1>::run(a, b);
-    return ok;
+    return ok ? 0 : 1;
 }
 
 }  // namespace oz

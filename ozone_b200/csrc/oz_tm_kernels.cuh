@@ -155,29 +155,46 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 break;
             }
             T Ma[MA][MA], b[MA], Jq[S][R::DQ > 0 ? R::DQ : 1][DA];
+            // the Newton matrix, entry by entry, through `put` (registers on the common path, local memory on the
+            // pivoting one)
+            auto assemble = [&](auto&& put) {
 #pragma unroll
-            for (int j = 0; j < S; ++j) {
-                T J[D * D];
-                R::jac(Y[j], ps[j], th, J);
+                for (int j = 0; j < S; ++j) {
+                    T J[D * D];
+                    R::jac(Y[j], ps[j], th, J);
 #pragma unroll
-                for (int i = 0; i < S; ++i) {
-                    const T ha = h * tab.a(i, j);
+                    for (int i = 0; i < S; ++i) {
+                        const T ha = h * tab.a(i, j);
 #pragma unroll
-                    for (int r = 0; r < DA; ++r)
+                        for (int r = 0; r < DA; ++r)
 #pragma unroll
-                        for (int c = 0; c < DA; ++c)
-                            Ma[i * DA + r][j * DA + c] = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+                            for (int c = 0; c < DA; ++c)
+                                put(i * DA + r, j * DA + c, ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c]);
+                    }
+#pragma unroll
+                    for (int q = 0; q < R::DQ; ++q)
+#pragma unroll
+                        for (int c = 0; c < DA; ++c) Jq[j][q][c] = J[(DA + q) * D + c];
                 }
-#pragma unroll
-                for (int q = 0; q < R::DQ; ++q)
-#pragma unroll
-                    for (int c = 0; c < DA; ++c) Jq[j][q][c] = J[(DA + q) * D + c];
-            }
+            };
+            assemble([&](int r, int c, T v) { Ma[r][c] = v; });
 #pragma unroll
             for (int i = 0; i < S; ++i)
 #pragma unroll
                 for (int r = 0; r < DA; ++r) b[i * DA + r] = -Rs[i][r];
-            if (!reg_solve<T, MA>(Ma, b)) {
+            int bad = reg_solve<T, MA>(Ma, b);
+            if (bad == 2) {  // a diagonal entry failed the threshold test: solve again with row exchanges
+                T ta[MA * MA], tb[MA];
+                assemble([&](int r, int c, T v) { ta[r * MA + c] = v; });
+#pragma unroll
+                for (int i = 0; i < S; ++i)
+#pragma unroll
+                    for (int r = 0; r < DA; ++r) tb[i * DA + r] = -Rs[i][r];
+                bad = finish_with_pivoting<T, MA>(ta, tb, 0) ? 0 : 1;
+#pragma unroll
+                for (int r = 0; r < MA; ++r) b[r] = tb[r];
+            }
+            if (bad) {
                 status |= OZ_STATUS_SINGULAR;
                 break;
             }
@@ -450,28 +467,39 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
         // M_aa^T Ybar_a = blk(J^T)(h b (x) lam) restricted to the active components.
         constexpr int DA = D - R::DQ, MA = S * DA;
         T Mt[MA][MA], b[MA];
+        auto assemble = [&](auto&& put, auto&& put_rhs) {  // transposed Newton matrix and right-hand side, entry by entry
 #pragma unroll
-        for (int j = 0; j < S; ++j) {
-            T J[D * D];
-            R::jac(Y[j], ps[j], th, J);
+            for (int j = 0; j < S; ++j) {
+                T J[D * D];
+                R::jac(Y[j], ps[j], th, J);
 #pragma unroll
-            for (int i = 0; i < S; ++i) {
-                const T ha = h * tab.a(i, j);
+                for (int i = 0; i < S; ++i) {
+                    const T ha = h * tab.a(i, j);
 #pragma unroll
-                for (int r = 0; r < DA; ++r)
+                    for (int r = 0; r < DA; ++r)
 #pragma unroll
-                    for (int c = 0; c < DA; ++c)
-                        Mt[j * DA + c][i * DA + r] = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+                        for (int c = 0; c < DA; ++c)
+                            put(j * DA + c, i * DA + r, ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c]);
+                }
+#pragma unroll
+                for (int c = 0; c < DA; ++c) {
+                    T acc = T(0);
+#pragma unroll
+                    for (int r = 0; r < D; ++r) acc += J[r * D + c] * lam[r];
+                    put_rhs(j * DA + c, h * tab.B[j] * acc);
+                }
             }
+        };
+        assemble([&](int r, int c, T v) { Mt[r][c] = v; }, [&](int r, T v) { b[r] = v; });
+        int bad = reg_solve<T, MA>(Mt, b);
+        if (bad == 2) {  // a diagonal entry failed the threshold test: solve again with row exchanges
+            T ta[MA * MA], tb[MA];
+            assemble([&](int r, int c, T v) { ta[r * MA + c] = v; }, [&](int r, T v) { tb[r] = v; });
+            bad = finish_with_pivoting<T, MA>(ta, tb, 0) ? 0 : 1;
 #pragma unroll
-            for (int c = 0; c < DA; ++c) {
-                T acc = T(0);
-#pragma unroll
-                for (int r = 0; r < D; ++r) acc += J[r * D + c] * lam[r];
-                b[j * DA + c] = h * tab.B[j] * acc;
-            }
+            for (int r = 0; r < MA; ++r) b[r] = tb[r];
         }
-        if (!reg_solve<T, MA>(Mt, b)) status |= OZ_STATUS_SINGULAR;
+        if (bad) status |= OZ_STATUS_SINGULAR;
 #pragma unroll
         for (int i = 0; i < S; ++i) {
 #pragma unroll
