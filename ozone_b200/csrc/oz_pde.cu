@@ -18,6 +18,7 @@
 // grid: reductions only count the cells it owns (see ozone_b200/parallel.py for the halo exchange).
 #include "oz_common.cuh"
 #include "oz_tm_launch.cuh"
+#include "oz_linalg.cuh"
 
 namespace oz {
 
@@ -97,6 +98,49 @@ OZ_D T block_sum(T v, T* sm) {
     return r;  // valid in warp 0
 }
 
+// ---- exp and reciprocal of the reaction term ------------------------------------------------------------------
+// The fused step evaluates exp(-gamma / (1 + x)) once per cell and stage.  The library exp costs ~20 FP64
+// instructions plus ~30 uniform-register moves for its 64-bit constants (they do not fit in the uniform file next
+// to the tableau, so every inlined copy re-creates them: 24 % of all issued instructions were UMOV), and the IEEE
+// division another ~10 with a slow-path branch.  Here:
+//   exp(t) = 2^k 2^(j/32) e^r,  round(32 t log2 e) = 32 k + j,  |r| <= ln2 / 64,  e^r by a degree-6 Taylor sum
+// (truncation 3e-18 relative), 2^(j/32) from a 32-entry shared-memory table: 11 FP64 instructions, 9 constants.
+// 1 / (1 + x) is the reciprocal seed plus two Newton steps (oz_linalg.cuh).  Relative error of both ~2e-16.
+// fp32 keeps expf and the plain division.
+constexpr int kExpTab = 32;
+
+template <typename T>
+OZ_D void pde_exp_table(T* tab) {  // caller synchronises before the first pde_exp
+    if (threadIdx.x < kExpTab) tab[threadIdx.x] = (T)exp2((double)threadIdx.x / kExpTab);
+}
+
+OZ_D float pde_exp(float t, const float*) { return expf(t); }
+OZ_D float pde_rcp(float x) { return 1.0f / x; }
+OZ_D double pde_rcp(double x) { return fast_rcp(x); }
+
+OZ_D double pde_exp(double t, const double* tab) {
+    constexpr double kMagic = 6755399441055744.0;                 // 1.5 * 2^52: adding it rounds to an integer
+    constexpr double kLn2Hi = 6.93147180369123816490e-01 / 32;    // ln2 split so that n * kLn2Hi is exact
+    constexpr double kLn2Lo = 1.90821492927058770002e-10 / 32;
+    const double kd = fma(t, 46.166241308446828384, kMagic);      // 32 log2(e) t
+    const int n = __double2loint(kd);
+    const double nf = kd - kMagic;
+    double r = fma(nf, -kLn2Hi, t);
+    r = fma(nf, -kLn2Lo, r);
+    double p = fma(r, 1.0 / 720, 1.0 / 120);
+    p = fma(p, r, 1.0 / 24);
+    p = fma(p, r, 1.0 / 6);
+    p = fma(p, r, 0.5);
+    p = fma(p, r, 1.0);
+    p = fma(p, r, 1.0);
+    const double v = tab[n & (kExpTab - 1)] * p;                  // in [1, 2.1): a NaN argument arrives here as NaN
+    const int k = n >> 5;
+    if (k > -1000 && k < 1000)                                     // exponent add; the result stays a normal number
+        return __hiloint2double(__double2hiint(v) + (k << 20), __double2loint(v));
+    const int kc = max(min(k, 2200), -2200), k1 = kc / 2;         // far out of range: overflow / underflow properly
+    return v * __hiloint2double((k1 + 1023) << 20, 0) * __hiloint2double((kc - k1 + 1023) << 20, 0);
+}
+
 // Per-CTA view of the tile.  EDGE = false is the fast path taken by CTAs whose extended tile lies inside the
 // domain and does not straddle an end of the control window: no per-cell predicates at all.
 template <typename T, bool EDGE>
@@ -113,7 +157,7 @@ struct PdeTile {
 // stage i's, so one barrier per stencil application is enough.
 template <typename T, int S, bool WITH_DIAG, bool EDGE>
 OZ_D void pde_stages(const PdeArgs<T>& a, const PdeTile<T, EDGE>& tl, T h, T ulo, T uhi, const T* yv,
-                     T (*F)[kPdeCpt], T (*Dg)[kPdeCpt], T* line2) {
+                     T (*F)[kPdeCpt], T (*Dg)[kPdeCpt], T* line2, const T* etab) {
     const Tableau<T>& tab = a.tab;
     const T du = uhi - ulo;
 #pragma unroll
@@ -141,8 +185,8 @@ OZ_D void pde_stages(const PdeArgs<T>& a, const PdeTile<T, EDGE>& tl, T h, T ulo
         for (int m = 0; m < kPdeCpt; ++m) {
             const int e = threadIdx.x + m * kPdeBlock;
             const T x = Yi[m];
-            const T q = T(1) / (T(1) + x);
-            const T ex = a.rhs.beta_t * exp(-a.rhs.gamma * q);
+            const T q = pde_rcp(T(1) + x);
+            const T ex = a.rhs.beta_t * pde_exp(-a.rhs.gamma * q, etab);
             T f = (line[e] - T(2) * x + line[e + 2]) * a.rhs.inv_dx2 + ex - a.rhs.bt_emg + (tl.mask(m) * bu_ui - a.rhs.beta_u * x);
             if (EDGE && !tl.inside[m]) f = T(0);
             F[i][m] = f;
@@ -176,7 +220,7 @@ OZ_D bool pde_is_edge(const PdeArgs<T>& a, long long base) {
 }
 
 template <typename T, int S, bool EDGE>
-OZ_D void pde_step_body(const PdeArgs<T>& a, long long base, T* line2, T* red) {
+OZ_D void pde_step_body(const PdeArgs<T>& a, long long base, T* line2, T* red, const T* etab) {
     constexpr int HALO = S;
     const int interior = a.tile;
     PdeTile<T, EDGE> tl;
@@ -185,7 +229,7 @@ OZ_D void pde_step_body(const PdeArgs<T>& a, long long base, T* line2, T* red) {
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) yv[m] = tl.in(m) ? __ldg(a.y_in + base + threadIdx.x + m * kPdeBlock) : T(0);
     const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
-    pde_stages<T, S, false, EDGE>(a, tl, h, ulo, uhi, yv, F, nullptr, line2);
+    pde_stages<T, S, false, EDGE>(a, tl, h, ulo, uhi, yv, F, nullptr, line2, etab);
     T acc2 = T(0);
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) {
@@ -213,15 +257,17 @@ template <typename T, int S>
 __global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE) pde_step_kernel(const PdeArgs<T> a) {
     __shared__ T line2[2 * kPdeLine];
     __shared__ T red[32];
+    __shared__ T etab[kExpTab];
+    pde_exp_table(etab);   // visible after the first barrier inside pde_stages
     const long long base = (long long)blockIdx.x * a.tile - S;
     if (threadIdx.x == 0) {
         line2[0] = line2[kPdeLine] = T(0);
         line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
     }
     if (pde_is_edge(a, base))
-        pde_step_body<T, S, true>(a, base, line2, red);
+        pde_step_body<T, S, true>(a, base, line2, red, etab);
     else
-        pde_step_body<T, S, false>(a, base, line2, red);
+        pde_step_body<T, S, false>(a, base, line2, red, etab);
 }
 
 // sum of squares of a vector over the owned cells (J_space of the initial condition)
@@ -238,7 +284,7 @@ __global__ void __launch_bounds__(kPdeBlock) pde_sumsq_kernel(const T* __restric
 }
 
 template <typename T, int S, bool EDGE>
-OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red) {
+OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red, const T* etab) {
     constexpr int HALO = 2 * S;
     const Tableau<T>& tab = a.tab;
     const int interior = a.tile;
@@ -256,7 +302,7 @@ OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red
     }
     const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
     const T fbs = a.field_bar ? __ldg(a.field_bar) * a.fb_scale : T(0);
-    pde_stages<T, S, true, EDGE>(a, tl, h, ulo, uhi, yv, F, Dg, line2);
+    pde_stages<T, S, true, EDGE>(a, tl, h, ulo, uhi, yv, F, Dg, line2, etab);
 
     // transposed stage chain:  W_i = b_i lam + sum_{j>i} a_ji Ybar_j,  G_i = h W_i,  Ybar_i = J(Y_i)^T G_i
     // h_bar = sum_i W_i . F_i (no division by h);  u_bar parts from beta_U H . G_i
@@ -319,15 +365,17 @@ template <typename T, int S>
 __global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE_ADJ) pde_adjoint_step_kernel(const PdeArgs<T> a) {
     __shared__ T line2[2 * kPdeLine];
     __shared__ T red[32];
+    __shared__ T etab[kExpTab];
+    pde_exp_table(etab);
     const long long base = (long long)blockIdx.x * a.tile - 2 * S;
     if (threadIdx.x == 0) {
         line2[0] = line2[kPdeLine] = T(0);
         line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
     }
     if (pde_is_edge(a, base))
-        pde_adjoint_body<T, S, true>(a, base, line2, red);
+        pde_adjoint_body<T, S, true>(a, base, line2, red, etab);
     else
-        pde_adjoint_body<T, S, false>(a, base, line2, red);
+        pde_adjoint_body<T, S, false>(a, base, line2, red, etab);
 }
 
 // lam_n = final_bar + hist_bar[n] + field_bar * (200/nx) * y_n
