@@ -274,6 +274,15 @@ class Runner:
                 pl.final_bar.copy_(plan.final_bar[:, :pl.spec.N])
             self.h2d, self.d2h = self.pipe.bytes_per_run()
             self.e2e_launches = self.pipe.launches
+            self.e2e_graph = False
+            if not args.no_e2e_graph:
+                try:                       # replay the slice pipeline as one CUDA graph (host enqueue cost off the path)
+                    self.pipe.capture()
+                    self.e2e_graph = True
+                except Exception as exc:   # noqa: BLE001 -- fall back to eager enqueue, and say so in the bench line
+                    self.pipe.graph = None
+                    self.e2e_graph_error = repr(exc)[:200]
+                    torch.cuda.synchronize()
         if self.kind == 'picard':
             self.launches = 1 + plan.launches_adjoint
         if self.kind == 'colloc':
@@ -371,6 +380,7 @@ def main():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--newton-tol', type=float, default=1e-7)
     ap.add_argument('--e2e-slices', type=int, default=6, help='sub-batches (streams) of the end-to-end leg')
+    ap.add_argument('--no-e2e-graph', action='store_true', help='enqueue the end-to-end pipeline eagerly (no CUDA graph)')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
 
@@ -537,7 +547,9 @@ def main():
                             'spatial shard: see ozone_b200/parallel.py'}, **extra_cfg),
             'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
                     'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps,
-                    'how': (f'engine.PipelinedTmSolve: {args.e2e_slices} sub-batches on their own streams, pinned host buffers'
+                    'how': (f'engine.PipelinedTmSolve: {args.e2e_slices} sub-batches on their own streams, pinned host buffers, '
+                            + ('slice pipeline replayed as one CUDA graph' if getattr(run, 'e2e_graph', False) else
+                               'eager enqueue' + (f' (graph capture failed: {run.e2e_graph_error})' if hasattr(run, 'e2e_graph_error') else ''))
                             if run.pipe is not None else 'engine plan API, pinned host buffers, one stream')},
             'gpu_launches': args.steps * run.launches,
             'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,

@@ -541,8 +541,35 @@ class PipelinedTmSolve:
                 if k not in self.upload:
                     getattr(pl, k).copy_(hin[k])
 
+    def capture(self):
+        """Record the slice pipeline of run() once as a CUDA graph; later run() calls replay it.  A run is ~10
+        enqueue calls per slice (copies, two solves, reducers, event bookkeeping), which at small sub-batches costs
+        the host more time than the GPU needs to execute them; the replay is one launch.  Buffers are the plan's
+        own, so the captured addresses stay valid.  Call after set_host_inputs()."""
+        self.graph = None
+        self.run()                                  # warm-up outside the capture (module loading, lazy init)
+        torch.cuda.synchronize()
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self._enqueue_slices()
+        self.graph = g
+        return self
+
     def run(self):
         """Enqueue upload -> forward -> reverse -> download for every slice; returns immediately."""
+        if getattr(self, 'graph', None) is not None:
+            self.graph.replay()
+        else:
+            self._enqueue_slices()
+        # gradients of batch-shared inputs: sum over the slices (fixed order), optional all-reduce over ranks, download
+        for k in self.host_grad[0]:
+            if self.shared[k]:
+                total = torch.stack([pl.grad[k] for pl in self.plans]).sum(0)
+                if self.reduce_shared is not None:
+                    self.reduce_shared(total)
+                self.host_shared[k].copy_(total, non_blocking=True)
+
+    def _enqueue_slices(self):
         cur = torch.cuda.current_stream()
         self._start.record(cur)
         for pl, st, hin, hg, hf, done in zip(self.plans, self.streams, self.host_in, self.host_grad, self.host_final,
@@ -561,13 +588,6 @@ class PipelinedTmSolve:
                 done.record(st)
         for done in self._done:
             cur.wait_event(done)
-        # gradients of batch-shared inputs: sum over the slices (fixed order), optional all-reduce over ranks, download
-        for k in self.host_grad[0]:
-            if self.shared[k]:
-                total = torch.stack([pl.grad[k] for pl in self.plans]).sum(0)
-                if self.reduce_shared is not None:
-                    self.reduce_shared(total)
-                self.host_shared[k].copy_(total, non_blocking=True)
 
     def bytes_per_run(self):
         w = 8 if self.spec.dtype == torch.float64 else 4

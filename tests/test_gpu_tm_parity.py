@@ -218,3 +218,16 @@ def test_pipelined_host_batch_equals_the_single_launch_solve():
         assert torch.equal(final, plan.final.cpu())
         assert torch.equal(grads['p'], plan.grad['p'].cpu())
         assert relerr(np_(grads['h']), np_(plan.grad['h'])) < 1e-13      # same terms, different summation order
+    # the same pipeline replayed as a CUDA graph, on NEW host inputs written into the pinned buffers it captured
+    pipe.capture()
+    p2 = p * 0.5
+    plan.p.copy_(p2)
+    plan.forward(); plan.adjoint()
+    pipe.set_host_inputs(p=p2.cpu())
+    for _ in range(2):
+        pipe.run()
+        torch.cuda.synchronize()
+        final, grads = pipe.gather()
+        assert torch.equal(final, plan.final.cpu())
+        assert torch.equal(grads['p'], plan.grad['p'].cpu())
+        assert relerr(np_(grads['h']), np_(plan.grad['h'])) < 1e-13
