@@ -284,6 +284,9 @@ def rhs_eval(spec: SolveSpec, y, p=None, th=None):
     return dy, prof, fld
 
 
+GRID_STEPS_PER_LAUNCH = 4      # OZ_PDE_FUSE in csrc/oz_pde.cu: forward grid steps fused into one launch
+
+
 class TmPlan:
     """A solve with every buffer allocated once: repeated forward()/adjoint() calls only enqueue
     kernels (no allocation, no host sync).  This is what a caller inside an optimisation loop
@@ -340,9 +343,11 @@ class TmPlan:
                           if flag and self.grad[k] is not None)
         self.launches_forward, self.launches_adjoint = 1, 1 + shared_rows
         if spec.info['kind'] == 1:      # grid: one launch per step (+ sum-of-squares, field / terminal, replay, gradient reducers)
-            nseg = (n // spec.num_inner) if (spec.num_inner > 0 and self.hist is None) else 0
-            self.launches_forward = n + 2
-            self.launches_adjoint = 1 + (n - nseg if nseg else 0) + n + 1
+            K, ni = GRID_STEPS_PER_LAUNCH, spec.num_inner
+            groups = lambda steps: -(-steps // K)          # launches of the fused forward kernel for a run of steps
+            nseg = (n // ni) if (ni > 0 and self.hist is None) else 0
+            self.launches_forward = ((n // ni) * groups(ni) if ni > 0 else groups(n)) + 2
+            self.launches_adjoint = 1 + (nseg * groups(ni - 1) if nseg else 0) + n + 1
 
     def forward(self):
         self.pb.stream = torch.cuda.current_stream().cuda_stream
