@@ -39,6 +39,10 @@ constexpr int kPdeCpt = OZ_PDE_CPT;                // cells per thread
 constexpr int kPdeExt = kPdeBlock * kPdeCpt;      // cells per CTA including halos
 constexpr int kPdeLine = kPdeExt + 2;             // one shared-memory line: the tile plus a zero cell at either end
 constexpr int kPdeFuse = OZ_PDE_FUSE;
+#ifndef OZ_PDE_FUSE_ADJ   /* reverse steps per launch */
+#define OZ_PDE_FUSE_ADJ 2
+#endif
+constexpr int kPdeFuseAdj = OZ_PDE_FUSE_ADJ;
 
 template <typename T>
 struct PdeRhs {
@@ -70,8 +74,8 @@ struct PdeArgs {
     long long own_lo, own_hi;  // local range whose cells count in reductions
     long long nx_global;
     int tile;            // interior cells per CTA (<= kPdeExt - 2*HALO), balanced over the resident CTA slots
-    int halo;            // forward launch: cells on either side of the interior (>= nsub * s)
-    int nsub;            // forward launch: steps fused in this launch (1 .. kPdeFuse)
+    int halo;            // cells on either side of the interior (forward: >= nsub * s, reverse: >= 2 * nsub * s)
+    int nsub;            // steps fused in this launch
     const T* y_in;
     T* y_out;            // state after the last fused step (or nullptr when rows_out takes every step)
     T* rows_out;         // optional: state after fused step j goes to rows_out + j * row_stride
@@ -82,9 +86,12 @@ struct PdeArgs {
     T* part_sq;          // partial sums of the new state squared over owned cells, row j (of sq_stride) per fused step, or nullptr
     long long sq_stride;
     // adjoint
+    // reverse launch: steps k, k-1, .., k-nsub+1; fused step j reads y_in - j*row_stride, h[-j], u_lo[-j], u_hi[-j],
+    // hist_bar_k - j*nx and writes its partial sums to row -j (of adj_stride) of part_h / part_ulo / part_uhi
     const T* lam_in;     // lambda_{k+1}
-    T* lam_out;          // lambda_k
+    T* lam_out;          // lambda_{k-nsub+1}
     const T* hist_bar_k; // direct cotangent of y_k or nullptr
+    long long adj_stride;
     const T* field_bar;  // device scalar (or nullptr): cotangent of the field output
     T fb_scale;          // 200 / nx_global: d J_space / d y_j = fb_scale * y_j
     T* part_h;           // [ncta]
@@ -300,11 +307,13 @@ __global__ void __launch_bounds__(kPdeBlock) pde_sumsq_kernel(const T* __restric
     if (threadIdx.x == 0) part[blockIdx.x] = s;
 }
 
+// Reverse launch: a.nsub consecutive reverse steps on the CTA's extended tile, multipliers kept in registers between
+// them.  Each step loads the exact y_k of the whole tile, re-derives its stages (s fringe cells per side go stale) and
+// runs the transposed chain (s more), so the multipliers of the interior are exact with a halo of 2 s nsub.
 template <typename T, int S, bool EDGE>
 OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red, const T* etab) {
-    constexpr int HALO = 2 * S;
     const Tableau<T>& tab = a.tab;
-    const int interior = a.tile;
+    const int halo = a.halo, interior = a.tile;
     PdeTile<T, EDGE> tl;
     pde_tile_setup<T, EDGE>(a, base, tl);
     T yv[kPdeCpt], lam[kPdeCpt], F[S][kPdeCpt], Yb[S][kPdeCpt], Dg[S][kPdeCpt];
@@ -312,70 +321,76 @@ OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red
 #pragma unroll
     for (int m = 0; m < kPdeCpt; ++m) {
         const int e = threadIdx.x + m * kPdeBlock;
-        const long long j = base + e;
-        yv[m] = tl.in(m) ? __ldg(a.y_in + j) : T(0);
-        lam[m] = tl.in(m) ? __ldg(a.lam_in + j) : T(0);
-        owned[m] = e >= HALO && e < HALO + interior && tl.in(m) && j >= a.own_lo && j < a.own_hi;
+        const long long c = base + e;
+        lam[m] = tl.in(m) ? __ldg(a.lam_in + c) : T(0);
+        owned[m] = e >= halo && e < halo + interior && tl.in(m) && c >= a.own_lo && c < a.own_hi;
     }
-    const T h = __ldg(a.h), ulo = __ldg(a.u_lo), uhi = __ldg(a.u_hi);
     const T fbs = a.field_bar ? __ldg(a.field_bar) * a.fb_scale : T(0);
-    pde_stages<T, S, true, EDGE>(a, tl, h, ulo, uhi, yv, F, Dg, line2, etab);
+    for (int j = 0; j < a.nsub; ++j) {
+        const T* yrow = a.y_in - j * a.row_stride;
+#pragma unroll
+        for (int m = 0; m < kPdeCpt; ++m) yv[m] = tl.in(m) ? __ldg(yrow + base + threadIdx.x + m * kPdeBlock) : T(0);
+        const T h = __ldg(a.h - j), ulo = __ldg(a.u_lo - j), uhi = __ldg(a.u_hi - j);
+        pde_stages<T, S, true, EDGE>(a, tl, h, ulo, uhi, yv, F, Dg, line2, etab);
 
-    // transposed stage chain:  W_i = b_i lam + sum_{j>i} a_ji Ybar_j,  G_i = h W_i,  Ybar_i = J(Y_i)^T G_i
-    // h_bar = sum_i W_i . F_i (no division by h);  u_bar parts from beta_U H . G_i
-    T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
+        // transposed stage chain:  W_i = b_i lam + sum_{j>i} a_ji Ybar_j,  G_i = h W_i,  Ybar_i = J(Y_i)^T G_i
+        // h_bar = sum_i W_i . F_i (no division by h);  u_bar parts from beta_U H . G_i
+        T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
 #pragma unroll
-    for (int i = S - 1; i >= 0; --i) {
-        T* line = line2 + ((S + (S - 1 - i)) & 1) * kPdeLine;   // keeps alternating after the S forward stages
-        T G[kPdeCpt];
+        for (int i = S - 1; i >= 0; --i) {
+            T* line = line2 + ((S + (S - 1 - i)) & 1) * kPdeLine;   // keeps alternating after the S forward stages
+            T G[kPdeCpt];
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) G[m] = tab.B[i] * lam[m];
+            for (int m = 0; m < kPdeCpt; ++m) G[m] = tab.B[i] * lam[m];
 #pragma unroll
-        for (int j = i + 1; j < S; ++j) {
-            const T aji = tab.a(j, i);
-            if (aji != T(0)) {
+            for (int q = i + 1; q < S; ++q) {
+                const T aqi = tab.a(q, i);
+                if (aqi != T(0)) {
 #pragma unroll
-                for (int m = 0; m < kPdeCpt; ++m) G[m] += aji * Yb[j][m];
+                    for (int m = 0; m < kPdeCpt; ++m) G[m] += aqi * Yb[q][m];
+                }
             }
-        }
-        T usum = T(0);
+            T usum = T(0);
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
-            if (owned[m]) h_acc += G[m] * F[i][m];
-            G[m] = (EDGE && !tl.inside[m]) ? T(0) : h * G[m];
-            if (owned[m]) usum += tl.mask(m) * G[m];
-            line[1 + threadIdx.x + m * kPdeBlock] = G[m];
+            for (int m = 0; m < kPdeCpt; ++m) {
+                if (owned[m]) h_acc += G[m] * F[i][m];
+                G[m] = (EDGE && !tl.inside[m]) ? T(0) : h * G[m];
+                if (owned[m]) usum += tl.mask(m) * G[m];
+                line[1 + threadIdx.x + m * kPdeBlock] = G[m];
+            }
+            __syncthreads();
+#pragma unroll
+            for (int m = 0; m < kPdeCpt; ++m) {
+                const int e = threadIdx.x + m * kPdeBlock;
+                const T v = (line[e] - T(2) * G[m] + line[e + 2]) * a.rhs.inv_dx2 + Dg[i][m] * G[m];
+                Yb[i][m] = (EDGE && !tl.inside[m]) ? T(0) : v;
+            }
+            usum *= a.rhs.beta_u;
+            u_hi_acc += tab.C[i] * usum;
+            u_lo_acc += usum - tab.C[i] * usum;
         }
-        __syncthreads();
+        const bool last = j == a.nsub - 1;
+        const T* hb = a.hist_bar_k ? a.hist_bar_k - j * a.nx : nullptr;
 #pragma unroll
         for (int m = 0; m < kPdeCpt; ++m) {
             const int e = threadIdx.x + m * kPdeBlock;
-            const T v = (line[e] - T(2) * G[m] + line[e + 2]) * a.rhs.inv_dx2 + Dg[i][m] * G[m];
-            Yb[i][m] = (EDGE && !tl.inside[m]) ? T(0) : v;
-        }
-        usum *= a.rhs.beta_u;
-        u_hi_acc += tab.C[i] * usum;
-        u_lo_acc += usum - tab.C[i] * usum;
-    }
-#pragma unroll
-    for (int m = 0; m < kPdeCpt; ++m) {
-        const int e = threadIdx.x + m * kPdeBlock;
-        const long long j = base + e;
-        if (e >= HALO && e < HALO + interior && tl.in(m)) {
+            const long long c = base + e;
             T yb = T(0);
 #pragma unroll
             for (int i = 0; i < S; ++i) yb += Yb[i][m];
             T out = lam[m] + yb + fbs * yv[m];
-            if (a.hist_bar_k) out += __ldg(a.hist_bar_k + j);
-            a.lam_out[j] = out;
+            if (hb && tl.in(m)) out += __ldg(hb + c);
+            lam[m] = out;                           // stays zero outside the domain
+            if (last && e >= halo && e < halo + interior && tl.in(m)) a.lam_out[c] = out;
         }
+        const long long row = -(long long)j * a.adj_stride + blockIdx.x;
+        T s = block_sum(h_acc, red);
+        if (threadIdx.x == 0) a.part_h[row] = s;
+        s = block_sum(u_lo_acc, red);
+        if (threadIdx.x == 0) a.part_ulo[row] = s;
+        s = block_sum(u_hi_acc, red);
+        if (threadIdx.x == 0) a.part_uhi[row] = s;
     }
-    T s = block_sum(h_acc, red);
-    if (threadIdx.x == 0) a.part_h[blockIdx.x] = s;
-    s = block_sum(u_lo_acc, red);
-    if (threadIdx.x == 0) a.part_ulo[blockIdx.x] = s;
-    s = block_sum(u_hi_acc, red);
-    if (threadIdx.x == 0) a.part_uhi[blockIdx.x] = s;
 }
 
 template <typename T, int S>
@@ -384,7 +399,7 @@ __global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE_ADJ) pde_adjoint_step_ker
     __shared__ T red[32];
     __shared__ T etab[kExpTab];
     pde_exp_table(etab);
-    const long long base = (long long)blockIdx.x * a.tile - 2 * S;
+    const long long base = (long long)blockIdx.x * a.tile - a.halo;
     if (threadIdx.x == 0) {
         line2[0] = line2[kPdeLine] = T(0);
         line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
@@ -474,7 +489,7 @@ static PdeLayout pde_layout(const oz_problem* pb) {
     if (occ_f < 1) occ_f = 1;
     if (occ_a < 1) occ_a = 1;
     L.ncta_f = balance(kPdeExt - 2 * S * kPdeFuse, sm_count() * occ_f, &L.tile_f);
-    L.ncta_a = balance(kPdeExt - 4 * S, sm_count() * occ_a, &L.tile_a);
+    L.ncta_a = balance(kPdeExt - 4 * S * kPdeFuseAdj, sm_count() * occ_a, &L.tile_a);
     const size_t nx = (size_t)L.nx, nt = (size_t)pb->n + 1;
     const size_t vec = (nx + 31) / 32 * 32;
     // forward: ping, pong, part_sq[nt][ncta_f]
@@ -647,10 +662,16 @@ static int pde_adjoint(const oz_problem* pb) {
                 q += nsub;
             }
         }
-        for (int k = lo + ni - 1; k >= lo; --k) {
+        for (int k = lo + ni - 1; k >= lo;) {          // steps k .. k - nsub + 1 in one launch, within the segment
+            const int nsub = k - lo + 1 < kPdeFuseAdj ? k - lo + 1 : kPdeFuseAdj;
+            const int kl = k - nsub + 1;
+            a.nsub = nsub;
+            a.halo = 2 * S * kPdeFuseAdj;
+            a.row_stride = use_seg ? (long long)vec : nx;
+            a.adj_stride = L.ncta_a;
             a.y_in = use_seg ? seg + (size_t)(k - lo) * vec : hist + (size_t)k * nx;
             a.lam_in = lam[cur];
-            a.lam_out = (k == 0 && pb->y0_bar) ? (T*)pb->y0_bar : lam[cur ^ 1];
+            a.lam_out = (kl == 0 && pb->y0_bar) ? (T*)pb->y0_bar : lam[cur ^ 1];
             a.hist_bar_k = hist_bar ? hist_bar + (size_t)k * nx : nullptr;
             a.h = h + k;
             a.u_lo = u + k;
@@ -660,6 +681,7 @@ static int pde_adjoint(const oz_problem* pb) {
             a.part_uhi = puhi + (size_t)k * L.ncta_a;
             pde_adjoint_step_kernel<T, S><<<(unsigned)L.ncta_a, kPdeBlock, 0, st>>>(a);
             cur ^= 1;
+            k = kl - 1;
         }
     }
     OZ_CUDA_CHECK(cudaGetLastError());

@@ -285,6 +285,7 @@ def rhs_eval(spec: SolveSpec, y, p=None, th=None):
 
 
 GRID_STEPS_PER_LAUNCH = 4      # OZ_PDE_FUSE in csrc/oz_pde.cu: forward grid steps fused into one launch
+GRID_REVERSE_STEPS_PER_LAUNCH = 2   # OZ_PDE_FUSE_ADJ
 
 
 class TmPlan:
@@ -347,7 +348,8 @@ class TmPlan:
             groups = lambda steps: -(-steps // K)          # launches of the fused forward kernel for a run of steps
             nseg = (n // ni) if (ni > 0 and self.hist is None) else 0
             self.launches_forward = ((n // ni) * groups(ni) if ni > 0 else groups(n)) + 2
-            self.launches_adjoint = 1 + (nseg * groups(ni - 1) if nseg else 0) + n + 1
+            rgroups = lambda steps: -(-steps // GRID_REVERSE_STEPS_PER_LAUNCH)
+            self.launches_adjoint = 1 + (nseg * (groups(ni - 1) + rgroups(ni)) if nseg else rgroups(n)) + 1
 
     def forward(self):
         self.pb.stream = torch.cuda.current_stream().cuda_stream
