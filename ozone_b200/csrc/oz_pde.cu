@@ -6,13 +6,15 @@
 //   field output J_space = (100/nx) sum_j x_j^2 + 20 u^2 with the rebound dx = 1/nx (:62-76)
 //
 // One trajectory whose d = nx components are the cells, so the parallel axis is SPACE.  One launch
-// advances the whole grid by one step with all s stages fused: a CTA loads its tile plus a halo of
-// s cells per side, the stage values circulate through one shared-memory line (each stencil
-// application invalidates one more halo cell per side), F_i stay in registers, and only y_{k+1}
-// is written.  HBM traffic per cell-step is one read + one write (2w), not 2w per stage.
-// The reverse step re-derives the stages the same way and then runs the transposed stage chain
-// (the 3-point stencil is symmetric, so it is the same access pattern on the multipliers) with a
-// halo of 2s.  Grid-wide sums (J_space, u_bar, h_bar) are per-CTA partials reduced in a fixed order.
+// advances the whole grid by up to four steps with all s stages of each fused: a CTA loads its tile plus
+// a halo of s cells per side and step, the stage values circulate through one shared-memory line (each
+// stencil application invalidates one more halo cell per side), F_i and the state stay in registers, and
+// only the interior of the last state (or of every state, when the history is kept) is written.  HBM /
+// L2 traffic per cell-step is at most one read + one write (2w), not 2w per stage.
+// The reverse launch (two steps) re-derives the stages of each step the same way and then runs the
+// transposed stage chain (the 3-point stencil is symmetric, so it is the same access pattern on the
+// multipliers) with a halo of 2s per step.  Grid-wide sums (J_space, u_bar, h_bar) are per-CTA partials
+// per step, reduced in a fixed order.
 //
 // `x_off`/`own_lo`/`own_hi` let a rank run the same kernels on a slab [x_off, x_off + nx) of a larger
 // grid: reductions only count the cells it owns (see ozone_b200/parallel.py for the halo exchange).

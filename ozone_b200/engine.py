@@ -343,7 +343,7 @@ class TmPlan:
         shared_rows = sum(1 for k, flag in (('h', spec.h_shared), ('p', spec.p_shared), ('th', spec.th_shared))
                           if flag and self.grad[k] is not None)
         self.launches_forward, self.launches_adjoint = 1, 1 + shared_rows
-        if spec.info['kind'] == 1:      # grid: one launch per step (+ sum-of-squares, field / terminal, replay, gradient reducers)
+        if spec.info['kind'] == 1:      # grid: fused multi-step launches (+ sum-of-squares, field / terminal, replay, gradient reducers)
             K, ni = GRID_STEPS_PER_LAUNCH, spec.num_inner
             groups = lambda steps: -(-steps // K)          # launches of the fused forward kernel for a run of steps
             nseg = (n // ni) if (ni > 0 and self.hist is None) else 0
