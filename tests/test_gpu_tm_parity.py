@@ -159,7 +159,12 @@ def test_config3_diffusion_reaction_grid_history_mode(method, nx):
     _compare(c, method)
 
 
-@pytest.mark.parametrize('nx,n,ni', [(777, 16, 4), (4100, 24, 6), (50, 9, 3)])
+def test_config3_grid_history_with_a_ragged_last_launch():
+    # 13 steps = three launches of four fused steps and one of a single step; 2500 cells = three CTAs
+    _compare(cases.pde_inputs(nx=2500, n=13), 'RK4')
+
+
+@pytest.mark.parametrize('nx,n,ni', [(777, 16, 4), (4100, 24, 6), (50, 9, 3), (2500, 15, 5), (1300, 14, 7)])
 def test_config3_checkpointed_grid_adjoint(nx, n, ni):
     # TimeMarchingCheckpoints on the grid: only nc+1 states kept, segments replayed in the reverse sweep
     c = cases.pde_inputs(nx=nx, n=n)
