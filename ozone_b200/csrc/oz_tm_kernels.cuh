@@ -679,6 +679,7 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
     const bool h_red = a.h_bar && a.h_shared, p_red = a.p_bar && a.p_shared && DM::P > 0;
     const int nq = (h_red ? 1 : 0) + (p_red ? DM::P : 0);   // rows per step
     const int kc = nq ? 32 / nq : 0;                        // steps per tile
+    const bool staged = STAGED && nq > 0 && nq <= 32;       // more than 32 shared quantities per step: shuffle path
     int fill = 0, kstart = 0;
     auto flush = [&]() {  // rows 0 .. fill * nq - 1 hold steps kstart, kstart - 1, ...
         __syncwarp();
@@ -836,7 +837,7 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
                                         (IMPL && a.stages && !use_seg) ? a.stages + (long long)k * S * D * N : nullptr, N, i);
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) pb_next[c] += pb_hi[c];
-            if constexpr (STAGED) {
+            if (staged) {
                 // shared-input cotangents of this step go to the warp's tile, one row per quantity; per-trajectory
                 // ones are stored directly
                 if (fill == 0) kstart = k;
@@ -885,9 +886,7 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
             }
         }
     }
-    if constexpr (STAGED) {
-        if (fill > 0) flush();
-    }
+    if (staged && fill > 0) flush();
     emit_p(0, warp);
     if (a.y0_bar && valid)
 #pragma unroll
