@@ -514,9 +514,10 @@ def main():
         dominant, other = (adj_e, fwd_e) if adj_avg_s >= fwd_avg_s else (fwd_e, adj_e)
         if run.kind == 'tm' and not run.spec.method.explicit:
             note = ('implicit Gauss-Legendre + Newton is FP64-ALU bound, not HBM bound (about 1 kflop per 100 compulsory '
-                    'bytes, ncu: fp64 pipe 44 % busy vs DRAM 6 %); the HBM fraction is reported because the metric asks for it')
+                    'bytes, ncu: fp64 pipe 54 % busy vs DRAM 9 %); the HBM fraction is reported because the metric asks for it, the FP64 '
+                    'fraction under roofline.fp64')
         elif run.kind == 'grid':
-            note = 'fp64 exp() per cell and stage makes the fused step FP64-issue bound (ncu launch list: 20 us per 10^6-cell step)'
+            note = 'one exponential per cell and stage: the fused steps are FP64-bound (ncu: fp64 pipe 55 %, state L2-resident)'
         else:
             note = 'HBM / FP64 co-limited explicit path (DESIGN.md section 5)'
         roof = dict({'bound': 'hbm'}, **dominant)
@@ -526,6 +527,17 @@ def main():
                                                 'f32': run.engine.measure_fma_peak(torch.float32, dev)}
         except Exception as exc:                                            # never let the probe break the bench line
             roof['fma_peak_measured_tflops'] = {'error': str(exc)}
+        # FP64-bound kernels: executed FP64 flops per launch (counted by ncu, profiles/traffic.json) over the live launch
+        # time, against the FMA peak measured above
+        flops = traffic.get('fp64_flops_per_launch', {})
+        f64_peak = roof['fma_peak_measured_tflops'].get('f64')
+        if flops and f64_peak and run.w == 8:
+            for entry in (roof, other):
+                fl = flops.get(entry['kernel'].split(' ')[0])
+                if fl:
+                    t = fl / (entry['avg_launch_ms'] * 1e-3) / 1e12
+                    entry['fp64'] = {'achieved_tflops': t, 'peak_tflops': f64_peak, 'frac': t / f64_peak,
+                                     'flops_per_launch': fl, 'source': flops.get('source')}
         roof.update({'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6650 GB/s',
                      'traffic_source': traffic.get('source'), 'other_kernel': other, 'note': note})
         cpu = None
