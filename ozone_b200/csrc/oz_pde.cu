@@ -128,8 +128,10 @@ OZ_D T block_sum(T v, T* sm) {
 constexpr int kExpTab = 32;
 
 template <typename T>
-OZ_D void pde_exp_table(T* tab) {  // caller synchronises before the first pde_exp
-    if (threadIdx.x < kExpTab) tab[threadIdx.x] = (T)exp2((double)threadIdx.x / kExpTab);
+OZ_D void pde_exp_table(T* tab) {  // caller synchronises before the first pde_exp; fp32 does not use the table
+    if constexpr (sizeof(T) == 8) {
+        if (threadIdx.x < kExpTab) tab[threadIdx.x] = (T)exp2((double)threadIdx.x / kExpTab);
+    }
 }
 
 OZ_D float pde_exp(float t, const float*) { return expf(t); }
