@@ -131,14 +131,15 @@ struct SmemSystem {
 // data, so a trajectory's result does not depend on its warp neighbours.  On return b holds the solution;
 // false = a zero / non-finite pivot was met.
 
-// Reciprocal of a pivot: hardware seed (rcp.approx, ~2^-23) + two Newton steps -> full double precision without the
-// special-case branches of an IEEE division (pivots here are O(1); a zero / non-finite pivot is flagged by the caller).
+// Reciprocal of a pivot: hardware seed r0 (rcp.approx, ~20 bits) corrected once to third order,
+// r = r0 (1 + e + e^2) with e = 1 - x r0: the error is e^3 < 2^-60, i.e. full double precision after three dependent
+// FMAs (two Newton steps need four) and without the special-case branches of an IEEE division (pivots here are O(1);
+// a zero / non-finite pivot is flagged by the caller).
 OZ_D double fast_rcp(double x) {
     double r;
     asm("rcp.approx.ftz.f64 %0, %1;" : "=d"(r) : "d"(x));
-    r = fma(fma(-x, r, 1.0), r, r);
-    r = fma(fma(-x, r, 1.0), r, r);
-    return r;
+    const double e = fma(-x, r, 1.0);
+    return fma(r, fma(e, e, e), r);
 }
 OZ_D float fast_rcp(float x) { return 1.0f / x; }
 
