@@ -227,9 +227,11 @@ struct RegElim {
 template <typename T, int M, int Rr>
 struct RegBack {
     OZ_D static void run(T (&a)[M][M], T (&b)[M]) {
+        // highest column first: the unknown found last (b[Rr + 1]) enters last, so everything else of this row's sum is
+        // already done when it arrives and the dependent chain per row is one FMA and one multiplication
         T acc = b[Rr];
 #pragma unroll
-        for (int c = Rr + 1; c < M; ++c) acc -= a[Rr][c] * b[c];
+        for (int c = M - 1; c > Rr; --c) acc -= a[Rr][c] * b[c];
         b[Rr] = acc * a[Rr][Rr];
         if constexpr (Rr > 0) RegBack<T, M, Rr - 1>::run(a, b);
     }

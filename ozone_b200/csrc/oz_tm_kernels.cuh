@@ -136,15 +136,18 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
             T Rs[S][D];
             T rn2 = T(0);
 #pragma unroll
-            for (int i = 0; i < S; ++i)
+            for (int i = 0; i < S; ++i) {
+                T part = T(0);   // per-stage partial sums: S short chains instead of one of S * D dependent FMAs
 #pragma unroll
                 for (int c = 0; c < D; ++c) {
                     T acc = T(0);
 #pragma unroll
                     for (int j = 0; j < S; ++j) acc += tab.a(i, j) * F[j][c];
                     Rs[i][c] = Y[i][c] - h * acc - y[c];
-                    rn2 += Rs[i][c] * Rs[i][c];
+                    part += Rs[i][c] * Rs[i][c];
                 }
+                rn2 += part;
+            }
             if (!(rn2 == rn2)) {
                 status |= OZ_STATUS_NONFINITE;
                 break;
