@@ -675,14 +675,13 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
     // instructions, do not reduce with shuffles every step (5 shuffle pairs + 5 adds per quantity): each warp parks
     // its lanes' values in a shared-memory tile, one row per (step, quantity), and once the tile holds 32 rows lane r
     // adds up row r and writes that warp partial.  Same partial-sum layout as the shuffle path, fixed order, no atomics.
-    constexpr bool STAGED = !IMPL;
+    constexpr bool STAGED = !IMPL && DM::P + 1 <= 32;   // a step never stages more than 1 + P rows
     constexpr int kRow = 33;  // row pitch: lane r reading row r at a fixed column touches distinct banks
     __shared__ T red_tile[STAGED ? (lb_threads<R, S, T, IMPL>() / 32) * 32 * kRow : 1];
     T* tile = red_tile + (STAGED ? (threadIdx.x >> 5) * 32 * kRow : 0);
     const bool h_red = a.h_bar && a.h_shared, p_red = a.p_bar && a.p_shared && DM::P > 0;
     const int nq = (h_red ? 1 : 0) + (p_red ? DM::P : 0);   // rows per step
     const int kc = nq ? 32 / nq : 0;                        // steps per tile
-    const bool staged = STAGED && nq > 0 && nq <= 32;       // more than 32 shared quantities per step: shuffle path
     int fill = 0, kstart = 0;
     auto flush = [&]() {  // rows 0 .. fill * nq - 1 hold steps kstart, kstart - 1, ...
         __syncwarp();
@@ -840,7 +839,7 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
                                         (IMPL && a.stages && !use_seg) ? a.stages + (long long)k * S * D * N : nullptr, N, i);
 #pragma unroll
             for (int c = 0; c < DM::P; ++c) pb_next[c] += pb_hi[c];
-            if (staged) {
+            if constexpr (STAGED) {
                 // shared-input cotangents of this step go to the warp's tile, one row per quantity; per-trajectory
                 // ones are stored directly
                 if (fill == 0) kstart = k;
@@ -889,7 +888,9 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
             }
         }
     }
-    if (staged && fill > 0) flush();
+    if constexpr (STAGED) {
+        if (fill > 0) flush();
+    }
     emit_p(0, warp);
     if (a.y0_bar && valid)
 #pragma unroll
