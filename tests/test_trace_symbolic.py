@@ -89,3 +89,26 @@ def test_second_derivative_of_the_van_der_pol_cost_is_constant():
     J = Y0 * Y0 + Y1 * Y1 + P0 * P0                             # van_der_pol/main_model.py:12
     assert evaluate(diff(diff(J, Y0, {}), Y0, {}), {}) == 2.0
     assert diff(diff(J, Y0, {}), Y1, {}).is_const(0.0)
+
+
+def test_generated_functor_compiles_and_registers_without_a_gpu():
+    """Trace the reference's Lotka-Volterra callback (lotka_volterra.py:51-62), emit the CUDA functor, build the
+    plugin with nvcc (cross-compiles for sm_100a here) and register it through the C ABI.  No kernel is launched."""
+    import torch
+    from ozone_b200 import trace
+    c = torch.tensor(0.5, dtype=torch.float64)
+
+    def ode_function(v):
+        a, x, y = v.dynamic_parameters['a'], v.states['x'], v.states['y']
+        v.d_states['y'] = a * y - 0.5 * y * x
+        v.d_states['x'] = 2.0 * x * y - c * x
+        v.field_outputs['field_x'] = x
+        v.profile_outputs['x_plus_y'] = x + y
+    t = trace.TracedRHS(ode_function, (), {}, {'y': (), 'x': ()}, {'a': ()})
+    assert (t.D, t.P, t.S, t.DQ) == (2, 1, 1, 0)            # the captured tensor c became a static parameter
+    src = t.cuda_source()
+    for piece in ('struct RhsTraced', 'static void f(', 'static void jac(', 'static void vjp(', 'static void out_vjp('):
+        assert piece in src, piece
+    rid = t.plugin_id(num_stages=4, implicit=False, fp64=True, kind=0)
+    assert rid >= 1000                                       # OZ_RHS_PLUGIN_BASE in include/ozone_b200.h
+    assert t.plugin_id(num_stages=4, implicit=False, fp64=True, kind=0) == rid       # cached: one registration
