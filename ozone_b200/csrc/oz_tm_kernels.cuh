@@ -27,6 +27,9 @@ constexpr bool use_reg_solve() {
 
 // Occupancy targets (threads per block, minimum resident blocks per SM) per kernel flavour.  Implicit
 // kernels that solve in registers run 64-thread blocks; the second number caps registers per thread.
+#ifndef OZ_IMPL_BLOCK   /* threads per block of the register-solve implicit kernels */
+#define OZ_IMPL_BLOCK 64
+#endif
 #ifndef OZ_MB_IMPL_FWD
 #define OZ_MB_IMPL_FWD 4
 #endif
@@ -41,7 +44,7 @@ constexpr bool use_reg_solve() {
 #endif
 template <class R, int S, typename T, bool IMPL>
 constexpr int lb_threads() {
-    return (IMPL && use_reg_solve<R, S, T>()) ? 64 : 128;
+    return (IMPL && use_reg_solve<R, S, T>()) ? OZ_IMPL_BLOCK : 128;
 }
 template <class R, int S, typename T, bool IMPL, bool ADJ>
 constexpr int lb_blocks() {

@@ -22,7 +22,7 @@ int pick_block(size_t* smem) {
         return 128;
     } else if constexpr (use_reg_solve<R, S, T>()) {
         *smem = 0;      // Newton matrix lives in registers
-        return 64;      // many small blocks: ~200 registers per thread, short tail on 148 SMs
+        return OZ_IMPL_BLOCK;      // many small blocks: ~200 registers per thread, short tail on 148 SMs
     } else {
         const size_t per = SmemSystem<T, S * R::D>::bytes_per_thread();
         int block = 64;
