@@ -27,6 +27,9 @@ constexpr bool use_reg_solve() {
 
 // Occupancy targets (threads per block, minimum resident blocks per SM) per kernel flavour.  Implicit
 // kernels that solve in registers run 64-thread blocks; the second number caps registers per thread.
+#ifndef OZ_ADJ_UNROLL   /* explicit reverse sweep: step-loop unroll factor (lets the compiler rename instead of rotating registers) */
+#define OZ_ADJ_UNROLL 2
+#endif
 #ifndef OZ_IMPL_BLOCK   /* threads per block of the register-solve implicit kernels */
 #define OZ_IMPL_BLOCK 64
 #endif
@@ -767,12 +770,14 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         // y_k is fetched one iteration ahead so that its load latency overlaps the previous step's arithmetic:
         // into registers for explicit methods, as an L1 prefetch for implicit ones (no registers to spare there)
         T ynext[D];
+        constexpr int kStepUnroll = IMPL ? 1 : OZ_ADJ_UNROLL;
         // row of y_k: the stored history, or this segment's recomputed rows (row k - lo of ws.seg)
         const T* yrow = (use_seg ? ws.seg + (long long)(ni - 1) * DN : a.hist + (long long)(lo + ni - 1) * DN) + i;
         if constexpr (PRELOAD) {
 #pragma unroll
             for (int c = 0; c < D; ++c) ynext[c] = use_seg ? yrow[c * N] : __ldg(yrow + c * N);
         }
+#pragma unroll kStepUnroll
         for (int k = lo + ni - 1; k >= lo; --k) {
             if constexpr (IMPL) {
                 // implicit steps are long and register-starved: rebuild the offsets here rather than keep seven
