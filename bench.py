@@ -27,6 +27,8 @@ import numpy as np
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+# which CUDA library the run loads: the in-tree build unless OZONE_B200_LIB points elsewhere (A/B experiments only)
+LIB_NOTE = os.environ.get('OZONE_B200_LIB') or 'ozone_b200/liboz_b200.so (in-tree build)'
 
 # name: dict(kind, rhs, method, N per GPU, nt, horizon, dtype)
 WORKLOADS = {
@@ -44,6 +46,25 @@ WORKLOADS = {
     'lunar_ascent_gl6_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='GaussLegendre6', N=16384, nt=101, T=0.1),
 }
 DEFAULT_WORKLOAD = 'van_der_pol_gl6_tm_adjoint_N65536_nt40'
+STATE_SIZE = {'van_der_pol': 3, 'lotka_volterra': 2, 'lunar_ascent': 7}     # packed state components per trajectory
+# compact entries of the default bench line (one short run each): the other BASELINE configs, driver-timed
+OTHER_WORKLOADS = ('lotka_volterra_rk4_tm_adjoint_N1M_nt101', 'diffusion_reaction_rk4_checkpoints_nx1M_n1024',
+                   'lunar_ascent_rk4_collocation_N16384_nt101')
+
+
+def workload_config(name, wl, world, newton_tol):
+    """The `config` object BOTH arms print, identical for the same command line, so the two lines compare field by field.
+    What is specific to an arm (sampling of the CPU run, solver statistics of the GPU run) is printed beside it."""
+    d = wl.get('nx') if wl['kind'] == 'grid' else STATE_SIZE[wl['rhs']]
+    if wl['kind'] == 'grid':
+        par = (f'spatial slabs x{world} (halo exchange between ranks)' if wl.get('sharded') else
+               'replicas only (one grid per GPU); the spatial shard is timed by the ..._sharded workload')
+    else:
+        par = f'trajectory-batch x{world}'
+    return {'workload': name, 'rhs': wl['rhs'], 'method': wl['method'], 'approach': wl['kind'],
+            'trajectories_per_gpu': wl['N'], 'num_times': wl['nt'], 'state_size': d, 'newton_tol': newton_tol,
+            'l2': 'GPU arm: flushed (256 MiB write) between timed steps', 'parallelism': par}
+
 
 ASCENT_IC = np.array([0.061663494666509, 0.055249439788994, -1.004110522066614, -0.465976472038572,
                       -0.416909510597800, -0.084973690970470, 11846.599614336959 / 15103.])
@@ -147,7 +168,6 @@ def cpu_port_throughput(wl, cores, units_per_core, repeats=1):
     """Time the oracle on `cores` processes, each working on `units_per_core` trajectories (or, for
     the grid workload, a grid of that many cells and 64 steps).  Returns (state-steps/s, sample, seconds)."""
     import multiprocessing as mp
-    from ozone_b200 import _native as nat
     jobs = []
     w = dict(wl)
     if wl['rhs'] == 'diffusion_reaction':
@@ -156,7 +176,7 @@ def cpu_port_throughput(wl, cores, units_per_core, repeats=1):
         per_job = d * n
         what = f'{cores} processes x one {units_per_core}-cell grid, 64 steps'
     else:
-        d = nat.rhs_info(nat.RHS_IDS[wl['rhs']])['d']
+        d = STATE_SIZE[wl['rhs']]
         n = wl['nt'] - 1
         per_job = units_per_core * d * n
         what = f'{cores} processes x {units_per_core} trajectories'
@@ -203,7 +223,8 @@ def run_reference(args, rank, world):
         'impl': 'reference', 'metric': 'state-steps/sec (fwd+adjoint)', 'value': value, 'unit': 'state-steps/s',
         'n_gpus': args.gpus, 'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': 1e3 * t_all / args.steps,
         'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-        'config': {'workload': args.workload, 'note': f'each step is a bounded sample of the workload ({sample})'},
+        'config': workload_config(args.workload, wl, world, args.newton_tol),
+        'sampling': f'same workload, sampled: each step is a bounded sample ({sample})',
         'cpu_baseline': {'value': value, 'unit': 'state-steps/s', 'cores': cores, 'kind': 'port', 'sample': sample},
         'e2e': {'value': value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
         'gpu_launches': 0,
@@ -215,7 +236,7 @@ def run_reference(args, rank, world):
 class Runner:
     """One workload on one rank: device-resident step (fwd, adj timed separately) and e2e step."""
 
-    def __init__(self, wl, name, rank, dev, args):
+    def __init__(self, wl, name, rank, dev, args, e2e=True):
         import torch
         from ozone_b200 import engine
         from ozone_b200.glms import get_integration_method
@@ -258,12 +279,12 @@ class Runner:
         self.host_out = {k: torch.empty_like(g, device='cpu').pin_memory() for k, g in plan.grad.items() if g is not None}
         self.obj = plan.field if self.kind == 'grid' else plan.final[-1]
         self.host_obj = torch.empty_like(self.obj, device='cpu').pin_memory()
-        self.e2e_inputs = ('h', 'p')
+        self.e2e_inputs = tuple(k for k in ('y0', 'h', 'p', 'th') if k in self.host)      # every input crosses the link each step
         self.h2d = sum(self.host[k].numel() * self.w for k in self.e2e_inputs)
         self.d2h = sum(v.numel() * self.w for v in self.host_out.values()) + self.host_obj.numel() * self.w
         self.launches = plan.launches_forward + plan.launches_adjoint
         self.pipe = None
-        if self.kind == 'tm':      # e2e leg: host-resident batch in sub-batches on their own streams (copy / compute overlap)
+        if self.kind == 'tm' and e2e:      # e2e leg: host-resident batch in sub-batches on their own streams (copy / compute overlap)
             self.pipe = engine.PipelinedTmSolve(spec, slices=args.e2e_slices, device=dev, grads=want, cotangents=cot,
                                                 upload=self.e2e_inputs)
             self.pipe.set_host_inputs(**self.host)
@@ -368,6 +389,85 @@ class Runner:
         return fwd, adj
 
 
+FP64_BOUND_NOTE = {
+    'tm_implicit': ('implicit Gauss-Legendre + Newton is FP64-ALU bound, not HBM bound (about 1 kflop per 100 compulsory bytes; '
+                    'ncu: fp64 pipe ~53 % busy vs DRAM ~12 %): frac is executed FP64 flops over the measured FMA peak, the HBM '
+                    'fractions the metric asks for are under roofline.hbm'),
+    'grid': ('one exponential per cell and stage: the fused steps are FP64-bound (ncu: fp64 pipe ~55 %, state L2-resident); HBM '
+             'fractions under roofline.hbm'),
+}
+
+
+def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
+    """roofline object of the bench line: the dominant kernel against the resource that bounds it.
+    HBM-bound families: algorithmic bytes / launch time over the measured copy bandwidth.
+    FP64-bound families (implicit time marching, the grid in fp64): executed FP64 flops per launch (ncu count of the
+    shipped build, profiles/traffic.json) / launch time over the FMA peak measured in this run; the HBM fractions stay
+    available under 'hbm' because the metric asks for them."""
+    fwd_b, adj_b = run.algorithmic_bytes()
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:
+        pass
+    peak = float(peaks.get('hbm_gbs', 6650.0))
+    names = {'tm': ('tm_adjoint_kernel', 'tm_forward_kernel'), 'picard': ('tm_adjoint_kernel', 'picard_kernel'),
+             'grid': ('pde_adjoint_step_kernel (+ replayed pde_step_kernel)', 'pde_step_kernel'),
+             'colloc': ('colloc_vjp_kernel', 'colloc_residual_kernel')}[run.kind]
+    traffic = {}
+    try:
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(workload, {})
+    except Exception:
+        pass
+
+    def hbm_entry(name, nbytes, secs):
+        ach = nbytes / secs / 1e9
+        return {'kernel': name, 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
+                'frac_of_nominal_8000': ach / 8000.0, 'traffic': traffic.get(name.split(' ')[0]),
+                'algorithmic_bytes_per_launch': nbytes, 'avg_launch_ms': secs * 1e3}
+
+    adj_e, fwd_e = hbm_entry(names[0], adj_b, adj_s), hbm_entry(names[1], fwd_b, fwd_s)
+    dominant, other = (adj_e, fwd_e) if adj_s >= fwd_s else (fwd_e, adj_e)
+    fma = {}
+    if probe:
+        try:
+            fma = {'f64': run.engine.measure_fma_peak(torch.float64, dev), 'f32': run.engine.measure_fma_peak(torch.float32, dev)}
+        except Exception as exc:                                            # never let the probe break the bench line
+            fma = {'error': str(exc)}
+    implicit = run.kind == 'tm' and not run.spec.method.explicit
+    fp64_bound = run.w == 8 and (implicit or run.kind == 'grid')
+    flops = traffic.get('fp64_flops_per_launch', {})
+    f64_peak = fma.get('f64') or traffic.get('fp64_peak_tflops_at_capture')
+    roof = None
+    if fp64_bound and f64_peak:
+        fl = flops.get(dominant['kernel'].split(' ')[0])
+        if fl:
+            t = fl / (dominant['avg_launch_ms'] * 1e-3) / 1e12
+            roof = {'bound': 'fp64', 'kernel': dominant['kernel'], 'achieved': t, 'peak': f64_peak, 'unit': 'TFLOP/s',
+                    'frac': t / f64_peak, 'traffic': dominant['traffic'], 'flops_per_launch': fl,
+                    'avg_launch_ms': dominant['avg_launch_ms'], 'flops_source': flops.get('source'),
+                    'peak_source': 'oz_fma_probe (register-resident DFMA loop) timed in this run' if fma.get('f64')
+                    else 'oz_fma_probe at capture time (profiles/traffic.json)',
+                    'note': FP64_BOUND_NOTE['tm_implicit' if implicit else 'grid']}
+            fo = flops.get(other['kernel'].split(' ')[0])
+            if fo:
+                to = fo / (other['avg_launch_ms'] * 1e-3) / 1e12
+                roof['other_kernel'] = {'kernel': other['kernel'], 'achieved': to, 'peak': f64_peak, 'unit': 'TFLOP/s',
+                                        'frac': to / f64_peak, 'avg_launch_ms': other['avg_launch_ms']}
+    if roof is None:
+        roof = dict({'bound': 'hbm'}, **dominant)
+        roof.update({'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6650 GB/s',
+                     'other_kernel': other,
+                     'note': ('FP64-bound family, but no flop count of this build is on file: HBM fraction only' if fp64_bound else
+                              'HBM / FP64 co-limited explicit path (DESIGN.md section 5)')})
+    roof['hbm'] = {'forward': fwd_e, 'reverse': adj_e, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks
+                   else 'fallback 6650 GB/s'}
+    roof['traffic_source'] = traffic.get('source')
+    if fma:
+        roof['fma_peak_measured_tflops'] = fma
+    return roof
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -378,6 +478,9 @@ def main():
     ap.add_argument('--cpu-traj-per-core', type=int, default=None,
                     help='CPU sample size per core (defaults: CPU_SAMPLE / CPU_SAMPLE_REF tables)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-other-workloads', action='store_true', help='skip the compact other_workloads entries of the default line')
+    ap.add_argument('--other-steps', type=int, default=5)
+    ap.add_argument('--trajectories', type=int, default=None, help='override the batch size per GPU (experiments only: the bench line names it)')
     ap.add_argument('--newton-tol', type=float, default=1e-7)
     ap.add_argument('--e2e-slices', type=int, default=6, help='sub-batches (streams) of the end-to-end leg')
     ap.add_argument('--no-e2e-graph', action='store_true', help='enqueue the end-to-end pipeline eagerly (no CUDA graph)')
@@ -403,7 +506,9 @@ def main():
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
 
-    wl = WORKLOADS[args.workload]
+    wl = dict(WORKLOADS[args.workload])
+    if args.trajectories:
+        wl['N'] = args.trajectories
     run = Runner(wl, args.workload, rank, dev, args)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
 
@@ -412,56 +517,92 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    def allreduce_shared(e2e=False):
+    # Gradients of batch-shared inputs (h: 39 scalars for C2) are summed over the ranks.  The all-reduce runs on its own
+    # stream: it overlaps the L2 flush and the next step's forward solve, and the next reverse sweep -- which overwrites
+    # the buffer -- waits for it.  The timed total ends when the LAST all-reduce has completed (tail added below), so
+    # every collective is inside the measurement; only its launch latency is off the kernels' critical path.
+    comm = torch.cuda.Stream(device=dev) if world > 1 else None
+    pending = [None]
+
+    def allreduce_shared(r, e2e=False):
         if world == 1:
             return
-        if e2e and run.pipe is not None:      # PipelinedTmSolve all-reduces its summed shared gradients itself
+        if e2e and r.pipe is not None:        # PipelinedTmSolve all-reduces its summed shared gradients itself
             return
-        g = run.shared_grad()
-        if g is not None:
+        g = r.shared_grad()
+        if g is None:
+            return
+        ready = torch.cuda.Event()
+        ready.record()
+        comm.wait_event(ready)
+        with torch.cuda.stream(comm):
             dist.all_reduce(g)
+            done = torch.cuda.Event()
+            done.record(comm)
+        pending[0] = done
+
+    def join_comm():
+        if pending[0] is not None:
+            torch.cuda.current_stream().wait_event(pending[0])
+            pending[0] = None
 
     ev = lambda: torch.cuda.Event(enable_timing=True)
 
-    def device_step(times):
+    def device_step(r, times):
         flush.fill_(rank & 0xff)
         e0, e1, e2 = ev(), ev(), ev()
-        e0.record(); run.forward(); e1.record(); run.adjoint(); allreduce_shared(); e2.record()
+        e0.record(); r.forward(); e1.record()
+        join_comm()                           # the previous step's all-reduce still owns the shared-gradient buffer
+        r.adjoint(); e2.record()
+        allreduce_shared(r)
         times.append((e0, e1, e2))
 
-    def e2e_step(times):
+    def e2e_step(r, times):
         flush.fill_(rank & 0xff)
         e0, e1 = ev(), ev()
         e0.record()
-        run.e2e()
-        allreduce_shared(e2e=True)
-        run.e2e_readback()
+        r.e2e()
+        allreduce_shared(r, e2e=True)
+        join_comm()
+        r.e2e_readback()
         e1.record()
         times.append((e0, e1))
 
+    def timed_device_steps(r, warmup, steps):
+        """-> (sum of forward ms, sum of reverse ms incl. the tail until the last all-reduce is done, wall ms)"""
+        for _ in range(warmup):
+            device_step(r, [])
+        join_comm()
+        barrier()
+        times = []
+        t0 = time.perf_counter()
+        for _ in range(steps):
+            device_step(r, times)
+        tail0, tail1 = ev(), ev()
+        tail0.record(); join_comm(); tail1.record()
+        barrier()
+        wall = time.perf_counter() - t0
+        fwd = float(np.sum([a.elapsed_time(b) for a, b, _ in times]))
+        adj = float(np.sum([b.elapsed_time(c) for _, b, c in times])) + tail0.elapsed_time(tail1)
+        return fwd, adj, wall * 1e3
+
     for _ in range(args.warmup):
-        device_step([])
+        device_step(run, [])
+    join_comm()
     barrier()
     sampler = ClockSampler(local_rank)
     if rank == 0:
         sampler.start()
-    times = []
-    barrier()
-    t_wall0 = time.perf_counter()
-    for _ in range(args.steps):
-        device_step(times)
-    barrier()
-    t_wall = time.perf_counter() - t_wall0
-    fwd_ms = [a.elapsed_time(b) for a, b, _ in times]
-    adj_ms = [b.elapsed_time(c) for _, b, c in times]
-    step_ms = float(np.sum(fwd_ms) + np.sum(adj_ms))
+    fwd_sum, adj_sum, wall_ms = timed_device_steps(run, 0, args.steps)
+    step_ms = fwd_sum + adj_sum
+    t_wall = wall_ms * 1e-3
 
     for _ in range(args.warmup):
-        e2e_step([])
+        e2e_step(run, [])
     barrier()
     etimes = []
     for _ in range(args.steps):
-        e2e_step(etimes)
+        e2e_step(run, etimes)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
     e2e_ms = float(np.sum([a.elapsed_time(b) for a, b in etimes]))
@@ -476,7 +617,7 @@ def main():
         extra_cfg['not_converged'] = int((run.pic['status'] != 0).sum().item())
         extra_cfg['mean_sweeps'] = float(run.pic['iters'].double().mean().item())
 
-    tot = torch.tensor([step_ms, e2e_ms, float(np.sum(fwd_ms)), float(np.sum(adj_ms))], dtype=torch.float64, device=dev)
+    tot = torch.tensor([step_ms, e2e_ms, fwd_sum, adj_sum], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     step_ms, e2e_ms, fwd_tot, adj_tot = tot.tolist()
@@ -485,61 +626,35 @@ def main():
     value = units_per_step * args.steps / (step_ms * 1e-3)
     e2e_value = units_per_step * args.steps / (e2e_ms * 1e-3)
 
+    # the other BASELINE configs, a few steps each, so that the driver-run record covers more than the headline
+    others = []
+    if args.workload == DEFAULT_WORKLOAD and not args.no_other_workloads and not args.trajectories:
+        for name in OTHER_WORKLOADS:
+            owl = dict(WORKLOADS[name])
+            try:
+                orun = Runner(owl, name, rank, dev, args, e2e=False)
+                of, oa, _ = timed_device_steps(orun, 3, args.other_steps)
+                t = torch.tensor([of, oa], dtype=torch.float64, device=dev)
+                if world > 1:
+                    dist.all_reduce(t, op=dist.ReduceOp.MAX)
+                of, oa = t.tolist()
+                if rank == 0:
+                    r = roofline_of(orun, name, of / args.other_steps * 1e-3, oa / args.other_steps * 1e-3, torch, dev, probe=False)
+                    others.append({'workload': name, 'value': world * orun.units * args.other_steps / ((of + oa) * 1e-3),
+                                   'unit': 'state-steps/s', 'steps': args.other_steps, 'fwd_ms': of / args.other_steps,
+                                   'adj_ms': oa / args.other_steps, 'bound': r['bound'], 'frac': r['frac'],
+                                   'hbm_frac_fwd_adj': [r['hbm']['forward']['frac'], r['hbm']['reverse']['frac']],
+                                   'parallelism': workload_config(name, owl, world, args.newton_tol)['parallelism']})
+                del orun
+                torch.cuda.empty_cache()
+            except Exception as exc:            # noqa: BLE001 -- an extra must never cost the headline line
+                if rank == 0:
+                    others.append({'workload': name, 'error': repr(exc)[:200]})
+
     if rank == 0:
-        fwd_b, adj_b = run.algorithmic_bytes()
         adj_avg_s = adj_tot / args.steps * 1e-3
         fwd_avg_s = fwd_tot / args.steps * 1e-3
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
-        except Exception:
-            pass
-        peak = float(peaks.get('hbm_gbs', 6650.0))
-        names = {'tm': ('tm_adjoint_kernel', 'tm_forward_kernel'), 'picard': ('tm_adjoint_kernel', 'picard_kernel'),
-                 'grid': ('pde_adjoint_step_kernel (+ replayed pde_step_kernel)', 'pde_step_kernel'),
-                 'colloc': ('colloc_vjp_kernel', 'colloc_residual_kernel')}[run.kind]
-        traffic = {}
-        try:
-            traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(args.workload, {})
-        except Exception:
-            pass
-
-        def kernel_entry(name, nbytes, secs):
-            ach = nbytes / secs / 1e9
-            return {'kernel': name, 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
-                    'traffic': traffic.get(name.split(' ')[0]), 'algorithmic_bytes_per_launch': nbytes,
-                    'avg_launch_ms': secs * 1e3}
-
-        adj_e, fwd_e = kernel_entry(names[0], adj_b, adj_avg_s), kernel_entry(names[1], fwd_b, fwd_avg_s)
-        dominant, other = (adj_e, fwd_e) if adj_avg_s >= fwd_avg_s else (fwd_e, adj_e)
-        if run.kind == 'tm' and not run.spec.method.explicit:
-            note = ('implicit Gauss-Legendre + Newton is FP64-ALU bound, not HBM bound (about 1 kflop per 100 compulsory '
-                    'bytes, ncu: fp64 pipe 54 % busy vs DRAM 9 %); the HBM fraction is reported because the metric asks for it, the FP64 '
-                    'fraction under roofline.fp64')
-        elif run.kind == 'grid':
-            note = 'one exponential per cell and stage: the fused steps are FP64-bound (ncu: fp64 pipe 55 %, state L2-resident)'
-        else:
-            note = 'HBM / FP64 co-limited explicit path (DESIGN.md section 5)'
-        roof = dict({'bound': 'hbm'}, **dominant)
-        roof['frac_of_nominal_8000'] = dominant['achieved'] / 8000.0       # the north star's denominator
-        try:
-            roof['fma_peak_measured_tflops'] = {'f64': run.engine.measure_fma_peak(torch.float64, dev),
-                                                'f32': run.engine.measure_fma_peak(torch.float32, dev)}
-        except Exception as exc:                                            # never let the probe break the bench line
-            roof['fma_peak_measured_tflops'] = {'error': str(exc)}
-        # FP64-bound kernels: executed FP64 flops per launch (counted by ncu, profiles/traffic.json) over the live launch
-        # time, against the FMA peak measured above
-        flops = traffic.get('fp64_flops_per_launch', {})
-        f64_peak = roof['fma_peak_measured_tflops'].get('f64')
-        if flops and f64_peak and run.w == 8:
-            for entry in (roof, other):
-                fl = flops.get(entry['kernel'].split(' ')[0])
-                if fl:
-                    t = fl / (entry['avg_launch_ms'] * 1e-3) / 1e12
-                    entry['fp64'] = {'achieved_tflops': t, 'peak_tflops': f64_peak, 'frac': t / f64_peak,
-                                     'flops_per_launch': fl, 'source': flops.get('source')}
-        roof.update({'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6650 GB/s',
-                     'traffic_source': traffic.get('source'), 'other_kernel': other, 'note': note})
+        roof = roofline_of(run, args.workload, fwd_avg_s, adj_avg_s, torch, dev)
         cpu = None
         if not args.no_cpu_baseline:
             cores = os.cpu_count() or 1
@@ -552,11 +667,10 @@ def main():
             'metric': 'state-steps/sec (fwd+adjoint)', 'value': value, 'unit': 'state-steps/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': step_ms / args.steps, 'higher_is_better': True,
             'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if wl.get('fp32') else 'f64', 'data': 'synthetic',
-            'config': dict({'workload': args.workload, 'rhs': wl['rhs'], 'method': wl['method'], 'approach': run.kind,
-                            'trajectories_per_gpu': wl['N'], 'num_times': wl['nt'], 'state_size': run.d,
-                            'newton_tol': args.newton_tol, 'l2': 'flushed (256 MiB write) between timed steps',
-                            'parallelism': f'trajectory-batch x{world}' if run.kind != 'grid' else 'replicas only (bench); '
-                            'spatial shard: see ozone_b200/parallel.py'}, **extra_cfg),
+            'config': workload_config(args.workload, wl, world, args.newton_tol),
+            'solver_stats': extra_cfg,
+            'shared_gradient_allreduce': ('NCCL on a side stream, overlapping the next forward solve; the last one is inside '
+                                          'the timed total') if world > 1 else 'none (1 GPU)',
             'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
                     'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps,
                     'how': (f'engine.PipelinedTmSolve: {args.e2e_slices} sub-batches on their own streams, pinned host buffers, '
@@ -565,7 +679,8 @@ def main():
                             if run.pipe is not None else 'engine plan API, pinned host buffers, one stream')},
             'gpu_launches': args.steps * run.launches,
             'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
-            'wall_ms_timed_loop': t_wall * 1e3,
+            'wall_ms_timed_loop': t_wall * 1e3, 'other_workloads': others,
+            'library': LIB_NOTE,
         }
         print(json.dumps(line), flush=True)
     if world > 1:

@@ -149,6 +149,13 @@ OZ_API int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfie
  * y [d][nodes], p [P][nodes], th [S] or [S][nodes]; dy [d][nodes], prof [NPROF][nodes], field [NFIELD][nodes]. */
 OZ_API int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* p, void* dy, void* prof, void* field);
 
+/* Transposed Jacobians of the profile / field outputs at `nodes` points: the reverse pass of the outputs that
+ * VectorBased.integrate evaluates on a whole history (ozone/integrators/vector_based.py:33-49; csdl differentiates
+ * them as graph nodes).  vprof [NPROF][nodes], vfield [NFIELD][nodes] (NULL = zero) -> y_bar [d][nodes],
+ * p_bar [P][nodes], th_bar [S][nodes]: one gradient per node, the caller sums what is shared.  NULL outputs are skipped. */
+OZ_API int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, const void* p, const void* vprof,
+                          const void* vfield, void* y_bar, void* p_bar, void* th_bar);
+
 /* TimeMarching.integrate: ozone/integrators/time_marching.py:6-59 (loop), :143-245 (stages,
  * explicit and Newton), :247-260 (update), :97-141 (outputs).  With num_inner > 0 it is
  * TimeMarchingUniform.integrate (ozone/integrators/time_marching_uniform.py:7-150): only `ckpt`

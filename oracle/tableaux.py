@@ -78,7 +78,7 @@ def tableau(name):
         raise KeyError(name)
     A = np.atleast_2d(np.asarray(A, dtype=float))
     b = np.asarray(b, dtype=float).reshape(-1)
-    c = A.sum(axis=1)                             # GLMs.py:28  C = A.1
+    c = A.dot(np.ones((A.shape[0], 1))).reshape(-1)   # GLMs.py:29  C = A.dot(ones): the same operation, so the same bits
     explicit = bool(np.linalg.norm(np.tril(A, -1) - A) < 1e-15)   # GLMs.py:37-39
     return A, b, c, explicit
 

@@ -59,6 +59,7 @@ SYMBOLS = {
     'oz_register_rhs_plugin': (C.c_int, [C.c_char_p]),
     'oz_fma_probe': (C.c_double, [C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'oz_rhs_eval': (C.c_int, [_PB, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    'oz_rhs_out_vjp': (C.c_int, [_PB, C.c_int64] + [C.c_void_p] * 7),
     'oz_tm_forward_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_forward': (C.c_int, [_PB]),
     'oz_tm_adjoint_workspace_bytes': (C.c_size_t, [_PB]),

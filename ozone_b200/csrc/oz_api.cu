@@ -1,6 +1,7 @@
 // extern "C" boundary of liboz_b200.so (declared in include/ozone_b200.h).
 #include <cstdarg>
 #include <dlfcn.h>
+#include <atomic>
 #include <mutex>
 #include "oz_plugin.h"
 #include "oz_common.cuh"
@@ -60,12 +61,12 @@ static const RhsInfo kInfo[OZ_RHS_COUNT] = {
 // ---- right-hand sides registered at run time (plugins built by ozone_b200/trace.py) -------------------
 constexpr int kMaxPlugins = 256;
 static oz_plugin_info g_plugins[kMaxPlugins];
-static int g_num_plugins = 0;
+static std::atomic<int> g_num_plugins{0};   // published with release order after the slot is filled: readers take no lock
 static std::mutex g_plugin_mu;
 
 static const oz_plugin_info* plugin_of(int rhs_id) {
     const int slot = rhs_id - OZ_RHS_PLUGIN_BASE;
-    if (slot < 0 || slot >= g_num_plugins) return nullptr;
+    if (slot < 0 || slot >= g_num_plugins.load(std::memory_order_acquire)) return nullptr;
     return &g_plugins[slot];
 }
 static bool known_rhs(int rhs_id) { return (rhs_id >= 0 && rhs_id < OZ_RHS_COUNT) || plugin_of(rhs_id) != nullptr; }
@@ -114,7 +115,8 @@ const char* oz_last_error(void) { return g_err; }
 int oz_register_rhs_plugin(const char* so_path) {
     OZ_REQUIRE(so_path != nullptr, "null plugin path");
     std::lock_guard<std::mutex> lock(g_plugin_mu);
-    OZ_REQUIRE(g_num_plugins < kMaxPlugins, "too many right-hand side plugins (%d)", kMaxPlugins);
+    const int slot = g_num_plugins.load(std::memory_order_relaxed);
+    OZ_REQUIRE(slot < kMaxPlugins, "too many right-hand side plugins (%d)", kMaxPlugins);
     void* handle = dlopen(so_path, RTLD_NOW | RTLD_LOCAL);
     OZ_REQUIRE(handle != nullptr, "cannot load plugin %s: %s", so_path, dlerror());
     auto describe = (void (*)(oz_plugin_info*))dlsym(handle, "oz_plugin_describe");
@@ -124,9 +126,10 @@ int oz_register_rhs_plugin(const char* so_path) {
     describe(&info);
     OZ_REQUIRE(info.abi == OZ_PLUGIN_ABI, "plugin %s was built for plugin ABI %d, this library speaks %d", so_path, info.abi,
                OZ_PLUGIN_ABI);
-    OZ_REQUIRE(info.tm && info.d >= 1, "plugin %s is incomplete", so_path);
-    g_plugins[g_num_plugins] = info;
-    return OZ_RHS_PLUGIN_BASE + g_num_plugins++;
+    OZ_REQUIRE(info.tm && info.picard && info.colloc && info.d >= 1, "plugin %s is incomplete", so_path);
+    g_plugins[slot] = info;
+    g_num_plugins.store(slot + 1, std::memory_order_release);
+    return OZ_RHS_PLUGIN_BASE + slot;
 }
 
 int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfield, int* kind) {
@@ -147,8 +150,20 @@ int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* 
     OZ_REQUIRE(pb != nullptr, "null problem descriptor");
     OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(nodes >= 0, "negative node count");
-    EvalArgs ev{nodes, y, p, dy, prof, field};
+    OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
+    EvalArgs ev{nodes, y, p, dy, prof, field, nullptr, nullptr, nullptr, nullptr, nullptr};
     return route(pb, TM_RHS_EVAL, nullptr, &ev);
+}
+
+int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, const void* p, const void* vprof, const void* vfield,
+                   void* y_bar, void* p_bar, void* th_bar) {
+    OZ_REQUIRE(pb != nullptr, "null problem descriptor");
+    OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
+    OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
+    OZ_REQUIRE(nodes >= 0, "negative node count");
+    OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "output VJPs are defined for per-trajectory right-hand sides");
+    EvalArgs ev{nodes, y, p, nullptr, nullptr, nullptr, vprof, vfield, y_bar, p_bar, th_bar};
+    return route(pb, TM_OUT_VJP, nullptr, &ev);
 }
 
 size_t oz_tm_forward_workspace_bytes(const oz_problem* pb) {

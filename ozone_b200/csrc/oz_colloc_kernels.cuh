@@ -224,15 +224,30 @@ __global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_vjp_kernel(const Col
     if (a.th_bar) {
 #pragma unroll
         for (int c = 0; c < DM::SP; ++c) {
-            const T s = warp_sum(valid ? tb[c] : T(0));
-            if (lane == 0) a.ws_th[((long long)c * a.nchunks + chunk_id) * a.W + wx] = s;
+            if (a.th_shared) {
+                const T s = warp_sum(valid ? tb[c] : T(0));
+                if (lane == 0) a.ws_th[((long long)c * a.nchunks + chunk_id) * a.W + wx] = s;
+            } else if (valid) {   // per-trajectory static parameter: one partial per (time chunk, trajectory)
+                a.ws_th[((long long)c * a.nchunks + chunk_id) * N + i] = tb[c];
+            }
         }
     }
 }
 
-// per-trajectory th_bar: sum the nchunks partial rows (lane-level partials kept per trajectory)
+// th_bar[c][i] = sum over the time chunks of one trajectory's partials (fixed order)
+template <typename T>
+__global__ void __launch_bounds__(256) sum_chunks_kernel(const T* __restrict__ part, int nchunks, long long N,
+                                                         T* __restrict__ out) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= N) return;
+    const long long c = blockIdx.y;
+    T acc = T(0);
+    for (int q = 0; q < nchunks; ++q) acc += part[(c * nchunks + q) * N + i];
+    out[c * N + i] = acc;
+}
+
 struct ColWs {
-    long long W, rows_h, rows_p, rows_th, off_h, off_p, off_th, total;
+    long long W, rows_h, rows_p, rows_th, th_elems, off_h, off_p, off_th, total;
     int chunk, nchunks;
 };
 
@@ -246,29 +261,13 @@ inline ColWs colloc_ws_layout(const oz_problem* pb) {
     w.rows_h = (pb->h_shared && pb->h_bar) ? pb->n : 0;
     w.rows_p = (pb->p_shared && pb->p_bar) ? (long long)(pb->n + 1) * R::P : 0;
     w.rows_th = pb->th_bar ? (long long)R::S : 0;  // always reduced over the time chunks
+    // shared th: one partial per (chunk, warp); per-trajectory th: one per (chunk, trajectory)
+    w.th_elems = w.rows_th * w.nchunks * (pb->th_shared ? w.W : (long long)pb->N);
     w.off_h = 0;
     w.off_p = w.off_h + w.rows_h * w.W;
     w.off_th = w.off_p + w.rows_p * w.W;
-    w.total = w.off_th + w.rows_th * w.nchunks * w.W;
+    w.total = w.off_th + w.th_elems;
     return w;
-}
-
-// th_bar per trajectory is not reducible by the row reducer (it keeps the trajectory axis), so for
-// per-trajectory static parameters the partials are lane-level: handled by colloc_th_kernel.
-template <typename T>
-__global__ void __launch_bounds__(256) reduce_rows_strided_kernel(const T* __restrict__ part, long long W, T* __restrict__ out) {
-    // identical to reduce_rows_kernel; kept separate so the collocation path owns its reducers
-    __shared__ T sm[256];
-    const long long row = blockIdx.x;
-    T acc = T(0);
-    for (long long w = threadIdx.x; w < W; w += 256) acc += part[row * W + w];
-    sm[threadIdx.x] = acc;
-    __syncthreads();
-    for (int s = 128; s > 0; s >>= 1) {
-        if (threadIdx.x < s) sm[threadIdx.x] += sm[threadIdx.x + s];
-        __syncthreads();
-    }
-    if (threadIdx.x == 0) out[row] = sm[0];
 }
 
 template <class R, typename T, int S>
@@ -307,8 +306,6 @@ int run_colloc(const oz_problem* pb, int mode, size_t* ws_bytes, const void* Y, 
         OZ_CUDA_CHECK(cudaGetLastError());
         return 0;
     }
-    OZ_REQUIRE(pb->th_shared || !pb->th_bar || R::S == 0,
-               "collocation VJP: gradients of per-trajectory static parameters are not implemented");
     OZ_REQUIRE(mu1 && mu2, "multipliers mu1, mu2 are required");
     OZ_REQUIRE((size_t)w.total * sizeof(T) <= pb->ws_bytes && (w.total == 0 || pb->ws),
                "collocation VJP workspace too small: need %zu bytes, got %zu", (size_t)w.total * sizeof(T), pb->ws_bytes);
@@ -326,10 +323,13 @@ int run_colloc(const oz_problem* pb, int mode, size_t* ws_bytes, const void* Y, 
     a.ws_th = ws + w.off_th;
     colloc_vjp_kernel<R, T, S><<<dim3(gx, w.nchunks), 128, 0, stream>>>(a);
     OZ_CUDA_CHECK(cudaGetLastError());
-    if (w.rows_h) reduce_rows_strided_kernel<T><<<(unsigned)w.rows_h, 256, 0, stream>>>(a.ws_h, w.W, a.h_bar);
-    if (w.rows_p) reduce_rows_strided_kernel<T><<<(unsigned)w.rows_p, 256, 0, stream>>>(a.ws_p, w.W, a.p_bar);
-    if (w.rows_th)
-        reduce_rows_strided_kernel<T><<<(unsigned)w.rows_th, 256, 0, stream>>>(a.ws_th, w.W * w.nchunks, a.th_bar);
+    if (w.rows_h) reduce_rows_kernel<T><<<(unsigned)w.rows_h, 256, 0, stream>>>(a.ws_h, w.W, a.h_bar);
+    if (w.rows_p) reduce_rows_kernel<T><<<(unsigned)w.rows_p, 256, 0, stream>>>(a.ws_p, w.W, a.p_bar);
+    if (w.rows_th && pb->th_shared)
+        reduce_rows_kernel<T><<<(unsigned)w.rows_th, 256, 0, stream>>>(a.ws_th, w.W * w.nchunks, a.th_bar);
+    if (w.rows_th && !pb->th_shared)
+        sum_chunks_kernel<T><<<dim3((unsigned)((pb->N + 255) / 256), (unsigned)w.rows_th), 256, 0, stream>>>(a.ws_th, w.nchunks,
+                                                                                                           pb->N, a.th_bar);
     OZ_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

@@ -39,13 +39,21 @@ struct PicardArgs {
 
 // C > 0: the lane's `chunk` of steps is the compile-time constant C and A.hF stays in REGISTERS (half the shared
 // memory per trajectory -> twice the resident warps, no LDS/STS for it); C = 0: any chunk, A.hF in shared memory.
+#ifndef OZ_PICARD_GS_MAX_D   /* compile-time per-component Gauss-Seidel blocks for right-hand sides with up to this many states */
+#define OZ_PICARD_GS_MAX_D 3
+#endif
+
 template <class R, int S>
 inline size_t picard_elems_per_lane(int chunk, bool af_in_regs) {
     return (size_t)(af_in_regs ? 1 : 2) * chunk * S * R::D + (size_t)chunk * R::D +
            (size_t)(chunk + 1) * AtLeast1<R::P>::value + chunk;
 }
 
-template <class R, typename T, int S, int C>
+// GS = 1: every packed component is its own Gauss-Seidel block (scalar states, the usual case): the block loop is
+// unrolled with compile-time bounds, so inside block b only component b of f, of A.hF and of the running sum is
+// computed at all (round 1 evaluated everything for every block and threw the other components away).
+// GS = 0: blocks come from the argument block; the products and scans of foreign components are skipped at run time.
+template <class R, typename T, int S, int C, int GS = 0>
 __global__ void __launch_bounds__(C > 0 ? 512 : 256) picard_kernel(const PicardArgs<T> a) {
     using DM = Dims<R>;
     constexpr int D = DM::D, P = DM::P;
@@ -97,84 +105,112 @@ __global__ void __launch_bounds__(C > 0 ? 512 : 256) picard_kernel(const PicardA
 
     int sweeps = 0, status = 0;
     T off[D];  // exclusive warp prefix of the lane totals (valid after the last scan)
-    for (;;) {
-        T rmax = T(0);
-        for (int b = 0; b < a.nblocks; ++b) {
-            const int lo = a.blk_lo[b], hi = a.blk_lo[b + 1];
-            // ---- pass 1: f at every node of this lane, A.hF and the running B.hF sum
-            T run[D];
 #pragma unroll
-            for (int cc = 0; cc < D; ++cc) run[cc] = T(0);
+    for (int cc = 0; cc < D; ++cc) off[cc] = T(0);
+    // One relaxation of the components [lo, hi).  B >= 0: lo = B, hi = B + 1 are compile-time constants.
+    // Returns this block's residual 2-norm squared and adds the squares of the new iterate to yn2.
+    auto relax_block = [&](auto btag, int lo_rt, int hi_rt, T& yn2) -> T {
+        constexpr int B = decltype(btag)::value;
+        const int lo = B >= 0 ? B : lo_rt, hi = B >= 0 ? B + 1 : hi_rt;
+        // ---- pass 1: f at every node of this lane, A.hF and the running B.hF sum
+        T run[D];
 #pragma unroll
-            for (int q = 0; q < c; ++q) {
-                if (k0 + q >= n) continue;
-                T Y[S][D], F[S][D], ps[S][DM::P1], plo[DM::P1], phi[DM::P1];
-                const T h = LP(hh, q);
+        for (int cc = 0; cc < D; ++cc) run[cc] = T(0);
 #pragma unroll
-                for (int cc = 0; cc < P; ++cc) {
-                    plo[cc] = LP(pp, q * P + cc);
-                    phi[cc] = LP(pp, (q + 1) * P + cc);
-                }
-                stage_params<R, T, S>(tab, plo, phi, ps);
+        for (int q = 0; q < c; ++q) {
+            if (k0 + q >= n) continue;
+            T Y[S][D], F[S][D], ps[S][DM::P1], plo[DM::P1], phi[DM::P1];
+            const T h = LP(hh, q);
 #pragma unroll
-                for (int s = 0; s < S; ++s) {
-#pragma unroll
-                    for (int cc = 0; cc < D; ++cc) Y[s][cc] = LP(Yb, (q * S + s) * D + cc);
-                    R::f(Y[s], ps[s], th, F[s]);
-                }
-#pragma unroll
-                for (int cc = 0; cc < D; ++cc) {
-                    T accb = T(0);
-#pragma unroll
-                    for (int s = 0; s < S; ++s) {
-                        accb += tab.B[s] * F[s][cc];
-                        T acca = T(0);
-#pragma unroll
-                        for (int j = 0; j < S; ++j) acca += tab.a(s, j) * F[j][cc];
-                        af_set(q, s, cc, h * acca);
-                    }
-                    run[cc] += h * accb;
-                    LP(inc, q * D + cc) = run[cc];
-                }
+            for (int cc = 0; cc < P; ++cc) {
+                plo[cc] = LP(pp, q * P + cc);
+                phi[cc] = LP(pp, (q + 1) * P + cc);
             }
-            // ---- exclusive scan of the lane totals across the warp (the (I - V shift)^-1 product)
+            stage_params<R, T, S>(tab, plo, phi, ps);
+#pragma unroll
+            for (int s = 0; s < S; ++s) {
+#pragma unroll
+                for (int cc = 0; cc < D; ++cc) Y[s][cc] = LP(Yb, (q * S + s) * D + cc);
+                R::f(Y[s], ps[s], th, F[s]);
+            }
 #pragma unroll
             for (int cc = 0; cc < D; ++cc) {
-                T v = run[cc];
+                if (cc < lo || cc >= hi) continue;
+                T accb = T(0);
 #pragma unroll
-                for (int o = 1; o < 32; o <<= 1) {
-                    const T u = __shfl_up_sync(0xffffffffu, v, o);
-                    if (lane >= o) v += u;
+                for (int s = 0; s < S; ++s) {
+                    accb += tab.B[s] * F[s][cc];
+                    T acca = T(0);
+#pragma unroll
+                    for (int j = 0; j < S; ++j) acca += tab.a(s, j) * F[j][cc];
+                    af_set(q, s, cc, h * acca);
                 }
-                off[cc] = v - run[cc];
+                run[cc] += h * accb;
+                LP(inc, q * D + cc) = run[cc];
             }
-            // ---- pass 2: stages = A.hF + S_k ; residual and update for the components of this block
-            T rn2 = T(0);
+        }
+        // ---- exclusive scan of the lane totals across the warp (the (I - V shift)^-1 product)
 #pragma unroll
-            for (int q = 0; q < c; ++q) {
-                if (k0 + q >= n) continue;
+        for (int cc = 0; cc < D; ++cc) {
+            if (cc < lo || cc >= hi) continue;
+            T v = run[cc];
 #pragma unroll
-                for (int cc = 0; cc < D; ++cc) {
-                    if (cc < lo || cc >= hi) continue;
-                    const T Sk = y0[cc] + off[cc] + (q > 0 ? LP(inc, (q - 1) * D + cc) : T(0));
+            for (int o = 1; o < 32; o <<= 1) {
+                const T u = __shfl_up_sync(0xffffffffu, v, o);
+                if (lane >= o) v += u;
+            }
+            off[cc] = v - run[cc];
+        }
+        // ---- pass 2: stages = A.hF + S_k ; residual and update for the components of this block
+        T rn2 = T(0);
 #pragma unroll
-                    for (int s = 0; s < S; ++s) {
-                        const T ynew = af_get(q, s, cc) + Sk;
-                        const T r = LP(Yb, (q * S + s) * D + cc) - ynew;
-                        rn2 += r * r;
-                        LP(Yb, (q * S + s) * D + cc) = ynew;
-                    }
+        for (int q = 0; q < c; ++q) {
+            if (k0 + q >= n) continue;
+#pragma unroll
+            for (int cc = 0; cc < D; ++cc) {
+                if (cc < lo || cc >= hi) continue;
+                const T Sk = y0[cc] + off[cc] + (q > 0 ? LP(inc, (q - 1) * D + cc) : T(0));
+#pragma unroll
+                for (int s = 0; s < S; ++s) {
+                    const T ynew = af_get(q, s, cc) + Sk;
+                    const T r = LP(Yb, (q * S + s) * D + cc) - ynew;
+                    rn2 += r * r;
+                    yn2 += ynew * ynew;
+                    LP(Yb, (q * S + s) * D + cc) = ynew;
                 }
             }
-            rn2 = warp_sum(rn2);
-            rmax = fmax(rmax, sqrt(rn2));
-            if (!(rn2 == rn2)) rmax = CUDART_INF;
+        }
+        return rn2;
+    };
+    // Round-off floor of the residual norm.  S_k is a running sum over up to n steps, so two successive iterates that are
+    // both correct to working precision still differ by ~eps sqrt(n) |Y| per entry.  A sweep whose residual is below
+    // 8 eps sqrt(n) ||Y||_2 and no longer halves has converged as far as this precision allows (fp32, n = 100, 800
+    // unknowns of size ~2: floor ~3e-4, above the usual tolerance 1e-4; fp64: ~6e-13, below every tolerance in use).
+    const T eps = sizeof(T) == 8 ? T(1.1102230246251565e-16) : T(5.9604645e-8);
+    const T floor_scale = T(8) * eps * sqrt((T)n);
+    T prev = CUDART_INF;
+    for (;;) {
+        T rmax = T(0), yn2 = T(0);
+        if constexpr (GS == 1) {
+            static_for<0, D>([&](auto bc) {
+                T rn2 = warp_sum(relax_block(bc, 0, 0, yn2));
+                rmax = fmax(rmax, sqrt(rn2));
+                if (!(rn2 == rn2)) rmax = CUDART_INF;
+            });
+        } else {
+            for (int b = 0; b < a.nblocks; ++b) {
+                T rn2 = warp_sum(relax_block(IC<-1>{}, a.blk_lo[b], a.blk_lo[b + 1], yn2));
+                rmax = fmax(rmax, sqrt(rn2));
+                if (!(rn2 == rn2)) rmax = CUDART_INF;
+            }
         }
         if (rmax < a.tol) break;
         if (!(rmax < CUDART_INF)) {
             status |= OZ_STATUS_NONFINITE;
             break;
         }
+        if (rmax > T(0.5) * prev && rmax <= floor_scale * sqrt(warp_sum(yn2))) break;   // stalled on the round-off floor
+        prev = rmax;
         if (sweeps >= a.max_sweeps) {
             status |= OZ_STATUS_NOT_CONVERGED;
             break;
@@ -323,10 +359,21 @@ int run_picard(const oz_problem* pb, const void* guess, double tol, int max_swee
         OZ_CUDA_CHECK(cudaGetLastError());
         return 0;
     };
-    if (regs && creg == 1) return launch(picard_kernel<R, T, S, 1>);
-    if (regs && creg == 2) return launch(picard_kernel<R, T, S, 2>);
-    if (regs && creg == 4) return launch(picard_kernel<R, T, S, 4>);
-    return launch(picard_kernel<R, T, S, 0>);
+    // scalar states relaxed one by one (the reference's block Gauss-Seidel over scalar states): compile-time blocks
+    bool single = nblocks == R::D && R::D >= 2;
+    for (int b = 0; b <= nblocks && single; ++b) single = blk_lo[b] == b;
+    if constexpr (R::D >= 2 && R::D <= OZ_PICARD_GS_MAX_D) {
+        if (single) {
+            if (regs && creg == 1) return launch(picard_kernel<R, T, S, 1, 1>);
+            if (regs && creg == 2) return launch(picard_kernel<R, T, S, 2, 1>);
+            if (regs && creg == 4) return launch(picard_kernel<R, T, S, 4, 1>);
+            return launch(picard_kernel<R, T, S, 0, 1>);
+        }
+    }
+    if (regs && creg == 1) return launch(picard_kernel<R, T, S, 1, 0>);
+    if (regs && creg == 2) return launch(picard_kernel<R, T, S, 2, 0>);
+    if (regs && creg == 4) return launch(picard_kernel<R, T, S, 4, 0>);
+    return launch(picard_kernel<R, T, S, 0, 0>);
 }
 
 template <class R>

@@ -16,7 +16,12 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_plugin_err, sizeof(g_plugin_err), fmt, ap);
     va_end(ap);
 }
-int sm_count() { return 148; }
+int sm_count() {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
+        return 148;
+    return n;
+}
 }  // namespace oz
 
 OZ_INSTANTIATE_TM(oz::RhsTraced, plugin)

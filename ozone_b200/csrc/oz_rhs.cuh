@@ -61,6 +61,10 @@ struct RhsLotkaVolterra {
 struct RhsVanDerPol {
     static constexpr int ID = OZ_RHS_VAN_DER_POL, D = 3, P = 1, S = 0, NPROF = 0, NFIELD = 0;
     static constexpr int DQ = 1;  // J is a pure quadrature: no right-hand side depends on it
+    // which df_r / dy_c can be nonzero (oz_sparse_solve.cuh): x1' = x0 is linear and no derivative depends on J
+    static constexpr unsigned char JP[9] = {1, 1, 0,
+                                            1, 0, 0,
+                                            1, 1, 0};
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T*, T* dy) {
         dy[0] = (T(1) - y[1] * y[1]) * y[0] - y[1] + p[0];

@@ -1,0 +1,201 @@
+// Structure-aware register elimination for the implicit stage systems.
+//
+// The Newton matrix of an implicit Runge-Kutta step, block (i, j) = delta_ij I - h a_ij J_f(Y_j)
+// (ozone/integrators/time_marching.py:235), inherits every structural zero of the right-hand side's
+// Jacobian: a state whose derivative does not depend on itself has a unit diagonal, a derivative that
+// does not depend on state c leaves whole S x S blocks empty.  A functor may declare that pattern,
+//
+//     static constexpr unsigned char JP[D * D] = { ... };      // 0: df_r/dy_c is identically zero
+//
+// and this header turns it into straight-line code: the unknowns are ordered component by component
+// (unit-diagonal components first), the fill-in of Gaussian elimination is worked out at COMPILE time
+// (constexpr), and only entries that can be nonzero exist as registers or cost an instruction.  For
+// Van der Pol under Gauss-Legendre 6 (x1' = x0 is linear) the 6 x 6 elimination collapses into a 3 x 3
+// Schur complement: 27 + 9 products to form it, a dense 3 x 3 solve, 9 products to recover the rest.
+// Functors without JP are treated as dense and get the same arithmetic as the dense register solve.
+//
+// Pivoting: same rule as reg_solve (oz_linalg.cuh).  Each column only TESTS its diagonal against the
+// entries that can be nonzero below it; on failure the caller re-assembles densely and solves in the
+// cold pivoting routine.  The decision depends on the thread's own data only.
+#pragma once
+#include <type_traits>
+#include "oz_linalg.cuh"
+
+namespace oz {
+
+template <int I>
+struct IC {
+    static constexpr int value = I;
+};
+// f(IC<B>{}), f(IC<B+1>{}), ... f(IC<E-1>{}): a loop whose index is a constant expression inside the body
+template <int B, int E, class F>
+OZ_D void static_for(F&& f) {
+    if constexpr (B < E) {
+        f(IC<B>{});
+        static_for<B + 1, E>(f);
+    }
+}
+
+template <class R, class = void>
+struct HasJP : std::false_type {};
+template <class R>
+struct HasJP<R, std::void_t<decltype(R::JP)>> : std::true_type {};
+
+// may df_r / dy_c be nonzero?
+template <class R>
+constexpr bool jac_nz(int r, int c) {
+    if constexpr (HasJP<R>::value)
+        return R::JP[r * R::D + c] != 0;
+    else
+        return true;
+}
+
+template <int M>
+struct Pat {           // 0: structurally zero, 1: exactly one, 2: general
+    unsigned char v[M][M];
+};
+
+template <class R>
+struct StageOrder {
+    static constexpr int DA = (R::D - R::DQ) > 0 ? (R::D - R::DQ) : 1;
+    int pos[DA];       // position of active component r in the elimination order
+};
+template <class R>
+constexpr StageOrder<R> stage_order() {
+    StageOrder<R> o{};
+    constexpr int DA = R::D - R::DQ;
+    int k = 0;
+    for (int r = 0; r < DA; ++r)
+        if (!jac_nz<R>(r, r)) o.pos[r] = k++;     // unit pivots first: they cost no reciprocal and no test
+    for (int r = 0; r < DA; ++r)
+        if (jac_nz<R>(r, r)) o.pos[r] = k++;
+    return o;
+}
+// index of unknown (stage i, active component r) in the ordered system
+template <class R, int S>
+constexpr int uidx(int i, int r) {
+    return stage_order<R>().pos[r] * S + i;
+}
+
+// pattern of the (transposed, if TR) Newton matrix in that order, assuming a full tableau
+template <class R, int S, bool TR>
+constexpr Pat<S*(R::D - R::DQ)> newton_pattern() {
+    constexpr int DA = R::D - R::DQ;
+    Pat<S * DA> p{};
+    for (int i = 0; i < S; ++i)
+        for (int r = 0; r < DA; ++r)
+            for (int j = 0; j < S; ++j)
+                for (int c = 0; c < DA; ++c) {
+                    const int row = uidx<R, S>(i, r), col = uidx<R, S>(j, c);
+                    const unsigned char t = jac_nz<R>(r, c) ? 2 : ((i == j && r == c) ? 1 : 0);
+                    if (TR)
+                        p.v[col][row] = t;
+                    else
+                        p.v[row][col] = t;
+                }
+    return p;
+}
+// pattern after columns 0 .. K-1 have been eliminated (entries below the diagonal of those columns are dead)
+template <int M>
+constexpr Pat<M> eliminated(Pat<M> p, int K) {
+    for (int k = 0; k < K; ++k)
+        for (int r = k + 1; r < M; ++r)
+            if (p.v[r][k])
+                for (int c = k + 1; c < M; ++c)
+                    if (p.v[k][c]) p.v[r][c] = 2;
+    return p;
+}
+// number of entries that ever hold a general value: what the register solve has to keep
+template <class R, int S>
+constexpr int newton_live_entries() {
+    constexpr int M = S * (R::D - R::DQ);
+    const Pat<M> p = eliminated<M>(newton_pattern<R, S, false>(), M);
+    int cnt = 0;
+    for (int r = 0; r < M; ++r)
+        for (int c = 0; c < M; ++c) cnt += p.v[r][c] == 2;
+    return cnt;
+}
+
+template <class R, int S, bool TR, typename T, int K>
+struct SparseElim {
+    static constexpr int M = S * (R::D - R::DQ);
+    static constexpr Pat<M> P = eliminated<M>(newton_pattern<R, S, TR>(), K);
+    OZ_D static void run(T (&a)[M][M], T (&b)[M], bool& ok, bool& bad) {
+        constexpr int pk = P.v[K][K];
+        static_assert(pk != 0, "structurally zero pivot");
+        if constexpr (K < M - 1) {
+            // No early exit: a failed test only raises `bad` and the elimination runs on (its result is then discarded by
+            // the caller).  A branch per column would cut the elimination into basic blocks the instruction scheduler cannot
+            // move work across, and this code is bound by the 8-cycle dependent-issue latency of the FP64 pipe.
+            int lim;
+            if constexpr (pk == 2)
+                lim = mag_bits(T(10) * fabs(a[K][K]));
+            else
+                lim = mag_bits(T(10));
+            static_for<K + 1, M>([&](auto rc) {
+                constexpr int r = decltype(rc)::value;
+                if constexpr (P.v[r][K] != 0) bad = bad | (mag_bits(a[r][K]) > lim);
+            });
+        }
+        T inv = T(1);
+        if constexpr (pk == 2) {
+            const T piv = a[K][K];
+            ok = ok & (fabs(piv) > T(0)) & (fabs(piv) < CUDART_INF);
+            inv = fast_rcp(piv);
+            a[K][K] = inv;
+        }
+        static_for<K + 1, M>([&](auto rc) {
+            constexpr int r = decltype(rc)::value;
+            if constexpr (P.v[r][K] != 0) {
+                T l = a[r][K];
+                if constexpr (pk == 2) l *= inv;
+                static_for<K + 1, M>([&](auto cc) {
+                    constexpr int c = decltype(cc)::value;
+                    if constexpr (P.v[K][c] != 0) {
+                        if constexpr (P.v[r][c] == 2)
+                            a[r][c] -= l * a[K][c];
+                        else if constexpr (P.v[r][c] == 1)
+                            a[r][c] = fma(-l, a[K][c], T(1));
+                        else
+                            a[r][c] = -(l * a[K][c]);
+                    }
+                });
+                b[r] -= l * b[K];
+            }
+        });
+        if constexpr (K + 1 < M) SparseElim<R, S, TR, T, K + 1>::run(a, b, ok, bad);
+    }
+};
+
+template <class R, int S, bool TR, typename T, int Rr>
+struct SparseBack {
+    static constexpr int M = S * (R::D - R::DQ);
+    static constexpr Pat<M> P = eliminated<M>(newton_pattern<R, S, TR>(), M);
+    OZ_D static void run(T (&a)[M][M], T (&b)[M]) {
+        // highest column first (see RegBack): the unknown found last enters last
+        T acc = b[Rr];
+        static_for<0, M - 1 - Rr>([&](auto kc) {
+            constexpr int c = M - 1 - decltype(kc)::value;
+            if constexpr (P.v[Rr][c] != 0) acc -= a[Rr][c] * b[c];
+        });
+        if constexpr (P.v[Rr][Rr] == 2)
+            b[Rr] = acc * a[Rr][Rr];
+        else
+            b[Rr] = acc;
+        if constexpr (Rr > 0) SparseBack<R, S, TR, T, Rr - 1>::run(a, b);
+    }
+};
+
+// Entries of `a` whose pattern is 0 or 1 are never read: the caller stores only the general ones (newton_pattern == 2).
+// Returns 0 (solved, b = solution in uidx order), 1 (zero / non-finite pivot) or 2 (a column failed the threshold
+// test: assemble densely and use finish_with_pivoting).
+template <class R, int S, bool TR, typename T>
+OZ_D int sparse_solve(T (&a)[S * (R::D - R::DQ)][S * (R::D - R::DQ)], T (&b)[S * (R::D - R::DQ)]) {
+    constexpr int M = S * (R::D - R::DQ);
+    bool ok = true, bad = false;
+    SparseElim<R, S, TR, T, 0>::run(a, b, ok, bad);
+    SparseBack<R, S, TR, T, M - 1>::run(a, b);
+    return bad ? 2 : (ok ? 0 : 1);
+}
+
+}  // namespace oz

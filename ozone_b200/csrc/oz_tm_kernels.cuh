@@ -7,6 +7,7 @@
 #pragma once
 #include "oz_common.cuh"
 #include "oz_linalg.cuh"
+#include "oz_sparse_solve.cuh"
 
 namespace oz {
 
@@ -30,6 +31,9 @@ constexpr bool use_reg_solve() {
 #ifndef OZ_ADJ_UNROLL   /* explicit reverse sweep: step-loop unroll factor (lets the compiler rename instead of rotating registers) */
 #define OZ_ADJ_UNROLL 2
 #endif
+#ifndef OZ_SPARSE_SOLVE   /* 1: structure-aware elimination (oz_sparse_solve.cuh); 0: dense register elimination (A/B baseline) */
+#define OZ_SPARSE_SOLVE 1
+#endif
 #ifndef OZ_IMPL_BLOCK   /* threads per block of the register-solve implicit kernels */
 #define OZ_IMPL_BLOCK 64
 #endif
@@ -38,6 +42,12 @@ constexpr bool use_reg_solve() {
 #endif
 #ifndef OZ_MB_IMPL_ADJ
 #define OZ_MB_IMPL_ADJ 4
+#endif
+#ifndef OZ_MB_IMPL_ADJ_SPARSE   /* reverse sweep of a system whose Newton matrix keeps few entries (oz_sparse_solve.cuh): 128 registers */
+#define OZ_MB_IMPL_ADJ_SPARSE 8
+#endif
+#ifndef OZ_SPARSE_LIVE_LIMIT    /* "few": at most this many general entries after fill-in (Van der Pol / Gauss-Legendre 6 has 27, a dense 6 x 6 has 36) */
+#define OZ_SPARSE_LIVE_LIMIT 30
 #endif
 #ifndef OZ_MB_EXPL_ADJ_F64   /* explicit reverse sweep, fp64: 128 registers (5 blocks = 96 registers spills the preloads) */
 #define OZ_MB_EXPL_ADJ_F64 4
@@ -51,9 +61,26 @@ constexpr int lb_threads() {
 }
 template <class R, int S, typename T, bool IMPL, bool ADJ>
 constexpr int lb_blocks() {
-    if (IMPL && use_reg_solve<R, S, T>()) return ADJ ? OZ_MB_IMPL_ADJ : OZ_MB_IMPL_FWD;
+    if constexpr (IMPL && use_reg_solve<R, S, T>()) {
+        // The reverse sweep factors one system per step and mostly waits on memory (stage cache, history): with a sparse
+        // system it fits 128 registers with little spilling and twice the resident warps win (Van der Pol GL6, 65,536
+        // trajectories: 0.153 -> 0.112 ms).  The forward sweep (three Newton iterations per step) loses more to the
+        // spills than it gains (0.221 -> 0.250 ms), and dense systems spill heavily either way: both stay at 4 blocks.
+        if (ADJ) return (OZ_SPARSE_SOLVE && newton_live_entries<R, S>() <= OZ_SPARSE_LIVE_LIMIT) ? OZ_MB_IMPL_ADJ_SPARSE : OZ_MB_IMPL_ADJ;
+        return OZ_MB_IMPL_FWD;
+    }
     if (!IMPL && ADJ) return sizeof(T) == 8 ? OZ_MB_EXPL_ADJ_F64 : OZ_MB_EXPL_ADJ_F32;
     return 1;
+}
+
+// where the register solve leaves unknown (stage i, active component r)
+template <class R, int S>
+constexpr int sol_idx(int i, int r) {
+#if OZ_SPARSE_SOLVE
+    return uidx<R, S>(i, r);
+#else
+    return i * (R::D - R::DQ) + r;
+#endif
 }
 
 template <bool B>
@@ -132,6 +159,12 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
         //   dY_a = -M_aa^-1 R_a ,   dY_q = -R_q + h sum_j a_ij J_j[q,a] dY_a[j]
         // gives exactly the iterates of the full (S D) Newton while factoring only (S DA)^2 entries.
         constexpr int DA = D - R::DQ, MA = S * DA;
+        const T tol2 = a.newton_tol * a.newton_tol;
+        T hA[S][S];   // h a_ij: used by the residual and by the Newton matrix of every iteration of this step
+#pragma unroll
+        for (int i = 0; i < S; ++i)
+#pragma unroll
+            for (int j = 0; j < S; ++j) hA[i][j] = h * tab.a(i, j);
 #pragma unroll
         for (int i = 0; i < S; ++i)
 #pragma unroll
@@ -146,26 +179,25 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 T part = T(0);   // per-stage partial sums: S short chains instead of one of S * D dependent FMAs
 #pragma unroll
                 for (int c = 0; c < D; ++c) {
-                    T acc = T(0);
+                    T acc = Y[i][c] - y[c];
 #pragma unroll
-                    for (int j = 0; j < S; ++j) acc += tab.a(i, j) * F[j][c];
-                    Rs[i][c] = Y[i][c] - h * acc - y[c];
-                    part += Rs[i][c] * Rs[i][c];
+                    for (int j = 0; j < S; ++j) acc -= hA[i][j] * F[j][c];
+                    Rs[i][c] = acc;
+                    part += acc * acc;
                 }
                 rn2 += part;
             }
-            if (!(rn2 == rn2)) {
-                status |= OZ_STATUS_NONFINITE;
-                break;
-            }
-            if (rn2 < a.newton_tol * a.newton_tol) break;   // ||R||_2 < tol without the square root
-            if (it >= a.newton_max_iter) {
-                status |= OZ_STATUS_NOT_CONVERGED;
+            // one exit test per iteration: ||R||_2 < tol (compared squared), a NaN residual, or out of iterations
+            if (!(rn2 >= tol2) || it >= a.newton_max_iter) {
+                if (!(rn2 == rn2))
+                    status |= OZ_STATUS_NONFINITE;
+                else if (!(rn2 < tol2))
+                    status |= OZ_STATUS_NOT_CONVERGED;
                 break;
             }
             T Ma[MA][MA], b[MA], Jq[S][R::DQ > 0 ? R::DQ : 1][DA];
-            // the Newton matrix, entry by entry, through `put` (registers on the common path, local memory on the
-            // pivoting one)
+            // the Newton matrix, entry by entry, through `put` (dense, stage-major: the cold pivoting path, and the
+            // dense register solve when OZ_SPARSE_SOLVE is 0)
             auto assemble = [&](auto&& put) {
 #pragma unroll
                 for (int j = 0; j < S; ++j) {
@@ -173,25 +205,57 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                     R::jac(Y[j], ps[j], th, J);
 #pragma unroll
                     for (int i = 0; i < S; ++i) {
-                        const T ha = h * tab.a(i, j);
+                        const T ha = hA[i][j];
 #pragma unroll
                         for (int r = 0; r < DA; ++r)
 #pragma unroll
                             for (int c = 0; c < DA; ++c)
                                 put(i * DA + r, j * DA + c, ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c]);
                     }
-#pragma unroll
-                    for (int q = 0; q < R::DQ; ++q)
-#pragma unroll
-                        for (int c = 0; c < DA; ++c) Jq[j][q][c] = J[(DA + q) * D + c];
                 }
             };
+            int bad;
+#if OZ_SPARSE_SOLVE
+            // only the entries the Jacobian pattern allows, in the component-major order of oz_sparse_solve.cuh
+            static_for<0, S>([&](auto jc) {
+                constexpr int j = decltype(jc)::value;
+                T J[D * D];
+                R::jac(Y[j], ps[j], th, J);
+                static_for<0, S>([&](auto ic) {
+                    constexpr int i = decltype(ic)::value;
+                    static_for<0, DA * DA>([&](auto rcc) {
+                        constexpr int r = decltype(rcc)::value / DA, c = decltype(rcc)::value % DA;
+                        if constexpr (jac_nz<R>(r, c))
+                            Ma[uidx<R, S>(i, r)][uidx<R, S>(j, c)] = ((i == j && r == c) ? T(1) : T(0)) - hA[i][j] * J[r * D + c];
+                    });
+                });
+#pragma unroll
+                for (int q = 0; q < R::DQ; ++q)
+#pragma unroll
+                    for (int c = 0; c < DA; ++c) Jq[j][q][c] = J[(DA + q) * D + c];
+            });
+            static_for<0, MA>([&](auto kc) {
+                constexpr int i = decltype(kc)::value / DA, r = decltype(kc)::value % DA;
+                b[uidx<R, S>(i, r)] = -Rs[i][r];
+            });
+            bad = sparse_solve<R, S, false, T>(Ma, b);
+#else
             assemble([&](int r, int c, T v) { Ma[r][c] = v; });
+#pragma unroll
+            for (int j = 0; j < S; ++j) {
+                T J[D * D];
+                R::jac(Y[j], ps[j], th, J);
+#pragma unroll
+                for (int q = 0; q < R::DQ; ++q)
+#pragma unroll
+                    for (int c = 0; c < DA; ++c) Jq[j][q][c] = J[(DA + q) * D + c];
+            }
 #pragma unroll
             for (int i = 0; i < S; ++i)
 #pragma unroll
                 for (int r = 0; r < DA; ++r) b[i * DA + r] = -Rs[i][r];
-            int bad = reg_solve<T, MA>(Ma, b);
+            bad = reg_solve<T, MA>(Ma, b);
+#endif
             if (bad == 2) {  // a diagonal entry failed the threshold test: solve again with row exchanges
                 T ta[MA * MA], tb[MA];
                 assemble([&](int r, int c, T v) { ta[r * MA + c] = v; });
@@ -200,13 +264,21 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
 #pragma unroll
                     for (int r = 0; r < DA; ++r) tb[i * DA + r] = -Rs[i][r];
                 bad = finish_with_pivoting<T, MA>(ta, tb, 0) ? 0 : 1;
-#pragma unroll
-                for (int r = 0; r < MA; ++r) b[r] = tb[r];
+                static_for<0, MA>([&](auto kc) {
+                    constexpr int k = decltype(kc)::value;
+                    b[sol_idx<R, S>(k / DA, k % DA)] = tb[k];
+                });
             }
             if (bad) {
                 status |= OZ_STATUS_SINGULAR;
                 break;
             }
+            // dYa[i][r]: the Newton update of the active components, read back in stage order
+            T dYa[S][DA];
+            static_for<0, MA>([&](auto kc) {
+                constexpr int i = decltype(kc)::value / DA, r = decltype(kc)::value % DA;
+                dYa[i][r] = b[sol_idx<R, S>(i, r)];
+            });
             if constexpr (R::DQ > 0) {
                 T wq[S][R::DQ];
 #pragma unroll
@@ -215,23 +287,23 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                     for (int q = 0; q < R::DQ; ++q) {
                         T acc = T(0);
 #pragma unroll
-                        for (int c = 0; c < DA; ++c) acc += Jq[j][q][c] * b[j * DA + c];
+                        for (int c = 0; c < DA; ++c) acc += Jq[j][q][c] * dYa[j][c];
                         wq[j][q] = acc;
                     }
 #pragma unroll
                 for (int i = 0; i < S; ++i)
 #pragma unroll
                     for (int q = 0; q < R::DQ; ++q) {
-                        T acc = T(0);
+                        T acc = -Rs[i][DA + q];
 #pragma unroll
-                        for (int j = 0; j < S; ++j) acc += tab.a(i, j) * wq[j][q];
-                        Y[i][DA + q] += -Rs[i][DA + q] + h * acc;
+                        for (int j = 0; j < S; ++j) acc += hA[i][j] * wq[j][q];
+                        Y[i][DA + q] += acc;
                     }
             }
 #pragma unroll
             for (int i = 0; i < S; ++i)
 #pragma unroll
-                for (int r = 0; r < DA; ++r) Y[i][r] += b[i * DA + r];
+                for (int r = 0; r < DA; ++r) Y[i][r] += dYa[i][r];
             ++iters;
         }
     } else {
@@ -499,23 +571,55 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 }
             }
         };
+        int bad;
+#if OZ_SPARSE_SOLVE
+        static_for<0, S>([&](auto jc) {
+            constexpr int j = decltype(jc)::value;
+            T J[D * D];
+            R::jac(Y[j], ps[j], th, J);
+            static_for<0, S>([&](auto ic) {
+                constexpr int i = decltype(ic)::value;
+                const T ha = h * tab.a(i, j);
+                static_for<0, DA * DA>([&](auto rcc) {
+                    constexpr int r = decltype(rcc)::value / DA, c = decltype(rcc)::value % DA;
+                    if constexpr (jac_nz<R>(r, c))
+                        Mt[uidx<R, S>(j, c)][uidx<R, S>(i, r)] = ((i == j && r == c) ? T(1) : T(0)) - ha * J[r * D + c];
+                });
+            });
+            static_for<0, DA>([&](auto cc) {
+                constexpr int c = decltype(cc)::value;
+                T acc = -T(0);
+                static_for<0, D>([&](auto rr) {
+                    constexpr int r = decltype(rr)::value;
+                    if constexpr (jac_nz<R>(r, c)) acc += J[r * D + c] * lam[r];
+                });
+                b[uidx<R, S>(j, c)] = h * tab.B[j] * acc;
+            });
+        });
+        bad = sparse_solve<R, S, true, T>(Mt, b);
+#else
         assemble([&](int r, int c, T v) { Mt[r][c] = v; }, [&](int r, T v) { b[r] = v; });
-        int bad = reg_solve<T, MA>(Mt, b);
+        bad = reg_solve<T, MA>(Mt, b);
+#endif
         if (bad == 2) {  // a diagonal entry failed the threshold test: solve again with row exchanges
             T ta[MA * MA], tb[MA];
             assemble([&](int r, int c, T v) { ta[r * MA + c] = v; }, [&](int r, T v) { tb[r] = v; });
             bad = finish_with_pivoting<T, MA>(ta, tb, 0) ? 0 : 1;
-#pragma unroll
-            for (int r = 0; r < MA; ++r) b[r] = tb[r];
+            static_for<0, MA>([&](auto kc) {
+                constexpr int k = decltype(kc)::value;
+                b[sol_idx<R, S>(k / DA, k % DA)] = tb[k];
+            });
         }
         if (bad) status |= OZ_STATUS_SINGULAR;
-#pragma unroll
-        for (int i = 0; i < S; ++i) {
-#pragma unroll
-            for (int c = 0; c < DA; ++c) Yb[i][c] = b[i * DA + c];
+        static_for<0, S>([&](auto ic) {
+            constexpr int i = decltype(ic)::value;
+            static_for<0, DA>([&](auto cc) {
+                constexpr int c = decltype(cc)::value;
+                Yb[i][c] = b[sol_idx<R, S>(i, c)];
+            });
 #pragma unroll
             for (int c = DA; c < D; ++c) Yb[i][c] = T(0);
-        }
+        });
     } else if constexpr (IMPL) {
         constexpr int M = S * D;
         using Sys = SmemSystem<T, M>;
@@ -612,9 +716,32 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
     }
 }
 
-template <class R, typename T, int S, bool IMPL>
+// SPEC selects a compile-time specialisation of the reverse sweep for the commonest request of an optimisation loop --
+// a cotangent on the final state only, gradients w.r.t. the shared step vector and the parameters, full history
+// stored, subdiagonal tableau (RK4):
+//   0  generic: every option is read from the argument block at run time
+//   1  final-state cotangent only, h shared + h_bar, p shared + p_bar
+//   2  final-state cotangent only, h shared + h_bar, p per trajectory + p_bar
+// The specialised kernels run the same code; the options are pinned to constants below, so the compiler removes
+// the per-step null-pointer branches, the second copy of the stage sweep and the output-cotangent arithmetic
+// (ncu, round 1: 12 uniform branches and ~22 register moves per step on a sweep that is issue-bound).
+template <class R, typename T, int S, bool IMPL, int SPEC = 0>
 __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S, T, IMPL, true>()))
-    tm_adjoint_kernel(const TmArgs<T> a, const AdjWsPtr<T> ws) {
+    tm_adjoint_kernel(const TmArgs<T> a_in, const AdjWsPtr<T> ws) {
+    TmArgs<T> a = a_in;
+    if constexpr (SPEC != 0) {
+        a.hist_bar = nullptr;
+        a.prof_bar = nullptr;
+        a.field_bar = nullptr;
+        a.num_inner = 0;
+        a.chain = 1;
+        a.h_shared = 1;
+        a.p_shared = SPEC == 1 ? 1 : 0;
+        __builtin_assume(a.h_bar != nullptr);
+        __builtin_assume(a.p_bar != nullptr);
+        __builtin_assume(a.hist != nullptr);
+        __builtin_assume(a.final_bar != nullptr);
+    }
     using DM = Dims<R>;
     constexpr int D = DM::D;
     constexpr bool HAS_OUT = (DM::NP + DM::NF) > 0;
@@ -665,7 +792,7 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         if (a.hist_bar)
 #pragma unroll
             for (int c = 0; c < D; ++c) lam[c] += hb[c];
-        if constexpr (HAS_OUT) R::out_vjp(yk, pk, th, vp, vf, lam, pb_next, tb);
+        if constexpr (HAS_OUT && SPEC == 0) R::out_vjp(yk, pk, th, vp, vf, lam, pb_next, tb);
     };
     auto load_hist_bar = [&](long long oy, T* hb) {
         if (a.hist_bar)
@@ -946,6 +1073,47 @@ __global__ void __launch_bounds__(128) rhs_eval_kernel(long long nodes, int th_s
 #pragma unroll
             for (int c = 0; c < DM::NF; ++c) field[c * nodes + i] = fl[c];
     }
+}
+
+// Transposed output Jacobians at `nodes` points: what csdl's reverse mode does with the profile / field outputs that
+// VectorBased.integrate evaluates on the whole history (ozone/integrators/vector_based.py:33-49).
+// vprof [NPROF][nodes], vfield [NFIELD][nodes] -> yb [D][nodes], pb [P][nodes], tb [S][nodes] (per node: the caller sums).
+template <class R, typename T>
+__global__ void __launch_bounds__(128) rhs_out_vjp_kernel(long long nodes, int th_shared, const T* __restrict__ y,
+                                                          const T* __restrict__ p, const T* __restrict__ th,
+                                                          const T* __restrict__ vprof, const T* __restrict__ vfield,
+                                                          T* __restrict__ yb, T* __restrict__ pb, T* __restrict__ tb) {
+    using DM = Dims<R>;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nodes) return;
+    T yy[DM::D], pp[DM::P1], tt[DM::S1], vp[DM::NP1], vf[DM::NF1], gy[DM::D], gp[DM::P1], gt[DM::S1];
+#pragma unroll
+    for (int c = 0; c < DM::D; ++c) {
+        yy[c] = y[c * nodes + i];
+        gy[c] = T(0);
+    }
+#pragma unroll
+    for (int c = 0; c < DM::P; ++c) pp[c] = p[c * nodes + i];
+#pragma unroll
+    for (int c = 0; c < DM::P1; ++c) gp[c] = T(0);
+#pragma unroll
+    for (int c = 0; c < DM::SP; ++c) tt[c] = th_shared ? th[c] : th[c * nodes + i];
+#pragma unroll
+    for (int c = 0; c < DM::S1; ++c) gt[c] = T(0);
+#pragma unroll
+    for (int c = 0; c < DM::NP; ++c) vp[c] = vprof ? vprof[c * nodes + i] : T(0);
+#pragma unroll
+    for (int c = 0; c < DM::NF; ++c) vf[c] = vfield ? vfield[c * nodes + i] : T(0);
+    if constexpr ((DM::NP + DM::NF) > 0) R::out_vjp(yy, pp, tt, vp, vf, gy, gp, gt);
+    if (yb)
+#pragma unroll
+        for (int c = 0; c < DM::D; ++c) yb[c * nodes + i] = gy[c];
+    if (pb)
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) pb[c * nodes + i] = gp[c];
+    if (tb)
+#pragma unroll
+        for (int c = 0; c < DM::SP; ++c) tb[c * nodes + i] = gt[c];
 }
 
 }  // namespace oz

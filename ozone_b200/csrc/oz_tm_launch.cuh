@@ -7,12 +7,19 @@
 
 namespace oz {
 
-enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3 };
+#ifndef OZ_ADJ_SPEC_STAGES   /* stage count whose explicit reverse sweep also gets the specialised kernels (RK4) */
+#define OZ_ADJ_SPEC_STAGES 4
+#endif
+
+enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3, TM_OUT_VJP = 4 };
 
 struct EvalArgs {
     long long nodes;
     const void *y, *p;
     void *dy, *prof, *field;
+    // TM_OUT_VJP: cotangents of the outputs in, gradients per node out
+    const void *vprof, *vfield;
+    void *yb, *pb, *tb;
 };
 
 template <class R, typename T, int S, bool IMPL>
@@ -65,11 +72,32 @@ int run_tm(const oz_problem* pb, int mode, size_t* ws_bytes) {
     wp.th = a.ws + w.off_th;
     wp.seg = a.ws + w.off_seg;
     wp.W = w.W;
-    auto kern = tm_adjoint_kernel<R, T, S, IMPL>;
-    if (smem > 48 * 1024)
-        OZ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    kern<<<(unsigned)nblocks, block, smem, stream>>>(a, wp);
-    OZ_CUDA_CHECK(cudaGetLastError());
+    // the specialised reverse sweeps (see tm_adjoint_kernel): RK4-shaped tableau, final-state cotangent only
+    int spec = 0;
+    if constexpr (!IMPL && S == OZ_ADJ_SPEC_STAGES && R::P > 0) {
+        if (a.chain && pb->hist && pb->final_bar && !pb->hist_bar && !pb->prof_bar && !pb->field_bar && pb->h_shared && pb->h_bar &&
+            pb->p_bar)
+            spec = pb->p_shared ? 1 : 2;
+    }
+    auto launch = [&](auto kern) -> int {
+        if (smem > 48 * 1024)
+            OZ_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        kern<<<(unsigned)nblocks, block, smem, stream>>>(a, wp);
+        OZ_CUDA_CHECK(cudaGetLastError());
+        return 0;
+    };
+    int rc = 0;
+    if constexpr (!IMPL && S == OZ_ADJ_SPEC_STAGES && R::P > 0) {
+        if (spec == 1)
+            rc = launch(tm_adjoint_kernel<R, T, S, IMPL, 1>);
+        else if (spec == 2)
+            rc = launch(tm_adjoint_kernel<R, T, S, IMPL, 2>);
+        else
+            rc = launch(tm_adjoint_kernel<R, T, S, IMPL, 0>);
+    } else {
+        rc = launch(tm_adjoint_kernel<R, T, S, IMPL, 0>);
+    }
+    if (rc) return rc;
     if (w.rows_h) reduce_rows_kernel<T><<<(unsigned)w.rows_h, 256, 0, stream>>>(wp.h, w.W, a.h_bar);
     if (w.rows_p) reduce_rows_kernel<T><<<(unsigned)w.rows_p, 256, 0, stream>>>(wp.p, w.W, a.p_bar);
     if (w.rows_th) reduce_rows_kernel<T><<<(unsigned)w.rows_th, 256, 0, stream>>>(wp.th, w.W, a.th_bar);
@@ -98,10 +126,37 @@ int dispatch_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
 
 template <class R>
 int dispatch_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    if (mode == TM_OUT_VJP) {
+        cudaStream_t stream = (cudaStream_t)pb->stream;
+        const unsigned grid = (unsigned)((ev->nodes + 127) / 128);
+        if (grid == 0) return 0;
+        OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
+        if constexpr (OZ_WANT_F64(true)) {
+            if (pb->dtype == OZ_F64) {
+                rhs_out_vjp_kernel<R, double><<<grid, 128, 0, stream>>>(
+                    ev->nodes, pb->th_shared, (const double*)ev->y, (const double*)ev->p, (const double*)pb->th,
+                    (const double*)ev->vprof, (const double*)ev->vfield, (double*)ev->yb, (double*)ev->pb, (double*)ev->tb);
+                OZ_CUDA_CHECK(cudaGetLastError());
+                return 0;
+            }
+        }
+        if constexpr (OZ_WANT_F64(false)) {
+            if (pb->dtype == OZ_F32) {
+                rhs_out_vjp_kernel<R, float><<<grid, 128, 0, stream>>>(
+                    ev->nodes, pb->th_shared, (const float*)ev->y, (const float*)ev->p, (const float*)pb->th,
+                    (const float*)ev->vprof, (const float*)ev->vfield, (float*)ev->yb, (float*)ev->pb, (float*)ev->tb);
+                OZ_CUDA_CHECK(cudaGetLastError());
+                return 0;
+            }
+        }
+        set_error("no output-VJP kernel for dtype %d in this build", pb->dtype);
+        return -1;
+    }
     if (mode == TM_RHS_EVAL) {
         cudaStream_t stream = (cudaStream_t)pb->stream;
         const unsigned grid = (unsigned)((ev->nodes + 127) / 128);
         if (grid == 0) return 0;
+        OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
         if constexpr (OZ_WANT_F64(true)) {
             if (pb->dtype == OZ_F64)
                 rhs_eval_kernel<R, double><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const double*)ev->y,

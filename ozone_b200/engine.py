@@ -449,8 +449,6 @@ def colloc_vjp(spec: SolveSpec, y0, h, p, th, Y, y, mu1, mu2, need=('y0', 'h', '
     shp = input_shapes(spec)
     grads = {k: (torch.zeros(shp[k], dtype=spec.dtype, device=dev) if (k in need and all(v > 0 for v in shp[k])) else None)
              for k in ('y0', 'h', 'p', 'th')}
-    if grads['th'] is not None and not spec.th_shared:
-        raise NotImplementedError('collocation gradients of per-trajectory static parameters are not implemented')
     pb.y0_bar, pb.h_bar, pb.p_bar, pb.th_bar = (_ptr(grads[k]) for k in ('y0', 'h', 'p', 'th'))
     Yb, yb = torch.empty_like(Y), torch.empty_like(y)
     ws_bytes = nat.lib.oz_colloc_vjp_workspace_bytes(C.byref(pb))
@@ -490,24 +488,83 @@ def collocation(spec: SolveSpec, y0, h, p, th, Y, y):
     return _Collocation.apply(spec, y0, h, p, th, Y, y)
 
 
-def outputs_on_history(spec: SolveSpec, hist, p, th):
-    """vector_based.py:33-49: profile outputs at every grid point of a solved history and field outputs
-    summed over time, with the RAW parameters.  (Values only: not on the autograd tape.)"""
+def _node_layout(spec: SolveSpec, hist, p, th):
+    """(y, p, th) of a history as oz_rhs_eval wants them: every (time point, trajectory) pair is one node."""
     nt, d, N = hist.shape
     info = spec.info
-    y = hist.detach().permute(1, 0, 2).reshape(d, nt * N).contiguous()
+    y = hist.permute(1, 0, 2).reshape(d, nt * N).contiguous()
     pp = None
     if info['P']:
-        pd = p.detach()
-        pp = (pd.unsqueeze(-1).expand(nt, info['P'], N) if spec.p_shared else pd).permute(1, 0, 2).reshape(info['P'], nt * N).contiguous()
+        pp = (p.unsqueeze(-1).expand(nt, info['P'], N) if spec.p_shared else p).permute(1, 0, 2).reshape(info['P'], nt * N).contiguous()
     tt = None
     if info['S']:
-        td = th.detach()
-        tt = td if spec.th_shared else td.unsqueeze(1).expand(info['S'], nt, N).reshape(info['S'], nt * N).contiguous()
-    _, prof, fld = rhs_eval(spec, y, pp, tt)
-    prof = prof.reshape(info['nprof'], nt, N).permute(1, 0, 2).contiguous() if prof is not None else None
-    fld = fld.reshape(info['nfield'], nt, N).sum(dim=1) if fld is not None else None
-    return prof, fld
+        tt = th.contiguous() if spec.th_shared else th.unsqueeze(1).expand(info['S'], nt, N).reshape(info['S'], nt * N).contiguous()
+    return y, pp, tt
+
+
+def rhs_out_vjp(spec: SolveSpec, y, p, th, vprof, vfield):
+    """oz_rhs_out_vjp: per-node gradients (y_bar (d, nodes), p_bar (P, nodes) | None, th_bar (S, nodes) | None)."""
+    pb = make_problem(spec)
+    info, nodes, dev = spec.info, y.shape[1], y.device
+    pb.th = _ptr(th)
+    pb.th_shared = int(th is None or th.dim() == 1)
+    new = lambda rows: torch.empty((rows, nodes), dtype=spec.dtype, device=dev)
+    yb = new(info['d'])
+    pbar = new(info['P']) if info['P'] else None
+    tbar = new(info['S']) if info['S'] else None
+    nat.check(nat.lib.oz_rhs_out_vjp(C.byref(pb), nodes, _ptr(y), _ptr(p), _ptr(vprof), _ptr(vfield), _ptr(yb), _ptr(pbar),
+                                     _ptr(tbar)), 'oz_rhs_out_vjp')
+    return yb, pbar, tbar
+
+
+class _OutputsOnHistory(torch.autograd.Function):
+    """Profile outputs at every grid point of a history and field outputs summed over time, on the tape
+    (the reference's are csdl graph nodes, vector_based.py:33-49): backward is one oz_rhs_out_vjp launch."""
+
+    @staticmethod
+    def forward(ctx, spec, hist, p, th):
+        nt, d, N = hist.shape
+        info = spec.info
+        y, pp, tt = _node_layout(spec, hist, p, th)
+        _, prof, fld = rhs_eval(spec, y, pp, tt)
+        ctx.spec, ctx.shape = spec, (nt, d, N)
+        ctx.has = (p is not None and info['P'] > 0, th is not None and info['S'] > 0)
+        ctx.save_for_backward(*[t for t in (y, pp, tt) if t is not None])
+        e = lambda: torch.empty(0, dtype=spec.dtype, device=hist.device)
+        prof = prof.reshape(info['nprof'], nt, N).permute(1, 0, 2).contiguous() if prof is not None else e()
+        fld = fld.reshape(info['nfield'], nt, N).sum(dim=1) if fld is not None else e()
+        return prof, fld
+
+    @staticmethod
+    def backward(ctx, g_prof, g_fld):
+        spec, (nt, d, N) = ctx.spec, ctx.shape
+        info = spec.info
+        it = iter(ctx.saved_tensors)
+        y = next(it)
+        pp = next(it) if ctx.has[0] else None
+        tt = next(it) if ctx.has[1] else None
+        vp = vf = None
+        if info['nprof'] and g_prof is not None and g_prof.numel():
+            vp = g_prof.permute(1, 0, 2).reshape(info['nprof'], nt * N).contiguous()
+        if info['nfield'] and g_fld is not None and g_fld.numel():      # the time sum broadcasts its cotangent
+            vf = g_fld.unsqueeze(1).expand(info['nfield'], nt, N).reshape(info['nfield'], nt * N).contiguous()
+        yb, pbar, tbar = rhs_out_vjp(spec, y, pp, tt, vp, vf)
+        g_hist = yb.reshape(d, nt, N).permute(1, 0, 2).contiguous()
+        g_p = g_th = None
+        if pbar is not None and ctx.needs_input_grad[2]:
+            g_p = pbar.reshape(info['P'], nt, N).permute(1, 0, 2)
+            g_p = g_p.sum(dim=2) if spec.p_shared else g_p.contiguous()
+        if tbar is not None and ctx.needs_input_grad[3]:
+            g_th = tbar.reshape(info['S'], nt, N).sum(dim=1)
+            g_th = g_th.sum(dim=1) if spec.th_shared else g_th
+        return None, g_hist, g_p, g_th
+
+
+def outputs_on_history(spec: SolveSpec, hist, p, th):
+    """vector_based.py:33-49: profile outputs at every grid point of a solved history and field outputs
+    summed over time, with the RAW parameters; differentiable w.r.t. the history, p and th."""
+    prof, fld = _OutputsOnHistory.apply(spec, hist, p, th)
+    return (prof if prof.numel() else None), (fld if fld.numel() else None)
 
 
 class PipelinedTmSolve:

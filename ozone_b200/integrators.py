@@ -46,6 +46,13 @@ def evaluate_device_rhs(rhs, ozone_vars: ODEVars, static_values: dict):
             off += k
 
 
+def default_newton_tolerance(dtype):
+    """1e-7 in fp64: the value the reference hard-codes (time_marching.py:220).  The kernel stops on the 2-norm of the
+    stacked stage residual Y - h A F - y, which in fp32 is quantised at ~1e-7 |y| per component, so 1e-7 could only be
+    met by an exactly zero residual and every step would run into newton_max_iter; fp32 problems default to 1e-5."""
+    return 1e-7 if dtype == torch.float64 else 1e-5
+
+
 def _dummy_method():
     from .glms import get_integration_method
     return get_integration_method('ForwardEuler')
@@ -90,7 +97,8 @@ class IntegratorBase(object):
             n=self.num_steps, dtype=pk.dtype,
             h_shared=pk.h_shared, p_shared=pk.p_shared, th_shared=pk.th_shared,
             store_history=any(s.output for s in self.states.states.values()),
-            newton_tol=opts.get('newton_tolerance', 1e-7), newton_max_iter=opts.get('newton_max_iter', 100),
+            newton_tol=opts.get('newton_tolerance', default_newton_tolerance(pk.dtype)),
+            newton_max_iter=opts.get('newton_max_iter', 100),
             d_override=pk.d if pk.grid else 0, rhs_cfg=rhs.rhs_cfg(static_values, self.states),
             state_blocks=tuple(pk.state_offsets()))
         return rhs

@@ -36,8 +36,8 @@ def _reject(kind, what):
 class ODEProblem(object):
     """``ODEProblem(method, approach, **engine_options)``
 
-    engine_options (all optional, none exist in the reference): ``newton_tolerance`` (1e-7, the value the
-    reference hard-codes at time_marching.py:220), ``newton_max_iter`` (100), ``verbose`` (checkpoint banner),
+    engine_options (all optional, none exist in the reference): ``newton_tolerance`` (1e-7 in fp64, the value the
+    reference hard-codes at time_marching.py:220; 1e-5 for fp32 problems, whose residual cannot get below ~1e-7), ``newton_max_iter`` (100), ``verbose`` (checkpoint banner),
     ``batched`` (Python callbacks only: the trailing axis of every state is the trajectory axis).
     """
 

@@ -592,12 +592,14 @@ class TracedRHS:
                        + [(f'field[{i}]', e) for i, e in enumerate(self.field_exprs)])
         ov_body = block([(f'yb[{j}]', e) for j, e in enumerate(self.ovjp_y)] + [(f'pb[{j}]', e) for j, e in enumerate(self.ovjp_p)]
                         + [(f'tb[{j}]', e) for j, e in enumerate(self.ovjp_th)], accumulate=True)
+        jp = ', '.join('0' if self.J[i][j].is_const(0.0) else '1' for i in range(D) for j in range(D))
         return f'''// generated by ozone_b200/trace.py from a Python right-hand side callback
 #include "oz_common.cuh"
 namespace oz {{
 struct RhsTraced {{
     static constexpr int ID = OZ_RHS_PLUGIN_BASE, D = {D}, P = {P}, S = {S}, NPROF = {NP}, NFIELD = {NF};
     static constexpr int DQ = {self.DQ};
+    static constexpr unsigned char JP[{D * D}] = {{{jp}}};   // which df_r/dy_c are not identically zero (oz_sparse_solve.cuh)
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T* th, T* dy) {{
 {f_body}
@@ -642,15 +644,17 @@ struct RhsTraced {{
         os.makedirs(PLUGIN_DIR, exist_ok=True)
         so = os.path.join(PLUGIN_DIR, f'oz_rhs_{tag}.so')
         if not os.path.exists(so):
-            cu = os.path.join(PLUGIN_DIR, f'oz_rhs_{tag}.cu')
+            # every rank under torchrun may build the same plugin at once: private file names, atomic publish
+            cu = os.path.join(PLUGIN_DIR, f'oz_rhs_{tag}.{os.getpid()}.cu')
+            tmp = f'{so}.{os.getpid()}.tmp'
             open(cu, 'w').write(src)
             cmd = ['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-std=c++17', '-lineinfo',
                    '--expt-relaxed-constexpr', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '-shared',
-                   f'-I{csrc}', *flags, cu, '-o', so + '.tmp', '-lcudart_static', '-lrt', '-lpthread', '-ldl']
+                   f'-I{csrc}', *flags, cu, '-o', tmp, '-lcudart_static', '-lrt', '-lpthread', '-ldl']
             res = subprocess.run(cmd, capture_output=True, text=True)
             if res.returncode != 0:
                 raise RuntimeError(f'nvcc failed on the traced right-hand side:\n{res.stderr[-4000:]}')
-            os.replace(so + '.tmp', so)
+            os.replace(tmp, so)
         rid = _REGISTERED.get(so)                 # one registration per shared object and process
         if rid is None:
             rid = nat.lib.oz_register_rhs_plugin(so.encode())

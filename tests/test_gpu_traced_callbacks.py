@@ -9,6 +9,7 @@ import ozone_b200 as ozone
 from ozone_b200 import ops
 from ozone_b200.approaches import TimeMarching, TimeMarchingCheckpoints, PicardIteration, Collocation
 from ozone_b200.methods import RK4, Trapezoidal, GaussLegendre6
+from tests import reference_callbacks as RC
 
 pytestmark = pytest.mark.gpu
 
@@ -131,13 +132,9 @@ def test_3_large_python_callback_with_captured_static_parameter():
 
 
 def test_van_der_pol_python_callback_equals_the_registered_functor():
-    # van_der_pol/main_model.py:6-14 verbatim; implicit GL6 -> Newton in registers, J detected as a quadrature state
-    def ode_func(ozone_vars: ozone.ODEVars):
-        x0, x1 = ozone_vars.states['x0'], ozone_vars.states['x1']
-        u = ozone_vars.dynamic_parameters['u']
-        ozone_vars.d_states['x0'] = ((1.0 + (- 1.0) * (x1**2.0))*x0 + (-1*x1) + u).reshape(-1, 1)
-        ozone_vars.d_states['x1'] = (x0*1.0).reshape(-1, 1)
-        ozone_vars.d_states['J'] = (x0**2.0 + x1**2.0 + u**2.0).reshape(-1, 1)
+    # van_der_pol/main_model.py:6-14 (tests/reference_callbacks.py, pinned on the reference's file by
+    # tests/test_reference_source_pins.py); implicit GL6 -> Newton in registers, J detected as a quadrature state
+    ode_func = RC.van_der_pol
 
     nt, N = 40, 256
     rng = np.random.default_rng(4)
@@ -163,16 +160,43 @@ def test_van_der_pol_python_callback_equals_the_registered_functor():
     assert torch.equal(res[0][4], res[1][4])                                         # same Newton iteration counts
 
 
+@pytest.mark.parametrize('approach', ['TimeMarching', 'Collocation'])
+def test_lunar_ascent_python_callback_equals_the_registered_functor(approach):
+    # ascent_system/main_model.py:6-21 traced vs the hand-written RhsLunarAscent: states, constraints and gradients
+    from tests import cases
+    nt, N = 21, 70
+    case = cases.ascent_inputs(N=N, nt=nt, seed=3)
+    names = ('rx', 'ry', 'rz', 'Vx', 'Vy', 'Vz', 'm')
+    res = []
+    for func, opts in ((RC.lunar_ascent, dict(batched=True)), (ozone.rhs.lunar_ascent, {})):
+        u = [var(case['p'][:, i, :]) for i in range(3)]
+        tf = var([0.1])
+        h = (tf / (nt - 1)).expand(nt - 1)
+        p = ozone.ODEProblem(RK4(), TimeMarching() if approach == 'TimeMarching' else Collocation(), **opts)
+        for i, nm in enumerate(names):
+            p.add_state(nm, var(case['y0'][i], False), store_history=True, store_final=True)
+        for nm, ui in zip(('ux', 'uy', 'uz'), u):
+            p.add_dynamic_parameter(nm, ui)
+        p.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+        p.set_function(func)
+        out = p.solve()
+        if approach == 'TimeMarching':
+            obj = sum((out.final_states[nm] ** 2).sum() for nm in names)
+            vals = [out.states[nm].detach() for nm in names]
+        else:
+            integ = p.integrator
+            obj = (integ.c1 ** 2).sum() + (integ.c2 * torch.arange(1, integ.c2.numel() + 1, device='cuda',
+                                                                    dtype=torch.float64).reshape(integ.c2.shape)).sum()
+            vals = [integ.c1.detach(), integ.c2.detach()]
+        res.append((vals, torch.autograd.grad(obj, u + [tf])))
+    for a, b in zip(res[0][0], res[1][0]):
+        assert float((a - b).abs().max()) <= 1e-13 * max(1.0, float(b.abs().max()))
+    for a, b in zip(res[0][1], res[1][1]):
+        assert float((a - b).abs().max()) <= 1e-13 * max(1.0, float(b.abs().max()))
+
+
 def test_lotka_volterra_example_python_callback_and_collocation_constraints():
-    # examples/simple_examples/lotka_volterra.py:51-62 verbatim
-    def ode_function(ozone_vars: ozone.ODEVars, c):
-        a = ozone_vars.dynamic_parameters['a']
-        x = ozone_vars.states['x']
-        y = ozone_vars.states['y']
-        ozone_vars.d_states['y'] = a*y - 0.5*y*x
-        ozone_vars.d_states['x'] = 2.0*x*y - c*x
-        ozone_vars.field_outputs['field_x'] = x
-        ozone_vars.profile_outputs['x_plus_y'] = x + y
+    ode_function = RC.lotka_volterra              # examples/simple_examples/lotka_volterra.py:51-62
 
     num_times = 10
     outs = {}

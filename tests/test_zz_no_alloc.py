@@ -76,6 +76,53 @@ def test_static_scratch_adjoint_matches_workspace_adjoint_twice(name, method):
             assert relerr(np_(v), expect[k]) < 1e-10, (call, k)
 
 
+@pytest.mark.parametrize('name,method', [('lotka_volterra', 'RK4'), ('van_der_pol', 'GaussLegendre4')])
+def test_static_scratch_adjoint_with_checkpoints_replays_segments_in_the_builtin_scratch(name, method):
+    """TimeMarchingCheckpoints without a stored history: besides the partial sums, the built-in scratch then also
+    holds the states of the segment being replayed (num_inner x d x N values)."""
+    from ozone_b200 import engine, _native as nat
+    if name == 'lotka_volterra':
+        case, grads = cases.lotka_volterra_inputs(N=2000, nt=41), ('y0', 'h', 'p', 'th')
+    else:
+        case, grads = cases.van_der_pol_inputs(N=1100, nt=21), ('y0', 'h', 'p')
+    ni = 5
+    spec = make_spec(case, method, num_inner=ni, store_history=False)
+    y0, h, p, th = dev_inputs(case, spec)
+    fwd = engine.tm_forward(spec, y0, h, p, th, keep_history=False)
+    assert fwd['hist'] is None and fwd['ckpt'] is not None
+    rng = np.random.default_rng(12)
+    t = lambda a: torch.tensor(a, dtype=spec.dtype, device='cuda')
+    final_bar = t(rng.standard_normal(tuple(fwd['final'].shape)))
+    prof_bar = t(rng.standard_normal(tuple(fwd['prof'].shape))) if fwd['prof'] is not None else None
+    field_bar = t(rng.standard_normal(tuple(fwd['field'].shape))) if fwd['field'] is not None else None
+    pb = engine.make_problem(spec)
+    keep = engine._set_inputs(pb, spec, y0, h, p, th)
+    pb.ckpt, pb.final_bar = fwd['ckpt'].data_ptr(), final_bar.data_ptr()
+    pb.prof_bar = None if prof_bar is None else prof_bar.data_ptr()
+    pb.field_bar = None if field_bar is None else field_bar.data_ptr()
+    shp = engine.input_shapes(spec)
+    out = {k: torch.full(shp[k], float('nan'), dtype=spec.dtype, device='cuda') for k in grads}
+    for k in grads:
+        setattr(pb, k + '_bar', out[k].data_ptr())
+    need = nat.lib.oz_tm_adjoint_workspace_bytes(C.byref(pb))
+    assert ni * spec.d * spec.N * 8 <= need <= nat.lib.oz_static_scratch_bytes()       # the segment states are in there
+    ws = torch.empty(need, dtype=torch.uint8, device='cuda')
+    pb.ws, pb.ws_bytes = ws.data_ptr(), need
+    nat.check(nat.lib.oz_tm_adjoint(C.byref(pb)), 'oz_tm_adjoint')
+    torch.cuda.synchronize()
+    expect = {k: np_(v) for k, v in out.items()}
+    assert all(np.isfinite(v).all() for v in expect.values())
+    pb.ws, pb.ws_bytes = None, 0
+    for call in range(2):
+        for v in out.values():
+            v.fill_(float('nan'))
+        nat.check(nat.lib.oz_tm_adjoint_static(C.byref(pb)), 'oz_tm_adjoint_static')
+        torch.cuda.synchronize()
+        for k, v in out.items():
+            assert relerr(np_(v), expect[k]) < 1e-10, (call, k)
+    del keep
+
+
 def test_static_scratch_refuses_problems_that_do_not_fit():
     case = cases.lotka_volterra_inputs(N=64, nt=41)
     nat, pb, out, keep = _problem(case, 'RK4', ('h', 'p'))

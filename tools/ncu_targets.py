@@ -27,7 +27,7 @@ if which == 'picard':
 
 
 class A:
-    newton_tol, e2e_slices, world = 1e-7, 2, 1
+    newton_tol, e2e_slices, world, no_e2e_graph = 1e-7, 2, 1, True
 
 
 run = bench.Runner(wl, name, 0, torch.device('cuda', 0), A)
