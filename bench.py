@@ -42,7 +42,12 @@ WORKLOADS = {
     'lotka_volterra_rk4_picard_jacobi_adjoint_N1M_nt101': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, jacobi=True),
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32),
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024_fp32': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, fp32=True),
+    # the same grid cut into spatial slabs over the ranks (strong scaling: the 10^6 cells are shared out)
+    'diffusion_reaction_rk4_checkpoints_nx1M_n1024_sharded': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, sharded=True),
     'lunar_ascent_rk4_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='RK4', N=16384, nt=101, T=0.1),
+    # one optimiser evaluation of config C5: constraints c (residual kernel) + the factored constraint Jacobian dc
+    # (f, df/dy, df/dp at every stage node: optimize.CollocationBlocks)
+    'lunar_ascent_rk4_optimizer_eval_N16384_nt101': dict(kind='coljac', rhs='lunar_ascent', method='RK4', N=16384, nt=101, T=0.1),
     'lunar_ascent_gl6_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='GaussLegendre6', N=16384, nt=101, T=0.1),
 }
 DEFAULT_WORKLOAD = 'van_der_pol_gl6_tm_adjoint_N65536_nt40'
@@ -146,7 +151,7 @@ def _oracle_chunk(args):
                            field_bar=np.ones_like(out['field']))
         return float(out['field'].sum()), float(np.abs(g['p']).sum())
     rhs = R.REGISTRY[wl['rhs']]()
-    if kind == 'colloc':
+    if kind in ('colloc', 'coljac'):
         from oracle.tableaux import tableau
         n, s = len(case['h']), tableau(method)[0].shape[0]
         Y, y = I.collocation_guess(case['y0'], n, s)
@@ -198,8 +203,8 @@ def cpu_port_throughput(wl, cores, units_per_core, repeats=1):
     return cores * per_job / best, sample, best
 
 
-CPU_SAMPLE = {'tm': 4096, 'picard': 256, 'colloc': 2048, 'grid': 4096}       # per core, ~10-30 s of CPU work in total
-CPU_SAMPLE_REF = {'tm': 1024, 'picard': 64, 'colloc': 512, 'grid': 2048}      # per step of --impl reference
+CPU_SAMPLE = {'tm': 4096, 'picard': 256, 'colloc': 2048, 'coljac': 2048, 'grid': 4096}       # per core, ~10-30 s of CPU work in total
+CPU_SAMPLE_REF = {'tm': 1024, 'picard': 64, 'colloc': 512, 'coljac': 512, 'grid': 2048}      # per step of --impl reference
 
 
 def run_reference(args, rank, world):
@@ -233,6 +238,104 @@ def run_reference(args, rank, world):
 
 
 # ------------------------------------------------------------------------------------------------
+class ShardedGridRunner:
+    """Config C3 with the grid cut into one slab per rank (ozone_b200/parallel.py): strong scaling.  The forward sweep
+    and the reverse sweep are each captured as ONE CUDA graph (kernels + the peer-memory halo kernels, nothing else);
+    the grid-wide sums (J, h_bar, u_bar) are all-reduced once per step, inside the timed region."""
+
+    def __init__(self, wl, name, rank, world, dev, args):
+        import torch
+        import torch.distributed as dist
+        from ozone_b200 import engine, parallel
+        from ozone_b200.glms import get_integration_method
+        self.torch, self.engine, self.dist = torch, engine, dist
+        self.wl, self.kind, self.world = wl, 'grid', world
+        self.dtype = torch.float32 if wl.get('fp32') else torch.float64
+        self.w = 4 if wl.get('fp32') else 8
+        nx, nt = wl['nx'], wl['nt']
+        self.n = nt - 1
+        self.d = nx
+        self.units = nx * self.n                      # the WHOLE grid: total work is fixed as ranks are added
+        case = synth_inputs(wl, 1, seed=0)            # the same problem on every rank
+        m = get_integration_method(wl['method'])
+        ni = self.n // wl['nc']
+        cfg = (np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx)))
+        t = lambda a: torch.tensor(np.ascontiguousarray(a), dtype=self.dtype, device=dev)
+        self.channel = parallel.make_channel(m, nx, ni, self.dtype, dev) if world > 1 else None
+        self.shard = parallel.GridShard(m, nx, self.n, ni, rank, world, t(case['y0'][:, 0]), t(case['h']), t(case['p'][:, 0, 0]),
+                                        cfg, self.dtype, dev, channel=self.channel)
+        self.spec = self.shard._spec(0, False)
+        self.pipe, self.plan = None, None
+        self.host, self.e2e_inputs, self.h2d, self.d2h = {}, (), 0, 0
+        (K, KR), ni_ = engine.grid_fusion(self.shard.slab.n_ext), ni
+        groups = lambda steps, k: -(-steps // k)
+        nseg = self.shard.nseg
+        self.launches = nseg * (groups(ni_, K) + 2 + groups(ni_ - 1, K) + groups(ni_, KR) + 2
+                                + (4 if world > 1 else 0))
+        self.graphs = None
+        self.packed = torch.zeros(1 + self.n + self.n + 1, dtype=self.dtype, device=dev)
+        if not args.no_shard_graph:
+            self._capture()
+
+    def _fwd(self):
+        sh = self.shard
+        for seg in range(sh.nseg):
+            sh.forward_segment(seg)
+            sh.exchange(sh.ckpts[seg + 1])
+
+    def _adj(self):
+        sh = self.shard
+        sh.start_adjoint(1.0)
+        for seg in reversed(range(sh.nseg)):
+            sh.adjoint_segment(seg)
+            sh.exchange(sh.lam_cur)
+        if sh.channel is not None:
+            sh.channel.advance(self.torch.cuda.current_stream().cuda_stream)
+        r = sh.results()
+        self.packed[0:1].copy_(r['field'].reshape(-1))
+        self.packed[1:1 + self.n].copy_(r['h_bar'])
+        self.packed[1 + self.n:].copy_(r['u_bar'].reshape(-1))
+
+    def _capture(self):
+        torch = self.torch
+        self._fwd(); self._adj()                      # warm-up outside the capture
+        torch.cuda.synchronize()
+        if self.world > 1:
+            self.dist.barrier()
+        gf, ga = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(gf):
+            self._fwd()
+        with torch.cuda.graph(ga):
+            self._adj()
+        self.graphs = (gf, ga)
+
+    def forward(self):
+        self.graphs[0].replay() if self.graphs else self._fwd()
+
+    def adjoint(self):
+        self.graphs[1].replay() if self.graphs else self._adj()
+        if self.world > 1:
+            self.dist.all_reduce(self.packed)         # J, h_bar, u_bar: sums over the slabs
+
+    def shared_grad(self):
+        return None                                   # reduced inside adjoint()
+
+    def e2e(self):
+        self.forward(); self.adjoint()
+
+    def e2e_readback(self):
+        pass
+
+    def check(self):
+        if self.channel is not None:
+            self.channel.check()
+
+    def algorithmic_bytes(self):
+        w, n = self.w, self.n
+        d = self.shard.slab.own_hi - self.shard.slab.own_lo
+        return 2 * w * d * n, 5 * w * d * n
+
+
 class Runner:
     """One workload on one rank: device-resident step (fwd, adj timed separately) and e2e step."""
 
@@ -306,7 +409,7 @@ class Runner:
                     torch.cuda.synchronize()
         if self.kind == 'picard':
             self.launches = 1 + plan.launches_adjoint
-        if self.kind == 'colloc':
+        if self.kind in ('colloc', 'coljac'):
             s = spec.method.num_stages
             rng = np.random.default_rng(1000 + rank)
             dev_t = lambda a: torch.tensor(a, dtype=self.dtype, device=dev)
@@ -322,7 +425,7 @@ class Runner:
         if self.kind == 'picard':
             pl = self.plan
             self.pic = self.engine.picard_forward(self.spec, pl.y0, pl.h, pl.p, pl.th, tol=1e-12 if self.w == 8 else 1e-4)
-        elif self.kind == 'colloc':
+        elif self.kind in ('colloc', 'coljac'):
             pl = self.plan
             self.c = self.engine.colloc_residual(self.spec, pl.y0, pl.h, pl.p, pl.th, self.Y, self.y)
         else:
@@ -333,6 +436,12 @@ class Runner:
             pl = self.plan
             self.g = self.engine.tm_adjoint(self.spec, pl.y0, pl.h, pl.p, pl.th, hist=self.pic['hist'], final_bar=pl.final_bar,
                                             need=('h', 'p', 'th'))
+        elif self.kind == 'coljac':
+            pl, sp = self.plan, self.spec
+            n, st, d, N, P = sp.n, sp.method.num_stages, sp.d, sp.N, sp.info['P']
+            pst = self.engine.stage_parameters(sp, pl.p).reshape(n * st, P, N)
+            self.jac = self.engine.rhs_jac_eval(sp, self.Y.reshape(n * st, d, N), pst, pl.th)
+            self.g = {'h': None}
         elif self.kind == 'colloc':
             pl = self.plan
             self.g = self.engine.colloc_vjp(self.spec, pl.y0, pl.h, pl.p, pl.th, self.Y, self.y, self.mu1, self.mu2,
@@ -341,7 +450,7 @@ class Runner:
             self.plan.adjoint()
 
     def shared_grad(self):
-        if self.kind in ('picard', 'colloc'):
+        if self.kind in ('picard', 'colloc', 'coljac'):
             return self.g['h']
         return self.plan.grad['h']
 
@@ -358,7 +467,7 @@ class Runner:
     def e2e_readback(self):
         if self.pipe is not None:
             return                  # downloads are part of every slice's stream
-        if self.kind in ('picard', 'colloc'):
+        if self.kind in ('picard', 'colloc', 'coljac'):
             src = self.pic['final'][-1] if self.kind == 'picard' else self.c[1][-1, 0]
             self.host_obj.copy_(src, non_blocking=True)
             for k, v in self.host_out.items():
@@ -376,6 +485,11 @@ class Runner:
         pN = 1 if self.p_shared else N
         if self.kind == 'grid':       # per cell-step: fwd 2w; replay 2w; adjoint step 3w  
             return 2 * w * d * n, 5 * w * d * n
+        if self.kind == 'coljac':
+            s = self.spec.method.num_stages
+            fwd = w * (2 * n * s * d * N + 2 * n * d * N + (n + 1) * P * pN)          # read Y, y, p; write c1, c2
+            adj = w * n * s * N * (d + P + d + d * d + d * P)                          # read Y, p at the nodes; write f, Jy, Jp
+            return fwd, adj
         if self.kind == 'colloc':
             s = self.spec.method.num_stages
             fwd = w * (2 * n * s * d * N + 2 * n * d * N + (n + 1) * P * pN)          # read Y, y, p; write c1, c2
@@ -413,7 +527,8 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
     peak = float(peaks.get('hbm_gbs', 6650.0))
     names = {'tm': ('tm_adjoint_kernel', 'tm_forward_kernel'), 'picard': ('tm_adjoint_kernel', 'picard_kernel'),
              'grid': ('pde_adjoint_step_kernel (+ replayed pde_step_kernel)', 'pde_step_kernel'),
-             'colloc': ('colloc_vjp_kernel', 'colloc_residual_kernel')}[run.kind]
+             'colloc': ('colloc_vjp_kernel', 'colloc_residual_kernel'),
+             'coljac': ('rhs_jac_kernel', 'colloc_residual_kernel')}[run.kind]
     traffic = {}
     try:
         traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(workload, {})
@@ -478,6 +593,8 @@ def main():
     ap.add_argument('--cpu-traj-per-core', type=int, default=None,
                     help='CPU sample size per core (defaults: CPU_SAMPLE / CPU_SAMPLE_REF tables)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--shared-sum', default='nccl', choices=['peer', 'nccl'], help='how gradients of batch-shared inputs are summed over ranks')
+    ap.add_argument('--no-shard-graph', action='store_true', help='sharded grid: enqueue eagerly instead of replaying CUDA graphs')
     ap.add_argument('--no-other-workloads', action='store_true', help='skip the compact other_workloads entries of the default line')
     ap.add_argument('--other-steps', type=int, default=5)
     ap.add_argument('--trajectories', type=int, default=None, help='override the batch size per GPU (experiments only: the bench line names it)')
@@ -509,7 +626,8 @@ def main():
     wl = dict(WORKLOADS[args.workload])
     if args.trajectories:
         wl['N'] = args.trajectories
-    run = Runner(wl, args.workload, rank, dev, args)
+    sharded = bool(wl.get('sharded'))
+    run = ShardedGridRunner(wl, args.workload, rank, world, dev, args) if sharded else Runner(wl, args.workload, rank, dev, args)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)     # > 126 MB L2
 
     def barrier():
@@ -517,12 +635,29 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    # Gradients of batch-shared inputs (h: 39 scalars for C2) are summed over the ranks.  The all-reduce runs on its own
-    # stream: it overlaps the L2 flush and the next step's forward solve, and the next reverse sweep -- which overwrites
-    # the buffer -- waits for it.  The timed total ends when the LAST all-reduce has completed (tail added below), so
-    # every collective is inside the measurement; only its launch latency is off the kernels' critical path.
+    # Gradients of batch-shared inputs (h: 39 scalars for C2) are summed over the ranks.
+    #   peer (default): one small kernel on the compute stream -- every rank stores its row sums into every peer's
+    #       symmetric-memory arena and adds up the world x rows values it received, in rank order (ozone_b200/peer.py,
+    #       csrc/oz_peer.cu): ~2 NVLink latencies instead of an NCCL launch (~12-26 us at 2-8 ranks in round 1).
+    #   nccl: dist.all_reduce on a side stream, overlapping the L2 flush and the next forward solve; the next reverse
+    #       sweep waits for it and the LAST one is inside the timed total (tail below).
     comm = torch.cuda.Stream(device=dev) if world > 1 else None
     pending = [None]
+    peer_sum = [None]
+    shared_mode = ['none (1 GPU)' if world == 1 else args.shared_sum]
+    if world > 1 and args.shared_sum == 'peer' and not sharded:
+        try:
+            from ozone_b200 import peer
+            g0 = run.shared_grad()
+            if g0 is not None:
+                arena = peer.PeerArena(1 << 20, dev)
+                peer_sum[0] = peer.PeerSum(arena, g0.numel(), g0.dtype)
+                shared_mode[0] = 'peer: oz_peer_sum kernel over symmetric memory, on the compute stream'
+        except Exception as exc:                 # noqa: BLE001 -- e.g. no symmetric memory on this box: use NCCL
+            peer_sum[0] = None
+            shared_mode[0] = f'nccl on a side stream (peer arena unavailable: {repr(exc)[:120]})'
+    elif world > 1:
+        shared_mode[0] = 'nccl on a side stream, overlapping the next forward solve; the last one is inside the timed total'
 
     def allreduce_shared(r, e2e=False):
         if world == 1:
@@ -531,6 +666,9 @@ def main():
             return
         g = r.shared_grad()
         if g is None:
+            return
+        if peer_sum[0] is not None and r is run:
+            peer_sum[0](g, g, torch.cuda.current_stream().cuda_stream)
             return
         ready = torch.cuda.Event()
         ready.record()
@@ -553,8 +691,9 @@ def main():
         e0, e1, e2 = ev(), ev(), ev()
         e0.record(); r.forward(); e1.record()
         join_comm()                           # the previous step's all-reduce still owns the shared-gradient buffer
-        r.adjoint(); e2.record()
-        allreduce_shared(r)
+        r.adjoint()
+        allreduce_shared(r)                   # peer mode: a kernel on this stream, inside the reverse interval
+        e2.record()
         times.append((e0, e1, e2))
 
     def e2e_step(r, times):
@@ -605,6 +744,10 @@ def main():
         e2e_step(run, etimes)
     barrier()
     clocks = sampler.stop() if rank == 0 else None
+    if hasattr(run, 'check'):
+        run.check()                            # a halo wait that timed out shows up here, not as a hang
+    if peer_sum[0] is not None:
+        peer_sum[0].check()
     e2e_ms = float(np.sum([a.elapsed_time(b) for a, b in etimes]))
 
     plan = run.plan
@@ -622,7 +765,7 @@ def main():
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
     step_ms, e2e_ms, fwd_tot, adj_tot = tot.tolist()
 
-    units_per_step = world * run.units
+    units_per_step = run.units if sharded else world * run.units
     value = units_per_step * args.steps / (step_ms * 1e-3)
     e2e_value = units_per_step * args.steps / (e2e_ms * 1e-3)
 
@@ -666,11 +809,10 @@ def main():
         line = {
             'metric': 'state-steps/sec (fwd+adjoint)', 'value': value, 'unit': 'state-steps/s', 'n_gpus': world,
             'steps': args.steps, 'warmup': args.warmup, 'ms_per_step': step_ms / args.steps, 'higher_is_better': True,
-            'scaling': 'weak', 'vs_baseline': None, 'dtype': 'f32' if wl.get('fp32') else 'f64', 'data': 'synthetic',
+            'scaling': 'strong' if sharded else 'weak', 'vs_baseline': None, 'dtype': 'f32' if wl.get('fp32') else 'f64', 'data': 'synthetic',
             'config': workload_config(args.workload, wl, world, args.newton_tol),
             'solver_stats': extra_cfg,
-            'shared_gradient_allreduce': ('NCCL on a side stream, overlapping the next forward solve; the last one is inside '
-                                          'the timed total') if world > 1 else 'none (1 GPU)',
+            'shared_gradient_allreduce': shared_mode[0],
             'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
                     'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps,
                     'how': (f'engine.PipelinedTmSolve: {args.e2e_slices} sub-batches on their own streams, pinned host buffers, '

@@ -156,6 +156,15 @@ OZ_API int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const
 OZ_API int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, const void* p, const void* vprof,
                           const void* vfield, void* y_bar, void* p_bar, void* th_bar);
 
+/* f and its Jacobians at blocks x nodes points, trajectory index innermost: y [blocks][d][nodes], p [blocks][P][nodes] ->
+ * f [blocks][d][nodes], Jy [blocks][d][d][nodes] (d f_r / d y_c at [r][c]), Jp [blocks][d][P][nodes]; NULL = skip.
+ * With blocks = n s and nodes = N the inputs are the Collocation stage variables as they lie in memory, and the blocks
+ * of the constraint Jacobian are products of these with tableau entries and step sizes
+ * (ozone/integrators/collocation.py:48-57: c1 = A hF + U y - Y, c2 = B hF + V y - y; the reference leaves the
+ * differentiation to csdl, an optimiser consumes it as `dc`, ozone/paper_examples/utils/utils.py:237,273-286). */
+OZ_API int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, const void* y, const void* p, void* f,
+                           void* Jy, void* Jp);
+
 /* TimeMarching.integrate: ozone/integrators/time_marching.py:6-59 (loop), :143-245 (stages,
  * explicit and Newton), :247-260 (update), :97-141 (outputs).  With num_inner > 0 it is
  * TimeMarchingUniform.integrate (ozone/integrators/time_marching_uniform.py:7-150): only `ckpt`
@@ -193,6 +202,26 @@ OZ_API double oz_fma_probe(int dtype, int iters, void* out, void* stream);
  * `oz_plugin_describe`; returns the rhs_id to put in oz_problem.rhs_id (>= OZ_RHS_PLUGIN_BASE) or < 0.
  * This is what stands in for "any Python f" of ozone/func_wrapper.py:90-107. */
 OZ_API int oz_register_rhs_plugin(const char* so_path);
+
+/* No counterpart in the reference (it has no distributed code).  Plumbing of the two multi-GPU paths over peer-mapped
+ * memory (NVLink / NVSwitch; each rank holds device pointers into every other rank's symmetric-memory arena): plain
+ * stores into the peer's arena + a release store of an epoch number, acquire polling on the receiver's own memory.
+ * Epochs are *epoch_base + epoch so a captured CUDA graph can be replayed (oz_peer_epoch_advance moves the base).  A wait
+ * that sees no signal for ~2 s sets *err to 1 and returns without copying.  NULL pointers = no neighbour on that side.
+ *   oz_peer_halo_push / oz_peer_halo_wait: neighbour exchange of the spatial shard (ozone_b200/parallel.py), `count`
+ *       values per side; push writes into the neighbours' slots, wait copies this rank's slots into its halo zones.
+ *   oz_peer_sum: all-reduce (sum, fixed rank order) of `rows` values: slots[r] -> rank r's [2][world][rows] slot array,
+ *       flags[r] -> rank r's [world] flags (both device arrays of `world` pointers). */
+OZ_API int oz_peer_halo_push(int dtype, const void* left_src, const void* right_src, int64_t count, void* left_dst,
+                             void* right_dst, uint64_t* left_flag, uint64_t* right_flag, const uint64_t* epoch_base,
+                             uint64_t epoch, void* stream);
+OZ_API int oz_peer_halo_wait(int dtype, const void* from_left_slot, const void* from_right_slot, int64_t count,
+                             void* left_halo, void* right_halo, const uint64_t* flag_left, const uint64_t* flag_right,
+                             const uint64_t* epoch_base, uint64_t epoch, int32_t* err, void* stream);
+OZ_API int oz_peer_epoch_advance(uint64_t* epoch_base, uint64_t by, void* stream);
+OZ_API int oz_peer_sum(int dtype, const void* local, int32_t rows, int32_t rank, int32_t world, void* const* slots,
+                       uint64_t* const* flags, const uint64_t* epoch_base, uint64_t epoch, void* out, int32_t* err,
+                       void* stream);
 
 /* No counterpart in the reference.  Same reverse sweep as oz_tm_adjoint, for callers that cannot
  * allocate device memory (plug-ins inside a host application that owns the GPU, real-time loops,

@@ -60,12 +60,20 @@ SYMBOLS = {
     'oz_fma_probe': (C.c_double, [C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'oz_rhs_eval': (C.c_int, [_PB, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'oz_rhs_out_vjp': (C.c_int, [_PB, C.c_int64] + [C.c_void_p] * 7),
+    'oz_rhs_jac_eval': (C.c_int, [_PB, C.c_int64, C.c_int64] + [C.c_void_p] * 5),
     'oz_tm_forward_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_forward': (C.c_int, [_PB]),
     'oz_tm_adjoint_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_adjoint': (C.c_int, [_PB]),
     'oz_static_scratch_bytes': (C.c_size_t, []),
     'oz_tm_adjoint_static': (C.c_int, [_PB]),
+    'oz_peer_halo_push': (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_uint64, C.c_void_p]),
+    'oz_peer_halo_wait': (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
+                                    C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    'oz_peer_epoch_advance': (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
+    'oz_peer_sum': (C.c_int, [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
+                              C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),
     'oz_picard_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_picard_forward': (C.c_int, [_PB, C.c_void_p, C.c_double, C.c_int]),
     'oz_colloc_residual': (C.c_int, [_PB, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),

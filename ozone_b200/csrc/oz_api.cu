@@ -151,7 +151,7 @@ int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* 
     OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(nodes >= 0, "negative node count");
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
-    EvalArgs ev{nodes, y, p, dy, prof, field, nullptr, nullptr, nullptr, nullptr, nullptr};
+    EvalArgs ev{nodes, y, p, dy, prof, field, nullptr, nullptr, nullptr, nullptr, nullptr, 1};
     return route(pb, TM_RHS_EVAL, nullptr, &ev);
 }
 
@@ -162,8 +162,19 @@ int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, const voi
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
     OZ_REQUIRE(nodes >= 0, "negative node count");
     OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "output VJPs are defined for per-trajectory right-hand sides");
-    EvalArgs ev{nodes, y, p, nullptr, nullptr, nullptr, vprof, vfield, y_bar, p_bar, th_bar};
+    EvalArgs ev{nodes, y, p, nullptr, nullptr, nullptr, vprof, vfield, y_bar, p_bar, th_bar, 1};
     return route(pb, TM_OUT_VJP, nullptr, &ev);
+}
+
+int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, const void* y, const void* p, void* f, void* Jy,
+                    void* Jp) {
+    OZ_REQUIRE(pb != nullptr, "null problem descriptor");
+    OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
+    OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
+    OZ_REQUIRE(nodes >= 0 && blocks >= 0, "negative node / block count");
+    OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "node Jacobians are defined for per-trajectory right-hand sides");
+    EvalArgs ev{nodes, y, p, f, nullptr, nullptr, nullptr, nullptr, Jy, Jp, nullptr, blocks};
+    return route(pb, TM_JAC_EVAL, nullptr, &ev);
 }
 
 size_t oz_tm_forward_workspace_bytes(const oz_problem* pb) {

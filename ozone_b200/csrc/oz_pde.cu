@@ -20,6 +20,7 @@
 // grid: reductions only count the cells it owns (see ozone_b200/parallel.py for the halo exchange).
 #include "oz_common.cuh"
 #include "oz_tm_launch.cuh"
+#include <cstdlib>
 #include "oz_linalg.cuh"
 
 namespace oz {
@@ -45,6 +46,18 @@ constexpr int kPdeFuse = OZ_PDE_FUSE;
 #define OZ_PDE_FUSE_ADJ 2
 #endif
 constexpr int kPdeFuseAdj = OZ_PDE_FUSE_ADJ;
+#ifndef OZ_PDE_TINY_CELLS        /* grids up to this many cells run 3 cells per thread instead of 4 */
+#define OZ_PDE_TINY_CELLS 160000
+#endif
+#ifndef OZ_PDE_SMALL_CELLS      /* grids up to this many cells (about one wave of CTAs) fuse more steps per launch */
+#define OZ_PDE_SMALL_CELLS 600000
+#endif
+#ifndef OZ_PDE_FUSE_SMALL
+#define OZ_PDE_FUSE_SMALL 16
+#endif
+#ifndef OZ_PDE_FUSE_ADJ_SMALL
+#define OZ_PDE_FUSE_ADJ_SMALL 8
+#endif
 
 template <typename T>
 struct PdeRhs {
@@ -124,7 +137,6 @@ OZ_D T block_sum(T v, T* sm) {
 //   exp(t) = 2^k 2^(j/32) e^r,  round(32 t log2 e) = 32 k + j,  |r| <= ln2 / 64,  e^r by a degree-6 Taylor sum
 // (truncation 3e-18 relative), 2^(j/32) from a 32-entry shared-memory table: 11 FP64 instructions, 9 constants.
 // 1 / (1 + x) is the reciprocal seed plus two Newton steps (oz_linalg.cuh).  Relative error of both ~2e-16.
-// fp32 keeps expf and the plain division.
 constexpr int kExpTab = 32;
 
 template <typename T>
@@ -134,8 +146,11 @@ OZ_D void pde_exp_table(T* tab) {  // caller synchronises before the first pde_e
     }
 }
 
-OZ_D float pde_exp(float t, const float*) { return expf(t); }
-OZ_D float pde_rcp(float x) { return 1.0f / x; }
+// fp32: the hardware exponential (ex2.approx after one multiply, relative error ~4e-7 for the arguments met here,
+// -gamma/(1+x) in [-2, -0.4]) and the approximate reciprocal (1 ulp): both far inside the 1e-5 the fp32 path promises,
+// and ~4 instructions instead of ~30 for expf + an IEEE division.
+OZ_D float pde_exp(float t, const float*) { return __expf(t); }
+OZ_D float pde_rcp(float x) { return __frcp_rn(x); }
 OZ_D double pde_rcp(double x) { return fast_rcp(x); }
 
 OZ_D double pde_exp(double t, const double* tab) {
@@ -163,10 +178,10 @@ OZ_D double pde_exp(double t, const double* tab) {
 
 // Per-CTA view of the tile.  EDGE = false is the fast path taken by CTAs whose extended tile lies inside the
 // domain and does not straddle an end of the control window: no per-cell predicates at all.
-template <typename T, bool EDGE>
+template <typename T, bool EDGE, int CPT>
 struct PdeTile {
-    bool inside[kPdeCpt];
-    T uh[kPdeCpt];     // 1 where the control acts on the cell, else 0 (EDGE only)
+    bool inside[CPT];
+    T uh[CPT];     // 1 where the control acts on the cell, else 0 (EDGE only)
     T uh_all;          // the same for the whole tile (fast path)
     OZ_D bool in(int m) const { return EDGE ? inside[m] : true; }
     OZ_D T mask(int m) const { return EDGE ? uh[m] : uh_all; }
@@ -175,34 +190,34 @@ struct PdeTile {
 // stages of one explicit step on the CTA's extended tile: F[i][m] for the cells this thread owns.
 // `line2` holds two lines used alternately: stage i+1 may overwrite its line while slower warps still read
 // stage i's, so one barrier per stencil application is enough.
-template <typename T, int S, bool WITH_DIAG, bool EDGE>
-OZ_D void pde_stages(const PdeArgs<T>& a, const PdeTile<T, EDGE>& tl, T h, T ulo, T uhi, const T* yv,
-                     T (*F)[kPdeCpt], T (*Dg)[kPdeCpt], T* line2, const T* etab, int phase = 0) {
+template <typename T, int S, bool WITH_DIAG, bool EDGE, int CPT>
+OZ_D void pde_stages(const PdeArgs<T>& a, const PdeTile<T, EDGE, CPT>& tl, T h, T ulo, T uhi, const T* yv,
+                     T (*F)[CPT], T (*Dg)[CPT], T* line2, const T* etab, int phase = 0) {
     const Tableau<T>& tab = a.tab;
     const T du = uhi - ulo;
 #pragma unroll
     for (int i = 0; i < S; ++i) {
-        T* line = line2 + ((i + phase) & 1) * kPdeLine;   // phase: stages done before this call (keeps the lines alternating)
-        T Yi[kPdeCpt];
+        T* line = line2 + ((i + phase) & 1) * (kPdeBlock * CPT + 2);   // phase: stages done before this call (keeps the lines alternating)
+        T Yi[CPT];
         const T bu_ui = a.rhs.beta_u * (ulo + tab.C[i] * du);   // beta_U * u at the stage abscissa
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) Yi[m] = yv[m];
+        for (int m = 0; m < CPT; ++m) Yi[m] = yv[m];
 #pragma unroll
         for (int j = 0; j < i; ++j) {
             const T haij = h * tab.a(i, j);          // CTA-uniform; the zero entries of a sparse tableau (RK4: 3 of 6)
-            if (haij != T(0)) {                      // skip their kPdeCpt FMAs with one uniform branch
+            if (haij != T(0)) {                      // skip their CPT FMAs with one uniform branch
 #pragma unroll
-                for (int m = 0; m < kPdeCpt; ++m) Yi[m] += haij * F[j][m];
+                for (int m = 0; m < CPT; ++m) Yi[m] += haij * F[j][m];
             }
         }
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
+        for (int m = 0; m < CPT; ++m) {
             if (EDGE && !tl.inside[m]) Yi[m] = T(0);
             line[1 + threadIdx.x + m * kPdeBlock] = Yi[m];
         }
         __syncthreads();
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
+        for (int m = 0; m < CPT; ++m) {
             const int e = threadIdx.x + m * kPdeBlock;
             const T x = Yi[m];
             const T q = pde_rcp(T(1) + x);
@@ -215,11 +230,11 @@ OZ_D void pde_stages(const PdeArgs<T>& a, const PdeTile<T, EDGE>& tl, T h, T ulo
     }
 }
 
-template <typename T, bool EDGE>
-OZ_D void pde_tile_setup(const PdeArgs<T>& a, long long base, PdeTile<T, EDGE>& tl) {
+template <typename T, bool EDGE, int CPT>
+OZ_D void pde_tile_setup(const PdeArgs<T>& a, long long base, PdeTile<T, EDGE, CPT>& tl) {
     if constexpr (EDGE) {
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
+        for (int m = 0; m < CPT; ++m) {
             const long long j = base + threadIdx.x + m * kPdeBlock;
             tl.inside[m] = j >= 0 && j < a.nx;
             const long long g = j + a.x_off;
@@ -232,11 +247,11 @@ OZ_D void pde_tile_setup(const PdeArgs<T>& a, long long base, PdeTile<T, EDGE>& 
 }
 
 // true when the CTA needs the predicated path: it touches an end of the domain or of the control window
-template <typename T>
+template <typename T, int CPT>
 OZ_D bool pde_is_edge(const PdeArgs<T>& a, long long base) {
-    const long long g0 = base + a.x_off, g1 = g0 + kPdeExt;   // global range of the extended tile
+    const long long g0 = base + a.x_off, g1 = g0 + (kPdeBlock * CPT);   // global range of the extended tile
     const bool cut_lo = g0 < a.rhs.h_lo && g1 > a.rhs.h_lo, cut_hi = g0 < a.rhs.h_hi && g1 > a.rhs.h_hi;
-    return base < 0 || base + kPdeExt > a.nx || cut_lo || cut_hi;
+    return base < 0 || base + (kPdeBlock * CPT) > a.nx || cut_lo || cut_hi;
 }
 
 // Forward launch: a.nsub consecutive steps on the CTA's extended tile.  Every step invalidates s more cells at
@@ -244,22 +259,22 @@ OZ_D bool pde_is_edge(const PdeArgs<T>& a, long long base) {
 // after the last one; what the fringe computes meanwhile is never stored.  The state stays in registers between the
 // fused steps: one global read of the tile and one write of the interior per launch instead of per step, and the
 // launch / fill / drain cost of a step-sized kernel (~5 us against ~10 us of work for 10^6 cells) is paid once.
-template <typename T, int S, bool EDGE>
+template <typename T, int S, bool EDGE, int CPT>
 OZ_D void pde_step_body(const PdeArgs<T>& a, long long base, T* line2, T* red, const T* etab) {
     const int halo = a.halo, interior = a.tile;
-    PdeTile<T, EDGE> tl;
-    pde_tile_setup<T, EDGE>(a, base, tl);
-    T yv[kPdeCpt], F[S][kPdeCpt];
+    PdeTile<T, EDGE, CPT> tl;
+    pde_tile_setup<T, EDGE, CPT>(a, base, tl);
+    T yv[CPT], F[S][CPT];
 #pragma unroll
-    for (int m = 0; m < kPdeCpt; ++m) yv[m] = tl.in(m) ? __ldg(a.y_in + base + threadIdx.x + m * kPdeBlock) : T(0);
+    for (int m = 0; m < CPT; ++m) yv[m] = tl.in(m) ? __ldg(a.y_in + base + threadIdx.x + m * kPdeBlock) : T(0);
     for (int j = 0; j < a.nsub; ++j) {
         const T h = __ldg(a.h + j), ulo = __ldg(a.u_lo + j), uhi = __ldg(a.u_hi + j);
-        pde_stages<T, S, false, EDGE>(a, tl, h, ulo, uhi, yv, F, nullptr, line2, etab, j * S);
+        pde_stages<T, S, false, EDGE, CPT>(a, tl, h, ulo, uhi, yv, F, nullptr, line2, etab, j * S);
         const bool last = j == a.nsub - 1;
         T* dst = a.rows_out ? a.rows_out + j * a.row_stride : (last ? a.y_out : nullptr);
         T acc2 = T(0);
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
+        for (int m = 0; m < CPT; ++m) {
             const int e = threadIdx.x + m * kPdeBlock;
             const long long c = base + e;
             T acc = T(0);
@@ -281,21 +296,25 @@ OZ_D void pde_step_body(const PdeArgs<T>& a, long long base, T* line2, T* red, c
 #ifndef OZ_MB_PDE
 #define OZ_MB_PDE 3
 #endif
-template <typename T, int S>
-__global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE) pde_step_kernel(const PdeArgs<T> a) {
-    __shared__ T line2[2 * kPdeLine];
+// resident CTAs per SM the kernels are compiled for, by cells per thread (fewer cells = fewer registers)
+constexpr int pde_mb_fwd(int cpt) { return cpt <= 2 ? 4 : OZ_MB_PDE; }
+constexpr int pde_mb_adj(int cpt) { return cpt <= 2 ? 3 : OZ_MB_PDE_ADJ; }
+
+template <typename T, int S, int CPT>
+__global__ void __launch_bounds__(kPdeBlock, pde_mb_fwd(CPT)) pde_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line2[2 * (kPdeBlock * CPT + 2)];
     __shared__ T red[32];
     __shared__ T etab[kExpTab];
     pde_exp_table(etab);   // visible after the first barrier inside pde_stages
     const long long base = (long long)blockIdx.x * a.tile - a.halo;
     if (threadIdx.x == 0) {
-        line2[0] = line2[kPdeLine] = T(0);
-        line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
+        line2[0] = line2[(kPdeBlock * CPT + 2)] = T(0);
+        line2[(kPdeBlock * CPT) + 1] = line2[(kPdeBlock * CPT + 2) + (kPdeBlock * CPT) + 1] = T(0);
     }
-    if (pde_is_edge(a, base))
-        pde_step_body<T, S, true>(a, base, line2, red, etab);
+    if (pde_is_edge<T, CPT>(a, base))
+        pde_step_body<T, S, true, CPT>(a, base, line2, red, etab);
     else
-        pde_step_body<T, S, false>(a, base, line2, red, etab);
+        pde_step_body<T, S, false, CPT>(a, base, line2, red, etab);
 }
 
 // sum of squares of a vector over the owned cells (J_space of the initial condition)
@@ -314,16 +333,16 @@ __global__ void __launch_bounds__(kPdeBlock) pde_sumsq_kernel(const T* __restric
 // Reverse launch: a.nsub consecutive reverse steps on the CTA's extended tile, multipliers kept in registers between
 // them.  Each step loads the exact y_k of the whole tile, re-derives its stages (s fringe cells per side go stale) and
 // runs the transposed chain (s more), so the multipliers of the interior are exact with a halo of 2 s nsub.
-template <typename T, int S, bool EDGE>
+template <typename T, int S, bool EDGE, int CPT>
 OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red, const T* etab) {
     const Tableau<T>& tab = a.tab;
     const int halo = a.halo, interior = a.tile;
-    PdeTile<T, EDGE> tl;
-    pde_tile_setup<T, EDGE>(a, base, tl);
-    T yv[kPdeCpt], lam[kPdeCpt], F[S][kPdeCpt], Yb[S][kPdeCpt], Dg[S][kPdeCpt];
-    bool owned[kPdeCpt];
+    PdeTile<T, EDGE, CPT> tl;
+    pde_tile_setup<T, EDGE, CPT>(a, base, tl);
+    T yv[CPT], lam[CPT], F[S][CPT], Yb[S][CPT], Dg[S][CPT];
+    bool owned[CPT];
 #pragma unroll
-    for (int m = 0; m < kPdeCpt; ++m) {
+    for (int m = 0; m < CPT; ++m) {
         const int e = threadIdx.x + m * kPdeBlock;
         const long long c = base + e;
         lam[m] = tl.in(m) ? __ldg(a.lam_in + c) : T(0);
@@ -333,30 +352,30 @@ OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red
     for (int j = 0; j < a.nsub; ++j) {
         const T* yrow = a.y_in - j * a.row_stride;
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) yv[m] = tl.in(m) ? __ldg(yrow + base + threadIdx.x + m * kPdeBlock) : T(0);
+        for (int m = 0; m < CPT; ++m) yv[m] = tl.in(m) ? __ldg(yrow + base + threadIdx.x + m * kPdeBlock) : T(0);
         const T h = __ldg(a.h - j), ulo = __ldg(a.u_lo - j), uhi = __ldg(a.u_hi - j);
-        pde_stages<T, S, true, EDGE>(a, tl, h, ulo, uhi, yv, F, Dg, line2, etab);
+        pde_stages<T, S, true, EDGE, CPT>(a, tl, h, ulo, uhi, yv, F, Dg, line2, etab);
 
         // transposed stage chain:  W_i = b_i lam + sum_{j>i} a_ji Ybar_j,  G_i = h W_i,  Ybar_i = J(Y_i)^T G_i
         // h_bar = sum_i W_i . F_i (no division by h);  u_bar parts from beta_U H . G_i
         T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
 #pragma unroll
         for (int i = S - 1; i >= 0; --i) {
-            T* line = line2 + ((S + (S - 1 - i)) & 1) * kPdeLine;   // keeps alternating after the S forward stages
-            T G[kPdeCpt];
+            T* line = line2 + ((S + (S - 1 - i)) & 1) * (kPdeBlock * CPT + 2);   // keeps alternating after the S forward stages
+            T G[CPT];
 #pragma unroll
-            for (int m = 0; m < kPdeCpt; ++m) G[m] = tab.B[i] * lam[m];
+            for (int m = 0; m < CPT; ++m) G[m] = tab.B[i] * lam[m];
 #pragma unroll
             for (int q = i + 1; q < S; ++q) {
                 const T aqi = tab.a(q, i);
                 if (aqi != T(0)) {
 #pragma unroll
-                    for (int m = 0; m < kPdeCpt; ++m) G[m] += aqi * Yb[q][m];
+                    for (int m = 0; m < CPT; ++m) G[m] += aqi * Yb[q][m];
                 }
             }
             T usum = T(0);
 #pragma unroll
-            for (int m = 0; m < kPdeCpt; ++m) {
+            for (int m = 0; m < CPT; ++m) {
                 if (owned[m]) h_acc += G[m] * F[i][m];
                 G[m] = (EDGE && !tl.inside[m]) ? T(0) : h * G[m];
                 if (owned[m]) usum += tl.mask(m) * G[m];
@@ -364,7 +383,7 @@ OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red
             }
             __syncthreads();
 #pragma unroll
-            for (int m = 0; m < kPdeCpt; ++m) {
+            for (int m = 0; m < CPT; ++m) {
                 const int e = threadIdx.x + m * kPdeBlock;
                 const T v = (line[e] - T(2) * G[m] + line[e + 2]) * a.rhs.inv_dx2 + Dg[i][m] * G[m];
                 Yb[i][m] = (EDGE && !tl.inside[m]) ? T(0) : v;
@@ -376,7 +395,7 @@ OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red
         const bool last = j == a.nsub - 1;
         const T* hb = a.hist_bar_k ? a.hist_bar_k - j * a.nx : nullptr;
 #pragma unroll
-        for (int m = 0; m < kPdeCpt; ++m) {
+        for (int m = 0; m < CPT; ++m) {
             const int e = threadIdx.x + m * kPdeBlock;
             const long long c = base + e;
             T yb = T(0);
@@ -397,21 +416,21 @@ OZ_D void pde_adjoint_body(const PdeArgs<T>& a, long long base, T* line2, T* red
     }
 }
 
-template <typename T, int S>
-__global__ void __launch_bounds__(kPdeBlock, OZ_MB_PDE_ADJ) pde_adjoint_step_kernel(const PdeArgs<T> a) {
-    __shared__ T line2[2 * kPdeLine];
+template <typename T, int S, int CPT>
+__global__ void __launch_bounds__(kPdeBlock, pde_mb_adj(CPT)) pde_adjoint_step_kernel(const PdeArgs<T> a) {
+    __shared__ T line2[2 * (kPdeBlock * CPT + 2)];
     __shared__ T red[32];
     __shared__ T etab[kExpTab];
     pde_exp_table(etab);
     const long long base = (long long)blockIdx.x * a.tile - a.halo;
     if (threadIdx.x == 0) {
-        line2[0] = line2[kPdeLine] = T(0);
-        line2[kPdeExt + 1] = line2[kPdeLine + kPdeExt + 1] = T(0);
+        line2[0] = line2[(kPdeBlock * CPT + 2)] = T(0);
+        line2[(kPdeBlock * CPT) + 1] = line2[(kPdeBlock * CPT + 2) + (kPdeBlock * CPT) + 1] = T(0);
     }
-    if (pde_is_edge(a, base))
-        pde_adjoint_body<T, S, true>(a, base, line2, red, etab);
+    if (pde_is_edge<T, CPT>(a, base))
+        pde_adjoint_body<T, S, true, CPT>(a, base, line2, red, etab);
     else
-        pde_adjoint_body<T, S, false>(a, base, line2, red, etab);
+        pde_adjoint_body<T, S, false, CPT>(a, base, line2, red, etab);
 }
 
 // lam_n = final_bar + hist_bar[n] + field_bar * (200/nx) * y_n
@@ -462,9 +481,30 @@ __global__ void __launch_bounds__(256) pde_grads_kernel(int n, long long ncta, c
     if (threadIdx.x == 0 && u_bar) u_bar[k] = s + ((field_bar && k < k_cost_end) ? T(40) * field_bar[0] * u[k] : T(0));
 }
 
+template <typename T, int S>
+static void launch_pde_step(int cpt, unsigned grid, cudaStream_t st, const PdeArgs<T>& a) {
+    if (cpt == 2)
+        pde_step_kernel<T, S, 2><<<grid, kPdeBlock, 0, st>>>(a);
+    else if (cpt == 3)
+        pde_step_kernel<T, S, 3><<<grid, kPdeBlock, 0, st>>>(a);
+    else
+        pde_step_kernel<T, S, 4><<<grid, kPdeBlock, 0, st>>>(a);
+}
+template <typename T, int S>
+static void launch_pde_adjoint(int cpt, unsigned grid, cudaStream_t st, const PdeArgs<T>& a) {
+    if (cpt == 2)
+        pde_adjoint_step_kernel<T, S, 2><<<grid, kPdeBlock, 0, st>>>(a);
+    else if (cpt == 3)
+        pde_adjoint_step_kernel<T, S, 3><<<grid, kPdeBlock, 0, st>>>(a);
+    else
+        pde_adjoint_step_kernel<T, S, 4><<<grid, kPdeBlock, 0, st>>>(a);
+}
+
 struct PdeLayout {
     long long nx, ncta_f, ncta_a, sq_blocks;
     int tile_f, tile_a;
+    int fuse_f, fuse_a;   // steps per forward / reverse launch
+    int cpt_f, cpt_a;     // cells per thread of the forward / reverse kernel (tile = 256 * cpt cells including halos)
     size_t off_ping, off_pong, off_sq, off_seg, off_lam0, off_lam1, off_ph, off_pulo, off_puhi, total_fwd, total_adj;
 };
 
@@ -487,13 +527,35 @@ static PdeLayout pde_layout(const oz_problem* pb) {
         *tile = (int)t;
         return (L.nx + t - 1) / t;
     };
-    int occ_f = 3, occ_a = 2;
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_f, pde_step_kernel<T, S>, kPdeBlock, 0);
-    cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ_a, pde_adjoint_step_kernel<T, S>, kPdeBlock, 0);
-    if (occ_f < 1) occ_f = 1;
-    if (occ_a < 1) occ_a = 1;
-    L.ncta_f = balance(kPdeExt - 2 * S * kPdeFuse, sm_count() * occ_f, &L.tile_f);
-    L.ncta_a = balance(kPdeExt - 4 * S * kPdeFuseAdj, sm_count() * occ_a, &L.tile_a);
+    // Steps fused per launch.  A launch costs ~5 us of launch + fill + drain whatever its size, a fused step adds s
+    // (forward) / 2 s (reverse) redundant cells per side of every tile.  Big grids (many waves of CTAs) do best with
+    // 4 / 2; a grid of a wave or two of CTAs -- the slab of a 2 to 8 GPU spatial shard -- is latency-bound per launch
+    // and takes the deeper fusion 16 / 8 (tools/pde_scaling.py, profiles/r2_pde_fusion_sweep.txt: 125k cells 3.79 + 10.34
+    // -> 3.26 + 8.31 us per forward / reverse step, 500k cells 8.05 + 20.76 -> 7.34 + 18.76; 10^6 cells are best at 4 / 2).
+    // OZ_PDE_FUSE_F / OZ_PDE_FUSE_A (environment) override for experiments.
+    const bool small = L.nx <= (long long)OZ_PDE_SMALL_CELLS;
+    L.fuse_f = small ? OZ_PDE_FUSE_SMALL : kPdeFuse;
+    L.fuse_a = small ? OZ_PDE_FUSE_ADJ_SMALL : kPdeFuseAdj;
+    if (const char* e = getenv("OZ_PDE_FUSE_F")) L.fuse_f = atoi(e);
+    if (const char* e = getenv("OZ_PDE_FUSE_A")) L.fuse_a = atoi(e);
+    if (L.fuse_f < 1) L.fuse_f = 1;
+    if (L.fuse_a < 1) L.fuse_a = 1;
+    // Cells per thread (tile = 256 x cpt cells including halos).  4 is best from 250k cells up, also for the reverse
+    // kernel although it spills 152 B there (3 cells per thread do not spill but lose more to halos: 34.8 vs 33.7 us per
+    // reverse step at 10^6 cells); a grid of about one wave of CTAs (<= OZ_PDE_TINY_CELLS, the slab of an 8-GPU shard)
+    // gains 6-8 % from 3 (profiles/r2_pde_cells_per_thread_sweep.txt).
+    const bool tiny = L.nx <= (long long)OZ_PDE_TINY_CELLS;
+    L.cpt_f = tiny ? 3 : kPdeCpt;
+    L.cpt_a = tiny ? 3 : kPdeCpt;
+    if (const char* e = getenv("OZ_PDE_CPT_F")) L.cpt_f = atoi(e);
+    if (const char* e = getenv("OZ_PDE_CPT_A")) L.cpt_a = atoi(e);
+    if (L.cpt_f != 2 && L.cpt_f != 3) L.cpt_f = 4;
+    if (L.cpt_a != 2 && L.cpt_a != 3) L.cpt_a = 4;
+    const int ext_f = kPdeBlock * L.cpt_f, ext_a = kPdeBlock * L.cpt_a;
+    while (2 * S * L.fuse_f > ext_f / 2) --L.fuse_f;      // keep at least half of every tile interior
+    while (4 * S * L.fuse_a > ext_a / 2) --L.fuse_a;
+    L.ncta_f = balance(ext_f - 2 * S * L.fuse_f, 0, &L.tile_f);
+    L.ncta_a = balance(ext_a - 4 * S * L.fuse_a, 0, &L.tile_a);
     const size_t nx = (size_t)L.nx, nt = (size_t)pb->n + 1;
     const size_t vec = (nx + 31) / 32 * 32;
     // forward: ping, pong, part_sq[nt][ncta_f]
@@ -560,13 +622,13 @@ static int pde_forward(const oz_problem* pb) {
         OZ_CUDA_CHECK(cudaMemsetAsync(part_sq, 0, (size_t)L.ncta_f * sizeof(T), st));
         pde_sumsq_kernel<T><<<(unsigned)(L.ncta_f < 1024 ? L.ncta_f : 1024), kPdeBlock, 0, st>>>(cur, a.own_lo, a.own_hi, part_sq);
     }
-    a.halo = S * kPdeFuse;
+    a.halo = S * L.fuse_f;
     a.sq_stride = L.ncta_f;
     a.row_stride = nx;
     int launch = 0;
     for (int k = 0; k < n;) {
         // steps k .. k + nsub - 1 in one launch; a group never crosses a checkpoint
-        int nsub = n - k < kPdeFuse ? n - k : kPdeFuse;
+        int nsub = n - k < L.fuse_f ? n - k : L.fuse_f;
         if (ckpt && ni > 0 && nsub > ni - k % ni) nsub = ni - k % ni;
         const int kl = k + nsub;                       // index of the state the launch ends on
         const bool at_ckpt = ckpt && ni > 0 && kl % ni == 0;
@@ -587,7 +649,7 @@ static int pde_forward(const oz_problem* pb) {
         a.u_lo = u + k;
         a.u_hi = u + k + 1;
         a.part_sq = part_sq ? part_sq + (size_t)(k + 1) * L.ncta_f : nullptr;
-        pde_step_kernel<T, S><<<(unsigned)L.ncta_f, kPdeBlock, 0, st>>>(a);
+        launch_pde_step<T, S>(L.cpt_f, (unsigned)L.ncta_f, st, a);
         if (hist && at_ckpt)
             OZ_CUDA_CHECK(cudaMemcpyAsync(ckpt + (size_t)(kl / ni) * nx, out, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
         cur = out;
@@ -649,10 +711,10 @@ static int pde_adjoint(const oz_problem* pb) {
             const T* start = (pb->num_inner > 0) ? ckpt + (size_t)o * nx : (const T*)pb->y0;
             OZ_CUDA_CHECK(cudaMemcpyAsync(seg, start, nx * sizeof(T), cudaMemcpyDeviceToDevice, st));
             for (int q = 0; q + 1 < ni;) {             // rows q+1 .. q+nsub of the segment from row q, fused
-                const int nsub = ni - 1 - q < kPdeFuse ? ni - 1 - q : kPdeFuse;
+                const int nsub = ni - 1 - q < L.fuse_f ? ni - 1 - q : L.fuse_f;
                 PdeArgs<T> f = a;
                 f.tile = L.tile_f;
-                f.halo = S * kPdeFuse;
+                f.halo = S * L.fuse_f;
                 f.nsub = nsub;
                 f.y_in = seg + (size_t)q * vec;
                 f.y_out = nullptr;
@@ -662,15 +724,15 @@ static int pde_adjoint(const oz_problem* pb) {
                 f.u_lo = u + lo + q;
                 f.u_hi = u + lo + q + 1;
                 f.part_sq = nullptr;
-                pde_step_kernel<T, S><<<(unsigned)L.ncta_f, kPdeBlock, 0, st>>>(f);
+                launch_pde_step<T, S>(L.cpt_f, (unsigned)L.ncta_f, st, f);
                 q += nsub;
             }
         }
         for (int k = lo + ni - 1; k >= lo;) {          // steps k .. k - nsub + 1 in one launch, within the segment
-            const int nsub = k - lo + 1 < kPdeFuseAdj ? k - lo + 1 : kPdeFuseAdj;
+            const int nsub = k - lo + 1 < L.fuse_a ? k - lo + 1 : L.fuse_a;
             const int kl = k - nsub + 1;
             a.nsub = nsub;
-            a.halo = 2 * S * kPdeFuseAdj;
+            a.halo = 2 * S * L.fuse_a;
             a.row_stride = use_seg ? (long long)vec : nx;
             a.adj_stride = L.ncta_a;
             a.y_in = use_seg ? seg + (size_t)(k - lo) * vec : hist + (size_t)k * nx;
@@ -683,7 +745,7 @@ static int pde_adjoint(const oz_problem* pb) {
             a.part_h = ph + (size_t)k * L.ncta_a;
             a.part_ulo = pulo + (size_t)k * L.ncta_a;
             a.part_uhi = puhi + (size_t)k * L.ncta_a;
-            pde_adjoint_step_kernel<T, S><<<(unsigned)L.ncta_a, kPdeBlock, 0, st>>>(a);
+            launch_pde_adjoint<T, S>(L.cpt_a, (unsigned)L.ncta_a, st, a);
             cur ^= 1;
             k = kl - 1;
         }

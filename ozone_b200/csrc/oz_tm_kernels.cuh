@@ -34,6 +34,9 @@ constexpr bool use_reg_solve() {
 #ifndef OZ_SPARSE_SOLVE   /* 1: structure-aware elimination (oz_sparse_solve.cuh); 0: dense register elimination (A/B baseline) */
 #define OZ_SPARSE_SOLVE 1
 #endif
+#ifndef OZ_ADJ_SOLVE_EARLY_EXIT   /* reverse sweep: pivot tests leave the elimination early (fewer live registers, see oz_sparse_solve.cuh) */
+#define OZ_ADJ_SOLVE_EARLY_EXIT true
+#endif
 #ifndef OZ_IMPL_BLOCK   /* threads per block of the register-solve implicit kernels */
 #define OZ_IMPL_BLOCK 64
 #endif
@@ -596,7 +599,7 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 b[uidx<R, S>(j, c)] = h * tab.B[j] * acc;
             });
         });
-        bad = sparse_solve<R, S, true, T>(Mt, b);
+        bad = sparse_solve<R, S, true, T, OZ_ADJ_SOLVE_EARLY_EXIT>(Mt, b);
 #else
         assemble([&](int r, int c, T v) { Mt[r][c] = v; }, [&](int r, T v) { b[r] = v; });
         bad = reg_solve<T, MA>(Mt, b);
@@ -725,11 +728,16 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
 // The specialised kernels run the same code; the options are pinned to constants below, so the compiler removes
 // the per-step null-pointer branches, the second copy of the stage sweep and the output-cotangent arithmetic
 // (ncu, round 1: 12 uniform branches and ~22 register moves per step on a sweep that is issue-bound).
+template <class R, typename T, int S, bool IMPL, int SPEC>
+OZ_D void tm_adjoint_body(const TmArgs<T>& a, const AdjWsPtr<T>& ws);
+
 template <class R, typename T, int S, bool IMPL, int SPEC = 0>
 __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S, T, IMPL, true>()))
     tm_adjoint_kernel(const TmArgs<T> a_in, const AdjWsPtr<T> ws) {
-    TmArgs<T> a = a_in;
-    if constexpr (SPEC != 0) {
+    if constexpr (SPEC == 0) {
+        tm_adjoint_body<R, T, S, IMPL, 0>(a_in, ws);      // straight from the parameter block (constant bank)
+    } else {
+        TmArgs<T> a = a_in;
         a.hist_bar = nullptr;
         a.prof_bar = nullptr;
         a.field_bar = nullptr;
@@ -741,7 +749,12 @@ __global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S
         __builtin_assume(a.p_bar != nullptr);
         __builtin_assume(a.hist != nullptr);
         __builtin_assume(a.final_bar != nullptr);
+        tm_adjoint_body<R, T, S, IMPL, SPEC>(a, ws);
     }
+}
+
+template <class R, typename T, int S, bool IMPL, int SPEC>
+OZ_D void tm_adjoint_body(const TmArgs<T>& a, const AdjWsPtr<T>& ws) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     constexpr bool HAS_OUT = (DM::NP + DM::NF) > 0;
@@ -1114,6 +1127,64 @@ __global__ void __launch_bounds__(128) rhs_out_vjp_kernel(long long nodes, int t
     if (tb)
 #pragma unroll
         for (int c = 0; c < DM::SP; ++c) tb[c * nodes + i] = gt[c];
+}
+
+// Jacobians of f at blocks x nodes points: what an optimiser needs to write down the constraint Jacobian of the
+// Collocation approach block by block (dc1/dY_k = h_k (A (x) I) blkdiag(J_y) - I, ...; ozone/integrators/collocation.py:48-57
+// leaves this to csdl's reverse mode).  Layouts keep the trajectory index innermost, one block per (step, stage):
+//   y [blocks][D][nodes], p [blocks][P][nodes]  ->  f [blocks][D][nodes], Jy [blocks][D][D][nodes] (d f_r / d y_c at [r][c]),
+//   Jp [blocks][D][P][nodes]; th [S] or [S][nodes].  With blocks = n s and nodes = N these are the stage design variables
+// of the Collocation approach as they lie in memory.
+template <class R, typename T>
+__global__ void __launch_bounds__(128) rhs_jac_kernel(long long nodes, int th_shared, const T* __restrict__ y,
+                                                      const T* __restrict__ p, const T* __restrict__ th, T* __restrict__ f,
+                                                      T* __restrict__ Jy, T* __restrict__ Jp) {
+    using DM = Dims<R>;
+    constexpr int D = DM::D;
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= nodes) return;
+    const long long b = blockIdx.y;
+    y += b * D * nodes;
+    p += b * DM::P * nodes;
+    T yy[D], pp[DM::P1], tt[DM::S1];
+#pragma unroll
+    for (int c = 0; c < D; ++c) yy[c] = y[c * nodes + i];
+#pragma unroll
+    for (int c = 0; c < DM::P; ++c) pp[c] = p[c * nodes + i];
+#pragma unroll
+    for (int c = 0; c < DM::SP; ++c) tt[c] = th_shared ? th[c] : th[c * nodes + i];
+    if (f) {
+        T d[D];
+        R::f(yy, pp, tt, d);
+#pragma unroll
+        for (int c = 0; c < D; ++c) f[(b * D + c) * nodes + i] = d[c];
+    }
+    if (Jy) {
+        T J[D * D];
+        R::jac(yy, pp, tt, J);
+#pragma unroll
+        for (int c = 0; c < D * D; ++c) Jy[(b * D * D + c) * nodes + i] = J[c];
+    }
+    if constexpr (DM::P > 0) {
+        if (Jp) {
+#pragma unroll
+            for (int r = 0; r < D; ++r) {      // row r of J_p = J_p^T e_r
+                T v[D], gy[D], gp[DM::P1], gt[DM::S1];
+#pragma unroll
+                for (int c = 0; c < D; ++c) {
+                    v[c] = c == r ? T(1) : T(0);
+                    gy[c] = T(0);
+                }
+#pragma unroll
+                for (int c = 0; c < DM::P1; ++c) gp[c] = T(0);
+#pragma unroll
+                for (int c = 0; c < DM::S1; ++c) gt[c] = T(0);
+                R::vjp(yy, pp, tt, v, gy, gp, gt);
+#pragma unroll
+                for (int c = 0; c < DM::P; ++c) Jp[((b * D + r) * DM::P + c) * nodes + i] = gp[c];
+            }
+        }
+    }
 }
 
 }  // namespace oz

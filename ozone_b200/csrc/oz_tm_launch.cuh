@@ -11,7 +11,7 @@ namespace oz {
 #define OZ_ADJ_SPEC_STAGES 4
 #endif
 
-enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3, TM_OUT_VJP = 4 };
+enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3, TM_OUT_VJP = 4, TM_JAC_EVAL = 5 };
 
 struct EvalArgs {
     long long nodes;
@@ -20,6 +20,7 @@ struct EvalArgs {
     // TM_OUT_VJP: cotangents of the outputs in, gradients per node out
     const void *vprof, *vfield;
     void *yb, *pb, *tb;
+    long long blocks;     // TM_JAC_EVAL: number of [D][nodes] blocks (one per (step, stage))
 };
 
 template <class R, typename T, int S, bool IMPL>
@@ -126,6 +127,31 @@ int dispatch_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
 
 template <class R>
 int dispatch_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    if (mode == TM_JAC_EVAL) {     // f -> ev->dy, Jy -> ev->yb, Jp -> ev->pb
+        cudaStream_t stream = (cudaStream_t)pb->stream;
+        const dim3 grid((unsigned)((ev->nodes + 127) / 128), (unsigned)ev->blocks);
+        if (grid.x == 0 || grid.y == 0) return 0;
+        OZ_REQUIRE(ev->blocks <= 65535, "at most 65535 blocks per Jacobian launch");
+        if constexpr (OZ_WANT_F64(true)) {
+            if (pb->dtype == OZ_F64) {
+                rhs_jac_kernel<R, double><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const double*)ev->y, (const double*)ev->p,
+                                                                  (const double*)pb->th, (double*)ev->dy, (double*)ev->yb,
+                                                                  (double*)ev->pb);
+                OZ_CUDA_CHECK(cudaGetLastError());
+                return 0;
+            }
+        }
+        if constexpr (OZ_WANT_F64(false)) {
+            if (pb->dtype == OZ_F32) {
+                rhs_jac_kernel<R, float><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const float*)ev->y, (const float*)ev->p,
+                                                                 (const float*)pb->th, (float*)ev->dy, (float*)ev->yb, (float*)ev->pb);
+                OZ_CUDA_CHECK(cudaGetLastError());
+                return 0;
+            }
+        }
+        set_error("no Jacobian kernel for dtype %d in this build", pb->dtype);
+        return -1;
+    }
     if (mode == TM_OUT_VJP) {
         cudaStream_t stream = (cudaStream_t)pb->stream;
         const unsigned grid = (unsigned)((ev->nodes + 127) / 128);

@@ -288,6 +288,12 @@ GRID_STEPS_PER_LAUNCH = 4      # OZ_PDE_FUSE in csrc/oz_pde.cu: forward grid ste
 GRID_REVERSE_STEPS_PER_LAUNCH = 2   # OZ_PDE_FUSE_ADJ
 
 
+def grid_fusion(nx):
+    """(forward, reverse) steps fused per launch for a grid of nx cells: mirrors pde_layout() in csrc/oz_pde.cu
+    (launch counting only)."""
+    return (16, 8) if nx <= 600000 else (GRID_STEPS_PER_LAUNCH, GRID_REVERSE_STEPS_PER_LAUNCH)
+
+
 class TmPlan:
     """A solve with every buffer allocated once: repeated forward()/adjoint() calls only enqueue
     kernels (no allocation, no host sync).  This is what a caller inside an optimisation loop
@@ -344,11 +350,11 @@ class TmPlan:
                           if flag and self.grad[k] is not None)
         self.launches_forward, self.launches_adjoint = 1, 1 + shared_rows
         if spec.info['kind'] == 1:      # grid: fused multi-step launches (+ sum-of-squares, field / terminal, replay, gradient reducers)
-            K, ni = GRID_STEPS_PER_LAUNCH, spec.num_inner
+            (K, KR), ni = grid_fusion(spec.d), spec.num_inner
             groups = lambda steps: -(-steps // K)          # launches of the fused forward kernel for a run of steps
             nseg = (n // ni) if (ni > 0 and self.hist is None) else 0
             self.launches_forward = ((n // ni) * groups(ni) if ni > 0 else groups(n)) + 2
-            rgroups = lambda steps: -(-steps // GRID_REVERSE_STEPS_PER_LAUNCH)
+            rgroups = lambda steps: -(-steps // KR)
             self.launches_adjoint = 1 + (nseg * (groups(ni - 1) + rgroups(ni)) if nseg else rgroups(n)) + 1
 
     def forward(self):
@@ -515,6 +521,33 @@ def rhs_out_vjp(spec: SolveSpec, y, p, th, vprof, vfield):
     nat.check(nat.lib.oz_rhs_out_vjp(C.byref(pb), nodes, _ptr(y), _ptr(p), _ptr(vprof), _ptr(vfield), _ptr(yb), _ptr(pbar),
                                      _ptr(tbar)), 'oz_rhs_out_vjp')
     return yb, pbar, tbar
+
+
+def rhs_jac_eval(spec: SolveSpec, y, p=None, th=None, want_f=True, want_p=True):
+    """oz_rhs_jac_eval on y (blocks, d, nodes), p (blocks, P, nodes) -> f (blocks, d, nodes), Jy (blocks, d, d, nodes),
+    Jp (blocks, d, P, nodes) | None.  th (S,) or (S, nodes)."""
+    pb = make_problem(spec)
+    info, dev = spec.info, y.device
+    blocks, _, nodes = y.shape
+    y = y.contiguous()
+    p = p.contiguous() if (p is not None and info['P']) else None
+    th = th.contiguous() if (th is not None and info['S']) else None
+    pb.th = _ptr(th)
+    pb.th_shared = int(th is None or th.dim() == 1)
+    d, P = info['d'], info['P']
+    f = torch.empty((blocks, d, nodes), dtype=spec.dtype, device=dev) if want_f else None
+    Jy = torch.empty((blocks, d, d, nodes), dtype=spec.dtype, device=dev)
+    Jp = torch.empty((blocks, d, P, nodes), dtype=spec.dtype, device=dev) if (P and want_p) else None
+    nat.check(nat.lib.oz_rhs_jac_eval(C.byref(pb), nodes, blocks, _ptr(y), _ptr(p), _ptr(f), _ptr(Jy), _ptr(Jp)), 'oz_rhs_jac_eval')
+    return f, Jy, Jp
+
+
+def stage_parameters(spec: SolveSpec, p):
+    """Dynamic parameters at the stage abscissae, (n, s, P, N): p[k] (1 - c_j) + p[k+1] c_j (collections.py:277-289)."""
+    n, N, P = spec.n, spec.N, spec.info['P']
+    Cc = torch.as_tensor(spec.method.C, dtype=spec.dtype, device=p.device).reshape(1, -1, 1, 1)
+    pf = p.unsqueeze(-1).expand(n + 1, P, N) if spec.p_shared else p
+    return (pf[:-1].unsqueeze(1) * (1.0 - Cc) + pf[1:].unsqueeze(1) * Cc).contiguous()
 
 
 class _OutputsOnHistory(torch.autograd.Function):

@@ -210,8 +210,14 @@ class Collocation(IntegratorBase):
         guess = pk.pack_guess(self.states)
         if guess is None:                                                    # collections.py:129-133
             guess = self.y0.detach().unsqueeze(0).expand(n, pk.d, pk.N)
-        stage_dv = guess.unsqueeze(1).expand(n, s, pk.d, pk.N).contiguous().clone().requires_grad_(True)
-        state_dv = guess.contiguous().clone().requires_grad_(True)
+        given = self.options.get('collocation_design_values')
+        if given is not None:            # an optimiser re-evaluating the model at its own iterate (optimize.py)
+            stage_dv, state_dv = given
+            if tuple(stage_dv.shape) != (n, s, pk.d, pk.N) or tuple(state_dv.shape) != (n, pk.d, pk.N):
+                raise ValueError(f'collocation_design_values must have shapes {(n, s, pk.d, pk.N)} and {(n, pk.d, pk.N)}')
+        else:
+            stage_dv = guess.unsqueeze(1).expand(n, s, pk.d, pk.N).contiguous().clone().requires_grad_(True)
+            state_dv = guess.contiguous().clone().requires_grad_(True)
         c1, c2 = engine.collocation(self.spec, self.y0, self.h, self.p, self.th, stage_dv, state_dv)
         hist = torch.cat([self.y0.unsqueeze(0), state_dv], dim=0)            # collections.py:228-232
         out = dict(hist=hist, final=hist[-1])

@@ -117,3 +117,134 @@ def solve_collocation(ode_problem, ftol=1e-9, maxiter=200, verbose=False):
     outputs = nlp.commit(res.x[:-1])
     outputs.optimizer_result = res
     return outputs
+
+
+# ================================================================================================
+# Batched {f, c, df, dc} for an optimiser (what `compute_optimization_derivatives()` hands modopt /
+# SNOPT in the reference, ozone/paper_examples/utils/utils.py:237, 273-286).
+class CollocationBlocks:
+    """The Jacobian of the collocation constraints of N independent designs in factored, per-step form.
+
+    For step k, stage i:  c1[k,i] = h_k sum_j a_ij f(Y[k,j], p_kj) + yfull[k] - Y[k,i]
+                          c2[k]   = h_k sum_j b_j  f(Y[k,j], p_kj) + yfull[k] - yfull[k+1]          (collocation.py:48-50)
+    with yfull = [y0; y] and p_kj = p[k] (1 - c_j) + p[k+1] c_j (collections.py:277-289).  Every block of dc is a product
+    of a tableau entry, a step size and a node Jacobian, so only those are stored (one kernel launch, HBM-lean):
+        F  [n, s, d, N]       f at the stage nodes            (d c / d h_k)
+        Jy [n, s, d, d, N]    df/dy at the stage nodes        (d c / d Y)
+        Jp [n, s, d, P, N]    df/dp at the stage nodes        (d c / d p[k], d p[k+1])
+    ``dense(i)`` expands one design's Jacobian; ``rmatvec`` is the transposed product through the VJP kernel."""
+
+    def __init__(self, integ, Y, y):
+        spec = integ.spec
+        self.integ, self.spec = integ, spec
+        n, s, d, N = spec.n, spec.method.num_stages, spec.d, spec.N
+        P = spec.info['P']
+        self.n, self.s, self.d, self.N, self.P = n, s, d, N, P
+        y0, h, p, th = (None if t is None else t.detach() for t in (integ.y0, integ.h, integ.p, integ.th))
+        A = torch.as_tensor(spec.method.A, dtype=spec.dtype, device=Y.device)
+        B = torch.as_tensor(spec.method.B, dtype=spec.dtype, device=Y.device).reshape(-1)
+        Cc = torch.as_tensor(spec.method.C, dtype=spec.dtype, device=Y.device).reshape(-1)
+        self.A, self.B, self.C = A, B, Cc
+        self.h = h if not spec.h_shared else h.unsqueeze(-1).expand(n, N)
+        pst = engine.stage_parameters(spec, p).reshape(n * s, P, N) if P else None
+        F, Jy, Jp = engine.rhs_jac_eval(spec, Y.detach().reshape(n * s, d, N), pst, th)     # ONE launch, no re-layout
+        self.F = F.reshape(n, s, d, N)
+        self.Jy = Jy.reshape(n, s, d, d, N)
+        self.Jp = Jp.reshape(n, s, d, P, N) if Jp is not None else None
+
+    # ---- one design, dense: rows [c1 (n s d), c2 (n d)], columns [Y (n s d), y (n d), y0 (d), h (n), p ((n+1) P)]
+    def dense(self, i):
+        n, s, d, P = self.n, self.s, self.d, self.P
+        A, B, Cc = (t.cpu().numpy() for t in (self.A, self.B, self.C))
+        F, Jy = self.F[..., i].cpu().numpy(), self.Jy[..., i].cpu().numpy()
+        Jp = self.Jp[..., i].cpu().numpy() if self.Jp is not None else None
+        h = self.h[:, i].cpu().numpy()
+        nY, ny = n * s * d, n * d
+        cols = dict(Y=(0, nY), y=(nY, ny), y0=(nY + ny, d), h=(nY + ny + d, n), p=(nY + ny + d + n, (n + 1) * P))
+        ncol = nY + ny + d + n + (n + 1) * P
+        J = np.zeros((nY + ny, ncol))
+        yf_col = lambda k: (cols['y0'][0] if k == 0 else cols['y'][0] + (k - 1) * d)
+        for k in range(n):
+            for i_ in range(s):
+                r0 = (k * s + i_) * d
+                for j in range(s):
+                    c0 = (k * s + j) * d
+                    J[r0:r0 + d, c0:c0 + d] += h[k] * A[i_, j] * Jy[k, j]
+                    if Jp is not None:
+                        for q, wgt in ((k, 1.0 - Cc[j]), (k + 1, Cc[j])):
+                            pc = cols['p'][0] + q * P
+                            J[r0:r0 + d, pc:pc + P] += h[k] * A[i_, j] * wgt * Jp[k, j]
+                    J[r0:r0 + d, cols['h'][0] + k] += A[i_, j] * F[k, j]
+                J[r0:r0 + d, r0:r0 + d] -= np.eye(d)
+                J[r0:r0 + d, yf_col(k):yf_col(k) + d] += np.eye(d)
+            r0 = nY + k * d
+            for j in range(s):
+                c0 = (k * s + j) * d
+                J[r0:r0 + d, c0:c0 + d] += h[k] * B[j] * Jy[k, j]
+                if Jp is not None:
+                    for q, wgt in ((k, 1.0 - Cc[j]), (k + 1, Cc[j])):
+                        pc = cols['p'][0] + q * P
+                        J[r0:r0 + d, pc:pc + P] += h[k] * B[j] * wgt * Jp[k, j]
+                J[r0:r0 + d, cols['h'][0] + k] += B[j] * F[k, j]
+            J[r0:r0 + d, yf_col(k):yf_col(k) + d] += np.eye(d)
+            J[r0:r0 + d, yf_col(k + 1):yf_col(k + 1) + d] -= np.eye(d)
+        return J, cols
+
+
+class CollocationProblem:
+    """``{f, c, df, dc}`` of a model built with ``approaches.Collocation()`` for a batch of N independent designs.
+
+    ``model(dv)`` receives a dict of leaf tensors (the user's design variables, trajectory axis last) and the
+    keyword ``collocation_design_values`` to pass to ``ODEProblem(...)``; it returns ``(ode_problem, objective,
+    constraints)`` with ``objective`` of shape (N,) and ``constraints`` a dict name -> tensor whose LAST axis is the
+    design axis.  This is the reference's ``build_recorder`` pattern (ascent_system/main_model.py:51-125) with
+    ``set_as_design_variable / set_as_objective / set_as_constraint`` replaced by the return value.
+
+    Scalers follow the reference: stage / state design variables and BOTH collocation constraints use
+    ``1 / mean|guess|`` (collections.py:204-209, collocation.py:56-57); user variables use the scaler given here."""
+
+    def __init__(self, model, design_variables: dict):
+        self.model = model
+        self.dv0 = {k: (v if isinstance(v, dict) else dict(value=v)) for k, v in design_variables.items()}
+        self.Y = self.y = None
+
+    def _leaves(self, values=None):
+        out = {}
+        for k, meta in self.dv0.items():
+            v = meta['value'] if values is None or k not in values else values[k]
+            out[k] = v.detach().clone().requires_grad_(True)
+        return out
+
+    def compute_optimization_derivatives(self, values=None, stage_dv=None, state_dv=None, dense_designs=()):
+        """-> dict(f (N,), c {name: tensor}, df {dv: tensor}, dc {'user': {cname: {dv: tensor}}, 'collocation':
+        CollocationBlocks}, scalers, x names).  User-constraint rows are differentiated one per-design row at a time
+        (designs are independent, so one backward pass yields that row for all N designs)."""
+        dv = self._leaves(values)
+        given = None
+        if stage_dv is not None:
+            given = (stage_dv.detach().clone().requires_grad_(True), state_dv.detach().clone().requires_grad_(True))
+        prob, f, cons = self.model(dv, collocation_design_values=given)
+        integ = prob.integrator
+        Y, y = integ.stage_dv, integ.state_dv
+        self.Y, self.y, self.integ = Y, y, integ
+        leaves = dict(dv, stage_dv=Y, state_dv=y)
+        names = list(leaves)
+        grads = torch.autograd.grad(f.sum(), [leaves[k] for k in names], retain_graph=True, allow_unused=True)
+        df = {k: (g if g is not None else torch.zeros_like(leaves[k])) for k, g in zip(names, grads)}
+        dc_user = {}
+        for cname, c in cons.items():
+            rows = c.reshape(-1, c.shape[-1])
+            per = {k: [] for k in names}
+            for r in range(rows.shape[0]):
+                g = torch.autograd.grad(rows[r].sum(), [leaves[k] for k in names], retain_graph=True, allow_unused=True)
+                for k, gi in zip(names, g):
+                    per[k].append(gi)
+            dc_user[cname] = {k: (torch.stack([gi if gi is not None else torch.zeros_like(leaves[k]) for gi in v])
+                                  if any(gi is not None for gi in v) else None) for k, v in per.items()}
+        blocks = CollocationBlocks(integ, Y, y)
+        sc = integ.scalers
+        cvals = dict(cons)
+        cvals['stage_c'], cvals['state_c'] = integ.c1, integ.c2
+        return dict(f=f.detach(), c={k: v.detach() for k, v in cvals.items()}, df=df,
+                    dc=dict(user=dc_user, collocation=blocks), scalers=sc, design_variables=names,
+                    problem=prob)

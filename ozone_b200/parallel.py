@@ -123,28 +123,59 @@ def exchange_halos(ext: torch.Tensor, slab: Slab, group=None):
 class GridShard:
     """One rank's part of a checkpointed diffusion-reaction solve (TimeMarchingCheckpoints, explicit method).
 
-    ``forward_segment`` / ``adjoint_segment`` run one checkpoint segment on the extended slab through
-    the ordinary C ABI in slab mode; between segments the caller exchanges halos (``halo_payloads`` /
-    ``set_halos``, or ``exchange_halos`` under torch.distributed)."""
+    Everything is allocated once: the checkpoints of the extended slab ``ckpts [nseg + 1][n_ext]``, the multiplier
+    ping-pong, per-segment gradient rows, one workspace, and one prebuilt C-ABI descriptor per (segment, direction),
+    so a solve only enqueues kernels -- the whole forward + reverse sweep can be captured in a CUDA graph when the
+    halo exchange is the peer-memory one (``channel``, peer.HaloChannel); with torch.distributed P2P (``group``, also
+    the gloo path on CPU tensors) the exchange is a batched isend / irecv per segment."""
 
     def __init__(self, method, nx, n, num_inner, rank, world, y0_global, h, u, rhs_cfg, dtype=torch.float64,
-                 device='cuda'):
+                 device='cuda', channel=None):
+        import ctypes as C
         if n % num_inner:
             raise ValueError(f'Number of timesteps ({n}) must be divisible by the segment length {num_inner}')
         s = method.num_stages
         self.method, self.nx, self.n, self.ni, self.nseg = method, nx, n, num_inner, n // num_inner
-        self.slab = make_slab(nx, rank, world, 2 * s * num_inner)
+        self.slab = sl = make_slab(nx, rank, world, 2 * s * num_inner)
         self.dtype, self.device = dtype, torch.device(device)
         self.h = h.to(self.device, dtype).contiguous()
         self.u = u.to(self.device, dtype).reshape(n + 1, 1).contiguous()
         self.rhs_cfg = tuple(rhs_cfg)
-        sl = self.slab
-        self.ext = y0_global[sl.ext_lo:sl.ext_hi].to(self.device, dtype).reshape(-1, 1).contiguous()
-        self.ckpts = [self.ext.clone()]
-        self.field = torch.zeros(1, 1, dtype=dtype, device=self.device)
-        self.h_bar = torch.zeros(n, dtype=dtype, device=self.device)
-        self.u_bar = torch.zeros(n + 1, 1, dtype=dtype, device=self.device)
-        self.lam = None
+        self.channel = channel
+        ne, ni, nseg = sl.n_ext, num_inner, self.nseg
+        new = lambda *shape: torch.zeros(shape, dtype=dtype, device=self.device)
+        self.ckpts = new(nseg + 1, ne, 1)
+        self.ckpts[0] = y0_global[sl.ext_lo:sl.ext_hi].to(self.device, dtype).reshape(-1, 1)
+        self.lam = [new(ne, 1), new(ne, 1)]
+        self.field_seg, self.field_bar = new(nseg, 1, 1), new(1, 1)
+        self.h_bar, self.u_seg = new(n), new(nseg, ni + 1, 1)
+        self._final_bar = None
+        # descriptors
+        self.pb_f, self.pb_a = [], []
+        ws_bytes = 8
+        for seg in range(nseg):
+            k0 = seg * ni
+            for adjoint in (False, True):
+                pb = engine.make_problem(self._spec(seg, adjoint))
+                pb.y0, pb.h, pb.p = self.ckpts[seg].data_ptr(), self.h[k0:].data_ptr(), self.u[k0:].data_ptr()
+                if adjoint:
+                    pb.ckpt = self.ckpts[seg].data_ptr()                 # rows seg, seg + 1: the segment's two checkpoints
+                    pb.final_bar, pb.y0_bar = None, None                 # set per call (ping-pong)
+                    pb.field_bar = self.field_bar.data_ptr()
+                    pb.h_bar, pb.p_bar = self.h_bar[k0:].data_ptr(), self.u_seg[seg].data_ptr()
+                    need = nat.lib.oz_tm_adjoint_workspace_bytes(C.byref(pb))
+                else:
+                    pb.yfinal, pb.field = self.ckpts[seg + 1].data_ptr(), self.field_seg[seg].data_ptr()
+                    need = nat.lib.oz_tm_forward_workspace_bytes(C.byref(pb))
+                if need == C.c_size_t(-1).value:
+                    raise nat.OzError(nat.lib.oz_last_error().decode())
+                ws_bytes = max(ws_bytes, need)
+                (self.pb_a if adjoint else self.pb_f).append(pb)
+        self.ws = torch.empty(ws_bytes, dtype=torch.uint8, device=self.device)
+        for pb in self.pb_f + self.pb_a:
+            pb.ws, pb.ws_bytes = self.ws.data_ptr(), ws_bytes
+        self.cur = 0
+        self.launches_per_solve = 0
 
     def _spec(self, seg, adjoint):
         sl = self.slab
@@ -159,86 +190,162 @@ class GridShard:
                                 d_override=sl.n_ext, rhs_cfg=self.rhs_cfg,
                                 grid_slab=(sl.ext_lo, self.nx, a, b, flags))
 
-    def forward_segment(self, seg):
-        k0 = seg * self.ni
-        out = engine.tm_forward(self._spec(seg, False), self.ext, self.h[k0:k0 + self.ni].contiguous(),
-                                self.u[k0:k0 + self.ni + 1].contiguous(), None, keep_history=False)
-        self.field += out['field']
-        self.ext = out['final']          # owned cells exact; the halo zones must be refreshed before the next segment
+    # ---- halo exchange of an extended-slab vector (after a segment: owned cells exact, halo zones stale)
+    def halo_views(self, ext):
+        """(left_src, right_src, left_halo, right_halo) views of `ext` (n_ext, 1): what the neighbours need / refresh."""
+        sl = self.slab
+        a, b = sl.local_own
+        v, hw = ext[:, 0], sl.halo
+        return (v[a:a + hw] if sl.rank > 0 else None, v[b - hw:b] if sl.rank < sl.world - 1 else None,
+                v[a - hw:a] if sl.rank > 0 else None, v[b:b + hw] if sl.rank < sl.world - 1 else None)
 
-    def end_forward_segment(self):
-        self.ckpts.append(self.ext.clone())
+    def exchange(self, ext, group=None, phase='both'):
+        sl = self.slab
+        if sl.world == 1:
+            return
+        if self.channel is not None:
+            ls, rs, lh, rh = self.halo_views(ext)
+            self.channel.exchange(ls, rs, lh, rh, torch.cuda.current_stream().cuda_stream, phase=phase)
+        elif phase in ('wait', 'both'):
+            exchange_halos(ext[:, 0], sl, group)
+
+    # ---- one segment each way (kernels only)
+    def forward_segment(self, seg):
+        import ctypes as C
+        pb = self.pb_f[seg]
+        pb.stream = torch.cuda.current_stream().cuda_stream
+        nat.check(nat.lib.oz_tm_forward(C.byref(pb)), 'oz_tm_forward')
 
     def start_adjoint(self, field_bar=1.0, final_bar_global=None):
         sl = self.slab
-        self.field_bar = torch.full((1, 1), float(field_bar), dtype=self.dtype, device=self.device)
-        self.lam = torch.zeros(sl.n_ext, 1, dtype=self.dtype, device=self.device)
+        self.field_bar.fill_(float(field_bar))
+        self.cur = 0
+        self.lam[0].zero_()
         if final_bar_global is not None:
-            self.lam += final_bar_global[sl.ext_lo:sl.ext_hi].to(self.device, self.dtype).reshape(-1, 1)
+            self.lam[0] += final_bar_global[sl.ext_lo:sl.ext_hi].to(self.device, self.dtype).reshape(-1, 1)
 
     def adjoint_segment(self, seg):
-        k0 = seg * self.ni
-        ck = torch.stack([self.ckpts[seg], self.ckpts[seg + 1]]).contiguous()
-        g = engine.tm_adjoint(self._spec(seg, True), self.ckpts[seg], self.h[k0:k0 + self.ni].contiguous(),
-                              self.u[k0:k0 + self.ni + 1].contiguous(), None, ckpt=ck, final_bar=self.lam,
-                              field_bar=self.field_bar, need=('y0', 'h', 'p'))
-        self.h_bar[k0:k0 + self.ni] = g['h']
-        self.u_bar[k0:k0 + self.ni + 1] += g['p']
-        self.lam = g['y0']               # owned cells exact; halo zones refreshed by the caller
+        import ctypes as C
+        pb = self.pb_a[seg]
+        pb.stream = torch.cuda.current_stream().cuda_stream
+        pb.final_bar, pb.y0_bar = self.lam[self.cur].data_ptr(), self.lam[self.cur ^ 1].data_ptr()
+        nat.check(nat.lib.oz_tm_adjoint(C.byref(pb)), 'oz_tm_adjoint')
+        self.cur ^= 1
+
+    @property
+    def lam_cur(self):
+        return self.lam[self.cur]
+
+    @property
+    def ext(self):                       # state of the extended slab after the last forward segment
+        return self.ckpts[self.nseg]
 
     def owned(self, ext):
         a, b = self.slab.local_own
         return ext[a:b, 0]
 
+    # ---- whole solve
+    def run(self, group=None, field_bar=1.0):
+        """Forward sweep, then reverse sweep; kernels (and peer-memory halo kernels) only when `channel` is set."""
+        for seg in range(self.nseg):
+            self.forward_segment(seg)
+            self.exchange(self.ckpts[seg + 1], group)
+        self.start_adjoint(field_bar)
+        for seg in reversed(range(self.nseg)):
+            self.adjoint_segment(seg)
+            self.exchange(self.lam_cur, group)
+        if self.channel is not None:
+            self.channel.advance(torch.cuda.current_stream().cuda_stream)
+
+    def results(self):
+        """Local (not yet all-reduced) field, h_bar, u_bar and the owned parts of the final state and of y0_bar."""
+        n, ni, nseg = self.n, self.ni, self.nseg
+        u_bar = torch.zeros(n + 1, 1, dtype=self.dtype, device=self.device)
+        u_bar[:n].view(nseg, ni, 1).add_(self.u_seg[:, :ni])
+        u_bar[ni::ni].add_(self.u_seg[:, ni])            # the last grid point of a segment is the first of the next
+        return dict(field=self.field_seg.sum(dim=0), h_bar=self.h_bar, u_bar=u_bar,
+                    final_owned=self.owned(self.ext), y0_bar_owned=self.owned(self.lam_cur))
+
+
+def make_channel(method, nx, num_inner, dtype, device, group=None):
+    """Peer-memory halo channel for the spatial shard (CUDA tensors, >1 rank, symmetric memory available), else None."""
+    from . import peer
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(group) == 1:
+        return None
+    if torch.device(device).type != 'cuda':
+        return None
+    halo = 2 * method.num_stages * num_inner
+    w = 8 if dtype == torch.float64 else 4
+    arena = peer.PeerArena(4096 + 4 * halo * w, device, group)
+    return peer.HaloChannel(arena, halo, dtype)
+
 
 def solve_grid_sharded(method, nx, n, num_inner, y0_global, h, u, rhs_cfg, field_bar=1.0, dtype=torch.float64,
-                       device=None, group=None):
+                       device=None, group=None, peer_halos=True):
     """Distributed driver (call from every rank): forward + reverse sweep of the diffusion-reaction grid
     cut into slabs.  Returns dict(field, y0_bar_owned, own_range, h_bar, u_bar, final_owned)."""
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     device = device or torch.device('cuda', torch.cuda.current_device())
-    sh = GridShard(method, nx, n, num_inner, rank, world, y0_global, h, u, rhs_cfg, dtype, device)
-    for seg in range(sh.nseg):
-        sh.forward_segment(seg)
-        exchange_halos(sh.ext[:, 0], sh.slab, group)
-        sh.end_forward_segment()
-    final_owned = sh.owned(sh.ext).clone()
-    sh.start_adjoint(field_bar)
-    for seg in reversed(range(sh.nseg)):
-        sh.adjoint_segment(seg)
-        exchange_halos(sh.lam[:, 0], sh.slab, group)
+    channel = make_channel(method, nx, num_inner, dtype, device, group) if peer_halos else None
+    sh = GridShard(method, nx, n, num_inner, rank, world, y0_global, h, u, rhs_cfg, dtype, device, channel=channel)
+    sh.run(group, field_bar)
+    res = sh.results()
+    if channel is not None:
+        torch.cuda.synchronize()
+        channel.check()
     if world > 1:
-        for t in (sh.field, sh.h_bar, sh.u_bar):
+        for t in (res['field'], res['h_bar'], res['u_bar']):
             dist.all_reduce(t, group=group)
-    return dict(field=sh.field, y0_bar_owned=sh.owned(sh.lam).clone(), own_range=(sh.slab.own_lo, sh.slab.own_hi),
-                h_bar=sh.h_bar, u_bar=sh.u_bar, final_owned=final_owned)
+    return dict(field=res['field'], y0_bar_owned=res['y0_bar_owned'].clone(), own_range=(sh.slab.own_lo, sh.slab.own_hi),
+                h_bar=res['h_bar'], u_bar=res['u_bar'], final_owned=res['final_owned'].clone(), shard=sh)
 
 
 def solve_grid_emulated(method, nx, n, num_inner, world, y0_global, h, u, rhs_cfg, field_bar=1.0,
-                        dtype=torch.float64, device='cuda'):
+                        dtype=torch.float64, device='cuda', peer_halos=True):
     """The same algorithm with all ``world`` ranks emulated in ONE process on one GPU (their kernels run
-    one after another; the halo exchange is a copy).  Used to test the slab logic without N GPUs."""
-    shards = [GridShard(method, nx, n, num_inner, r, world, y0_global, h, u, rhs_cfg, dtype, device) for r in range(world)]
+    one after another).  With peer_halos the exchange goes through the oz_peer_* kernels over a LocalArena --
+    every rank pushes, then every rank waits -- else it is a tensor copy.  Tests the slab logic without N GPUs."""
+    from . import peer
+    channels = [None] * world
+    if peer_halos and world > 1:
+        halo = 2 * method.num_stages * num_inner
+        arena = peer.LocalArena(4096 + 4 * halo * (8 if dtype == torch.float64 else 4), device, world)
+        offs = None
+        for r in range(world):
+            view = arena.view(r)
+            view._cursor = 0
+            channels[r] = peer.HaloChannel(view, halo, dtype)
+    shards = [GridShard(method, nx, n, num_inner, r, world, y0_global, h, u, rhs_cfg, dtype, device, channel=channels[r])
+              for r in range(world)]
 
     def swap(get):
+        if peer_halos and world > 1:
+            for ph in ('push', 'wait'):
+                for s in shards:
+                    s.exchange(get(s), phase=ph)
+            return
         pay = [halo_payloads(get(s)[:, 0], s.slab) for s in shards]
         pay = [(None if l is None else l.clone(), None if r is None else r.clone()) for l, r in pay]
         for r, s in enumerate(shards):
             set_halos(get(s)[:, 0], s.slab, pay[r - 1][1] if r > 0 else None, pay[r + 1][0] if r < world - 1 else None)
 
-    for seg in range(shards[0].nseg):
+    nseg = shards[0].nseg
+    for seg in range(nseg):
         for s in shards:
             s.forward_segment(seg)
-        swap(lambda s: s.ext)
-        for s in shards:
-            s.end_forward_segment()
-    final = torch.cat([s.owned(s.ext) for s in shards])
+        swap(lambda s: s.ckpts[seg + 1])
     for s in shards:
         s.start_adjoint(field_bar)
-    for seg in reversed(range(shards[0].nseg)):
+    for seg in reversed(range(nseg)):
         for s in shards:
             s.adjoint_segment(seg)
-        swap(lambda s: s.lam)
-    return dict(field=sum(s.field for s in shards), y0_bar=torch.cat([s.owned(s.lam) for s in shards]),
-                h_bar=sum(s.h_bar for s in shards), u_bar=sum(s.u_bar for s in shards), final=final)
+        swap(lambda s: s.lam_cur)
+    res = [s.results() for s in shards]
+    if peer_halos and world > 1:
+        torch.cuda.synchronize()
+        for c in channels:
+            c.check()
+    return dict(field=sum(r['field'] for r in res), y0_bar=torch.cat([r['y0_bar_owned'] for r in res]),
+                h_bar=sum(r['h_bar'] for r in res), u_bar=sum(r['u_bar'] for r in res),
+                final=torch.cat([r['final_owned'] for r in res]))

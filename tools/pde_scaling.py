@@ -7,11 +7,13 @@ from ozone_b200 import engine
 from ozone_b200.glms import get_integration_method
 m = get_integration_method('RK4')
 n = 256
+sizes = [int(a) for a in sys.argv[1].split(',')] if len(sys.argv) > 1 else (125_000, 250_000, 500_000, 1_000_000, 2_000_000, 4_000_000, 8_000_000)
+print('fuse', os.environ.get('OZ_PDE_FUSE_F'), os.environ.get('OZ_PDE_FUSE_A'))
 for dtype in (torch.float64, torch.float32):
-    for nx in (125_000, 250_000, 500_000, 1_000_000, 2_000_000, 4_000_000, 8_000_000):
+    for nx in sizes:
         cfg = (np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx)))
         spec = engine.SolveSpec(rhs_name='diffusion_reaction', method=m, N=1, n=n, dtype=dtype, h_shared=True, p_shared=True,
-                                th_shared=True, num_inner=16, store_history=False, d_override=nx, rhs_cfg=cfg)
+                                th_shared=True, num_inner=32, store_history=False, d_override=nx, rhs_cfg=cfg)
         plan = engine.TmPlan(spec, grads=('y0', 'h', 'p'), cotangents=('field',))
         plan.y0.fill_(0.5); plan.h.fill_(0.4 * (np.pi / nx) ** 2); plan.p.fill_(-0.3); plan.field_bar.fill_(1.0)
         for _ in range(2):
