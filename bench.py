@@ -388,8 +388,9 @@ class Runner:
         self.launches = plan.launches_forward + plan.launches_adjoint
         self.pipe = None
         if self.kind == 'tm' and e2e:      # e2e leg: host-resident batch in sub-batches on their own streams (copy / compute overlap)
+            fr = [float(x) for x in args.e2e_fractions.split(',')] if args.e2e_fractions else None
             self.pipe = engine.PipelinedTmSolve(spec, slices=args.e2e_slices, device=dev, grads=want, cotangents=cot,
-                                                upload=self.e2e_inputs)
+                                                upload=self.e2e_inputs, fractions=fr)
             self.pipe.set_host_inputs(**self.host)
             if args.world > 1:
                 import torch.distributed as dist
@@ -507,9 +508,12 @@ FP64_BOUND_NOTE = {
     'tm_implicit': ('implicit Gauss-Legendre + Newton is FP64-ALU bound, not HBM bound (about 1 kflop per 100 compulsory bytes; '
                     'ncu: fp64 pipe ~53 % busy vs DRAM ~12 %): frac is executed FP64 flops over the measured FMA peak, the HBM '
                     'fractions the metric asks for are under roofline.hbm'),
-    'grid': ('one exponential per cell and stage: the fused steps are FP64-bound (ncu: fp64 pipe ~55 %, state L2-resident); HBM '
+    'grid': ('one exponential per cell and stage: the fused steps are FP64-bound (ncu: fp64 pipe 50-60 %, state L2-resident); HBM '
              'fractions under roofline.hbm'),
+    'other': ('this kernel is closer to the FP64 roof than to the HBM one (ncu, profiles/r2c_ncu_summary.txt: explicit reverse sweep '
+              'fp64 pipe 78 % busy vs DRAM 26 %; Picard sweeps never leave the chip); HBM fractions under roofline.hbm'),
 }
+FP64_PEAK_FALLBACK_TFLOPS = 36.3      # oz_fma_probe on this pool's B200 (used only when the live probe is skipped)
 
 
 def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
@@ -531,14 +535,35 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
              'coljac': ('rhs_jac_kernel', 'colloc_residual_kernel')}[run.kind]
     traffic = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(workload, {})
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(workload.replace('_sharded', ''), {})
     except Exception:
         pass
+
+    # profiles/traffic.json holds ncu counts PER CAPTURED LAUNCH; one timed forward / reverse call of the bench is many
+    # launches for the grid (fused steps) and a larger batch for Picard (captured at 131,072 trajectories)
+    def per_call(table, name):
+        key = name.split(' ')[0]
+        v = table.get(key)
+        if v is None:
+            return None
+        if run.kind == 'grid':
+            nx = run.shard.slab.n_ext if hasattr(run, 'shard') else run.d
+            K, KR = run.engine.grid_fusion(nx)
+            n, ni = run.n, run.n // run.wl['nc']
+            nseg = n // ni
+            up = lambda a, b: -(-a // b)
+            if key == 'pde_step_kernel':
+                return v * nseg * up(ni, K)
+            step = table.get('pde_step_kernel') or 0
+            return v * nseg * up(ni, KR) + step * nseg * up(ni - 1, K)       # reverse launches + the replayed forward ones
+        if run.kind == 'picard' and key == 'picard_kernel':
+            return v * run.wl['N'] / 131072.0
+        return v
 
     def hbm_entry(name, nbytes, secs):
         ach = nbytes / secs / 1e9
         return {'kernel': name, 'achieved': ach, 'peak': peak, 'unit': 'GB/s', 'frac': ach / peak,
-                'frac_of_nominal_8000': ach / 8000.0, 'traffic': traffic.get(name.split(' ')[0]),
+                'frac_of_nominal_8000': ach / 8000.0, 'traffic': per_call(traffic, name),
                 'algorithmic_bytes_per_launch': nbytes, 'avg_launch_ms': secs * 1e3}
 
     adj_e, fwd_e = hbm_entry(names[0], adj_b, adj_s), hbm_entry(names[1], fwd_b, fwd_s)
@@ -550,12 +575,14 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
         except Exception as exc:                                            # never let the probe break the bench line
             fma = {'error': str(exc)}
     implicit = run.kind == 'tm' and not run.spec.method.explicit
-    fp64_bound = run.w == 8 and (implicit or run.kind == 'grid')
     flops = traffic.get('fp64_flops_per_launch', {})
-    f64_peak = fma.get('f64') or traffic.get('fp64_peak_tflops_at_capture')
+    f64_peak = fma.get('f64') or FP64_PEAK_FALLBACK_TFLOPS
     roof = None
-    if fp64_bound and f64_peak:
-        fl = flops.get(dominant['kernel'].split(' ')[0])
+    # the dominant kernel is reported against the roof it is closer to: executed FP64 flops over the FMA peak, or
+    # algorithmic bytes over the copy bandwidth
+    fl = per_call(flops, dominant['kernel']) if run.w == 8 else None
+    fp64_bound = bool(fl) and (fl / (dominant['avg_launch_ms'] * 1e-3) / 1e12 / f64_peak) > dominant['frac']
+    if fp64_bound:
         if fl:
             t = fl / (dominant['avg_launch_ms'] * 1e-3) / 1e12
             roof = {'bound': 'fp64', 'kernel': dominant['kernel'], 'achieved': t, 'peak': f64_peak, 'unit': 'TFLOP/s',
@@ -563,8 +590,8 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
                     'avg_launch_ms': dominant['avg_launch_ms'], 'flops_source': flops.get('source'),
                     'peak_source': 'oz_fma_probe (register-resident DFMA loop) timed in this run' if fma.get('f64')
                     else 'oz_fma_probe at capture time (profiles/traffic.json)',
-                    'note': FP64_BOUND_NOTE['tm_implicit' if implicit else 'grid']}
-            fo = flops.get(other['kernel'].split(' ')[0])
+                    'note': FP64_BOUND_NOTE['tm_implicit' if implicit else ('grid' if run.kind == 'grid' else 'other')]}
+            fo = per_call(flops, other['kernel'])
             if fo:
                 to = fo / (other['avg_launch_ms'] * 1e-3) / 1e12
                 roof['other_kernel'] = {'kernel': other['kernel'], 'achieved': to, 'peak': f64_peak, 'unit': 'TFLOP/s',
@@ -573,8 +600,7 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
         roof = dict({'bound': 'hbm'}, **dominant)
         roof.update({'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks else 'fallback 6650 GB/s',
                      'other_kernel': other,
-                     'note': ('FP64-bound family, but no flop count of this build is on file: HBM fraction only' if fp64_bound else
-                              'HBM / FP64 co-limited explicit path (DESIGN.md section 5)')})
+                     'note': 'HBM-bound by this measure (algorithmic bytes over the measured copy bandwidth exceed the FP64 fraction)'})
     roof['hbm'] = {'forward': fwd_e, 'reverse': adj_e, 'peak_source': 'MEASURED_PEAKS.json hbm_gbs (burst copy)' if peaks
                    else 'fallback 6650 GB/s'}
     roof['traffic_source'] = traffic.get('source')
@@ -599,7 +625,8 @@ def main():
     ap.add_argument('--other-steps', type=int, default=5)
     ap.add_argument('--trajectories', type=int, default=None, help='override the batch size per GPU (experiments only: the bench line names it)')
     ap.add_argument('--newton-tol', type=float, default=1e-7)
-    ap.add_argument('--e2e-slices', type=int, default=6, help='sub-batches (streams) of the end-to-end leg')
+    ap.add_argument('--e2e-slices', type=int, default=4, help='sub-batches (streams) of the end-to-end leg')
+    ap.add_argument('--e2e-fractions', default='', help='relative sub-batch sizes of the end-to-end leg, e.g. 4,3,2,1 (overrides --e2e-slices)')
     ap.add_argument('--no-e2e-graph', action='store_true', help='enqueue the end-to-end pipeline eagerly (no CUDA graph)')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
@@ -815,7 +842,7 @@ def main():
             'shared_gradient_allreduce': shared_mode[0],
             'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
                     'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps,
-                    'how': (f'engine.PipelinedTmSolve: {args.e2e_slices} sub-batches on their own streams, pinned host buffers, '
+                    'how': (f'engine.PipelinedTmSolve: {len(run.pipe.plans) if run.pipe is not None else 1} sub-batches (sizes {[b - a for a, b in run.pipe.bounds] if run.pipe is not None else []}) on their own streams, pinned host buffers, '
                             + ('slice pipeline replayed as one CUDA graph' if getattr(run, 'e2e_graph', False) else
                                'eager enqueue' + (f' (graph capture failed: {run.e2e_graph_error})' if hasattr(run, 'e2e_graph_error') else ''))
                             if run.pipe is not None else 'engine plan API, pinned host buffers, one stream')},

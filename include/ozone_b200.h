@@ -208,7 +208,7 @@ OZ_API int oz_register_rhs_plugin(const char* so_path);
  * stores into the peer's arena + a release store of an epoch number, acquire polling on the receiver's own memory.
  * Epochs are *epoch_base + epoch so a captured CUDA graph can be replayed (oz_peer_epoch_advance moves the base).  A wait
  * that sees no signal for ~2 s sets *err to 1 and returns without copying.  NULL pointers = no neighbour on that side.
- *   oz_peer_halo_push / oz_peer_halo_wait: neighbour exchange of the spatial shard (ozone_b200/parallel.py), `count`
+ *   oz_peer_halo_push / oz_peer_halo_wait (/ oz_peer_halo_exchange = both in one launch): neighbour exchange of the spatial shard (ozone_b200/parallel.py), `count`
  *       values per side; push writes into the neighbours' slots, wait copies this rank's slots into its halo zones.
  *   oz_peer_sum: all-reduce (sum, fixed rank order) of `rows` values: slots[r] -> rank r's [2][world][rows] slot array,
  *       flags[r] -> rank r's [world] flags (both device arrays of `world` pointers). */
@@ -218,6 +218,12 @@ OZ_API int oz_peer_halo_push(int dtype, const void* left_src, const void* right_
 OZ_API int oz_peer_halo_wait(int dtype, const void* from_left_slot, const void* from_right_slot, int64_t count,
                              void* left_halo, void* right_halo, const uint64_t* flag_left, const uint64_t* flag_right,
                              const uint64_t* epoch_base, uint64_t epoch, int32_t* err, void* stream);
+/* push + wait in one launch: only when every rank's kernel can be resident at once (one process per GPU) */
+OZ_API int oz_peer_halo_exchange(int dtype, const void* left_src, const void* right_src, int64_t count, void* left_dst,
+                                 void* right_dst, uint64_t* left_flag, uint64_t* right_flag, const void* from_left_slot,
+                                 const void* from_right_slot, void* left_halo, void* right_halo, const uint64_t* flag_left,
+                                 const uint64_t* flag_right, const uint64_t* epoch_base, uint64_t epoch, int32_t* err,
+                                 void* stream);
 OZ_API int oz_peer_epoch_advance(uint64_t* epoch_base, uint64_t by, void* stream);
 OZ_API int oz_peer_sum(int dtype, const void* local, int32_t rows, int32_t rank, int32_t world, void* const* slots,
                        uint64_t* const* flags, const uint64_t* epoch_base, uint64_t epoch, void* out, int32_t* err,

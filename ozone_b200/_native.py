@@ -71,6 +71,7 @@ SYMBOLS = {
                                     C.c_void_p, C.c_uint64, C.c_void_p]),
     'oz_peer_halo_wait': (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p,
                                     C.c_void_p, C.c_uint64, C.c_void_p, C.c_void_p]),
+    'oz_peer_halo_exchange': (C.c_int, [C.c_int, C.c_void_p, C.c_void_p, C.c_int64] + [C.c_void_p] * 11 + [C.c_uint64, C.c_void_p, C.c_void_p]),
     'oz_peer_epoch_advance': (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
     'oz_peer_sum': (C.c_int, [C.c_int, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_void_p, C.c_void_p,
                               C.c_uint64, C.c_void_p, C.c_void_p, C.c_void_p]),

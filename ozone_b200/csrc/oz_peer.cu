@@ -83,6 +83,41 @@ __global__ void __launch_bounds__(256) halo_wait_kernel(const T* from_left_slot,
     }
 }
 
+// Push and wait in one launch (real ranks only: every rank's kernel is resident at the same time; ranks emulated on
+// one stream must push first and wait afterwards, or the first one would wait for a kernel queued behind it).
+template <typename T>
+__global__ void __launch_bounds__(256) halo_exchange_kernel(const T* __restrict__ left_src, const T* __restrict__ right_src,
+                                                            long long count, T* left_dst, T* right_dst,
+                                                            unsigned long long* left_flag, unsigned long long* right_flag,
+                                                            const T* from_left_slot, const T* from_right_slot,
+                                                            T* __restrict__ left_halo, T* __restrict__ right_halo,
+                                                            const unsigned long long* flag_left, const unsigned long long* flag_right,
+                                                            const unsigned long long* epoch_base, unsigned long long epoch, int* err) {
+    __shared__ int ok;
+    for (long long j = threadIdx.x; j < count; j += blockDim.x) {
+        if (left_dst) left_dst[j] = left_src[j];
+        if (right_dst) right_dst[j] = right_src[j];
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned long long e = *epoch_base + epoch;
+        if (left_flag) st_release_sys(left_flag, e);
+        if (right_flag) st_release_sys(right_flag, e);
+        bool good = true;
+        if (flag_left) good = peer_wait(flag_left, e) && good;
+        if (flag_right) good = peer_wait(flag_right, e) && good;
+        if (!good && err) atomicExch(err, 1);
+        ok = good ? 1 : 0;
+    }
+    __syncthreads();
+    if (!ok) return;
+    for (long long j = threadIdx.x; j < count; j += blockDim.x) {
+        if (from_left_slot) left_halo[j] = __ldcg(from_left_slot + j);
+        if (from_right_slot) right_halo[j] = __ldcg(from_right_slot + j);
+    }
+}
+
 __global__ void epoch_advance_kernel(unsigned long long* epoch_base, unsigned long long by) { *epoch_base += by; }
 
 // All-reduce (sum) of `rows` values over `world` ranks in a fixed order (rank 0 first): bit-identical on every rank.
@@ -162,6 +197,34 @@ OZ_API int oz_peer_halo_wait(int dtype, const void* from_left_slot, const void* 
     else
         halo_wait_kernel<float><<<1, 256, 0, st>>>((const float*)from_left_slot, (const float*)from_right_slot, count,
                                                   (float*)left_halo, (float*)right_halo, fl, fr, eb, epoch, err);
+    OZ_CUDA_CHECK(cudaGetLastError());
+    return 0;
+}
+
+OZ_API int oz_peer_halo_exchange(int dtype, const void* left_src, const void* right_src, int64_t count, void* left_dst,
+                                 void* right_dst, uint64_t* left_flag, uint64_t* right_flag, const void* from_left_slot,
+                                 const void* from_right_slot, void* left_halo, void* right_halo, const uint64_t* flag_left,
+                                 const uint64_t* flag_right, const uint64_t* epoch_base, uint64_t epoch, int32_t* err,
+                                 void* stream) {
+    OZ_REQUIRE(dtype == OZ_F64 || dtype == OZ_F32, "unknown dtype %d", dtype);
+    OZ_REQUIRE(count >= 0 && epoch_base, "halo exchange: bad arguments");
+    OZ_REQUIRE((!left_dst || (left_src && left_flag && from_left_slot && left_halo && flag_left)) &&
+                   (!right_dst || (right_src && right_flag && from_right_slot && right_halo && flag_right)),
+               "halo exchange: a neighbour needs source, slot, halo and both flags");
+    cudaStream_t st = (cudaStream_t)stream;
+    auto lf = (unsigned long long*)left_flag, rf = (unsigned long long*)right_flag;
+    auto fl = (const unsigned long long*)flag_left, fr = (const unsigned long long*)flag_right;
+    auto eb = (const unsigned long long*)epoch_base;
+    if (dtype == OZ_F64)
+        halo_exchange_kernel<double><<<1, 256, 0, st>>>((const double*)left_src, (const double*)right_src, count, (double*)left_dst,
+                                                       (double*)right_dst, lf, rf, (const double*)from_left_slot,
+                                                       (const double*)from_right_slot, (double*)left_halo, (double*)right_halo, fl, fr,
+                                                       eb, epoch, err);
+    else
+        halo_exchange_kernel<float><<<1, 256, 0, st>>>((const float*)left_src, (const float*)right_src, count, (float*)left_dst,
+                                                      (float*)right_dst, lf, rf, (const float*)from_left_slot,
+                                                      (const float*)from_right_slot, (float*)left_halo, (float*)right_halo, fl, fr, eb,
+                                                      epoch, err);
     OZ_CUDA_CHECK(cudaGetLastError());
     return 0;
 }

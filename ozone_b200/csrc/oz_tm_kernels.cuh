@@ -34,6 +34,10 @@ constexpr bool use_reg_solve() {
 #ifndef OZ_SPARSE_SOLVE   /* 1: structure-aware elimination (oz_sparse_solve.cuh); 0: dense register elimination (A/B baseline) */
 #define OZ_SPARSE_SOLVE 1
 #endif
+#ifndef OZ_FWD_SOLVE_EARLY_EXIT   /* forward sweep, by system size M: measured per size on Van der Pol (GL2 M = 2: branch-free 0.072 ->
+                                      0.062 ms; GL4 M = 4: branch-free 0.112 -> 0.129 ms; GL6 M = 6: branch-free 0.220 -> 0.195 ms) */
+#define OZ_FWD_SOLVE_EARLY_EXIT(M) ((M) == 4)
+#endif
 #ifndef OZ_ADJ_SOLVE_EARLY_EXIT   /* reverse sweep: pivot tests leave the elimination early (fewer live registers, see oz_sparse_solve.cuh) */
 #define OZ_ADJ_SOLVE_EARLY_EXIT true
 #endif
@@ -57,6 +61,12 @@ constexpr bool use_reg_solve() {
 #endif
 #ifndef OZ_MB_EXPL_ADJ_F32
 #define OZ_MB_EXPL_ADJ_F32 6
+#endif
+#ifndef OZ_MB_EXPL_ADJ_LEAN_F64   /* specialised explicit reverse sweep (tm_adjoint_kernel SPEC != 0) */
+#define OZ_MB_EXPL_ADJ_LEAN_F64 5
+#endif
+#ifndef OZ_MB_EXPL_ADJ_LEAN_F32
+#define OZ_MB_EXPL_ADJ_LEAN_F32 6
 #endif
 template <class R, int S, typename T, bool IMPL>
 constexpr int lb_threads() {
@@ -241,7 +251,7 @@ OZ_D void solve_stages(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
                 constexpr int i = decltype(kc)::value / DA, r = decltype(kc)::value % DA;
                 b[uidx<R, S>(i, r)] = -Rs[i][r];
             });
-            bad = sparse_solve<R, S, false, T>(Ma, b);
+            bad = sparse_solve<R, S, false, T, OZ_FWD_SOLVE_EARLY_EXIT(MA)>(Ma, b);
 #else
             assemble([&](int r, int c, T v) { Ma[r][c] = v; });
 #pragma unroll
@@ -731,8 +741,16 @@ OZ_D void adjoint_step(const TmArgs<T>& a, const T* y, T h, const T (*ps)[Dims<R
 template <class R, typename T, int S, bool IMPL, int SPEC>
 OZ_D void tm_adjoint_body(const TmArgs<T>& a, const AdjWsPtr<T>& ws);
 
+// resident blocks the reverse kernel is compiled for: the specialised explicit sweeps carry far less state than the
+// generic one (80-94 registers instead of 128 in fp64), so more of them fit
+template <class R, typename T, int S, bool IMPL, int SPEC>
+constexpr int lb_blocks_adj() {
+    if (!IMPL && SPEC != 0) return sizeof(T) == 8 ? OZ_MB_EXPL_ADJ_LEAN_F64 : OZ_MB_EXPL_ADJ_LEAN_F32;
+    return lb_blocks<R, S, T, IMPL, true>();
+}
+
 template <class R, typename T, int S, bool IMPL, int SPEC = 0>
-__global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks<R, S, T, IMPL, true>()))
+__global__ void __launch_bounds__((lb_threads<R, S, T, IMPL>()), (lb_blocks_adj<R, T, S, IMPL, SPEC>()))
     tm_adjoint_kernel(const TmArgs<T> a_in, const AdjWsPtr<T> ws) {
     if constexpr (SPEC == 0) {
         tm_adjoint_body<R, T, S, IMPL, 0>(a_in, ws);      // straight from the parameter block (constant bank)

@@ -608,12 +608,23 @@ class PipelinedTmSolve:
     added up over the slices at the end (fixed order)."""
 
     def __init__(self, spec: SolveSpec, slices=4, device='cuda', grads=('h', 'p'), cotangents=('final',),
-                 upload=('h', 'p')):
+                 upload=('h', 'p'), fractions=None):
+        """`fractions`: relative sizes of the sub-batches (default: equal).  Decreasing sizes shorten the tail of the
+        pipeline -- the last slice's kernels and download cannot overlap anything -- while the big early slices keep
+        the kernels efficient; all uploads still queue back to back on the copy engine."""
         from .parallel import shard_bounds
         self.spec, self.upload = spec, tuple(upload)
         dev = torch.device(device)
-        slices = max(1, min(slices, spec.N))
-        self.bounds = [shard_bounds(spec.N, i, slices) for i in range(slices)]
+        if fractions:
+            tot, acc, cuts = float(sum(fractions)), 0.0, [0]
+            for f in fractions[:-1]:
+                acc += f
+                cuts.append(min(spec.N, max(cuts[-1] + 1, int(round(spec.N * acc / tot / 64.0)) * 64)))
+            cuts.append(spec.N)
+            self.bounds = [(a, b) for a, b in zip(cuts[:-1], cuts[1:]) if b > a]
+        else:
+            slices = max(1, min(slices, spec.N))
+            self.bounds = [shard_bounds(spec.N, i, slices) for i in range(slices)]
         self.plans = [TmPlan(replace(spec, N=hi - lo), device=dev, grads=grads, cotangents=cotangents)
                       for lo, hi in self.bounds]
         self.streams = [torch.cuda.Stream(device=dev) for _ in self.plans]

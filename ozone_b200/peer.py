@@ -97,6 +97,7 @@ class HaloChannel:
         self.off_slots = arena.region(4 * self.count * self.w)
         self.rank, self.world = arena.rank, arena.world
         self.epoch = 0                           # epochs issued since the last advance (relative to *epoch_base)
+        self.fused = isinstance(arena, PeerArena)   # one launch per exchange when every rank is its own process / GPU
         self.err = arena.local(self.off_ctl + 24, 1, torch.int32)
 
     def _slot(self, rank, parity, side):
@@ -114,6 +115,17 @@ class HaloChannel:
         par = e & 1
         base = self.arena.addr(r, self.off_ctl + 16)
         has_l, has_r = r > 0, r < last
+        if phase == 'both' and self.fused:
+            nat.check(nat.lib.oz_peer_halo_exchange(
+                self.code, left_src.data_ptr() if has_l else None, right_src.data_ptr() if has_r else None, self.count,
+                self._slot(r - 1, par, 1) if has_l else None, self._slot(r + 1, par, 0) if has_r else None,
+                self._flag(r - 1, 1) if has_l else None, self._flag(r + 1, 0) if has_r else None,
+                self._slot(r, par, 0) if has_l else None, self._slot(r, par, 1) if has_r else None,
+                left_halo.data_ptr() if has_l else None, right_halo.data_ptr() if has_r else None,
+                self._flag(r, 0) if has_l else None, self._flag(r, 1) if has_r else None,
+                base, e, self.err.data_ptr(), stream), 'oz_peer_halo_exchange')
+            self.epoch = e
+            return
         if phase in ('push', 'both'):
             nat.check(nat.lib.oz_peer_halo_push(
                 self.code, left_src.data_ptr() if has_l else None, right_src.data_ptr() if has_r else None, self.count,

@@ -10,8 +10,9 @@ inside a CUDA kernel, so each named problem of the reference is restated as a de
 States / dynamic parameters are matched BY NAME with what was added to the problem, exactly as the
 reference callback would index ``ozone_vars.states[name]`` (a missing name is a KeyError).  Extra
 positional / keyword arguments are the callback's static ("closure-captured") parameters; they
-are differentiable inputs.  Arbitrary Python callbacks are validated (same error behaviour as
-``ozone/func_wrapper.py``) but cannot be executed -- tracing them to device code is a planned row.
+are differentiable inputs.  Any other (node-wise) Python callback goes through ``ozone_b200/trace.py``: it is run once
+on symbolic inputs, differentiated, emitted as a device functor of the same contract and compiled into a plugin
+(same error behaviour as ``ozone/func_wrapper.py`` for malformed callbacks); the handles here skip that step.
 """
 from __future__ import annotations
 

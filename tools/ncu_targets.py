@@ -1,7 +1,7 @@
 #!/usr/bin/env python
 """Launch each kernel family a few times at its bench size so that `ncu --set full` sees a short launch list.
 
-    python tools/ncu_targets.py vdp|lv|lv32|pde|colloc|picard
+    python tools/ncu_targets.py vdp|lv|lv32|pde|pde32|colloc|coljac|picard
 
 (The bench itself issues thousands of launches for the grid workload; profiling it directly is slow.)
 """
@@ -18,16 +18,18 @@ from ozone_b200 import engine
 which = sys.argv[1]
 name = {'vdp': 'van_der_pol_gl6_tm_adjoint_N65536_nt40', 'lv': 'lotka_volterra_rk4_tm_adjoint_N1M_nt101',
         'lv32': 'lotka_volterra_rk4_tm_adjoint_N1M_nt101_fp32', 'pde': 'diffusion_reaction_rk4_checkpoints_nx1M_n1024',
-        'colloc': 'lunar_ascent_rk4_collocation_N16384_nt101', 'picard': 'lotka_volterra_rk4_picard_adjoint_N1M_nt101'}[which]
+        'pde32': 'diffusion_reaction_rk4_checkpoints_nx1M_n1024_fp32',
+        'colloc': 'lunar_ascent_rk4_collocation_N16384_nt101', 'coljac': 'lunar_ascent_rk4_optimizer_eval_N16384_nt101',
+        'picard': 'lotka_volterra_rk4_picard_adjoint_N1M_nt101'}[which]
 wl = dict(bench.WORKLOADS[name])
-if which == 'pde':
+if which in ('pde', 'pde32'):
     wl.update(nt=17, nc=4)            # 16 steps, 4 segments: same kernels, short launch list
 if which == 'picard':
     wl.update(N=1 << 17)              # 131,072 trajectories: 16k CTAs, same kernel
 
 
 class A:
-    newton_tol, e2e_slices, world, no_e2e_graph = 1e-7, 2, 1, True
+    newton_tol, e2e_slices, world, no_e2e_graph, e2e_fractions = 1e-7, 2, 1, True, ''
 
 
 run = bench.Runner(wl, name, 0, torch.device('cuda', 0), A)
