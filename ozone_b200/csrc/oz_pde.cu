@@ -169,10 +169,10 @@ OZ_D double pde_exp(double t, const double* tab) {
     p = fma(p, r, 1.0);
     p = fma(p, r, 1.0);
     const double v = tab[n & (kExpTab - 1)] * p;                  // in [1, 2.1): a NaN argument arrives here as NaN
-    const int k = n >> 5;
-    if (k > -1000 && k < 1000)                                     // exponent add; the result stays a normal number
-        return __hiloint2double(__double2hiint(v) + (k << 20), __double2loint(v));
-    const int kc = max(min(k, 2200), -2200), k1 = kc / 2;         // far out of range: overflow / underflow properly
+    // 2^k as two factors, branch-free: overflow, underflow and NaN come out right, and the four exponentials a thread
+    // evaluates per stage stay in one basic block (a fast path with an exponent add behind a range test cost a
+    // BSSY / BRA / BSYNC triple per call and kept the scheduler from interleaving them)
+    const int kc = max(min(n >> 5, 2046), -2044), k1 = kc >> 1;   // both factors stay normal numbers; beyond: inf / 0
     return v * __hiloint2double((k1 + 1023) << 20, 0) * __hiloint2double((kc - k1 + 1023) << 20, 0);
 }
 

@@ -23,6 +23,12 @@
 
 namespace oz {
 
+#ifndef OZ_SOLVE_CLOSED_TAIL   /* 1: a dense trailing block of at most 3 x 3 is solved in closed form (branch-free solves only).  Measured on
+                                  Van der Pol GL6: 0.195 -> 0.200 ms (one reciprocal instead of three, but 33 products instead of
+                                  ~20 on a pipe that is already 59 % busy): off. */
+#define OZ_SOLVE_CLOSED_TAIL 0
+#endif
+
 template <int I>
 struct IC {
     static constexpr int value = I;
@@ -116,6 +122,57 @@ constexpr int newton_live_entries() {
     return cnt;
 }
 
+// First column K from which the remaining (M - K) x (M - K) block is dense and at most 3 x 3: that tail is solved in closed
+// form (adjugate) instead of by elimination -- one reciprocal instead of three dependent ones, cofactors and right-hand
+// side products in parallel.  M when there is no such tail.  (Van der Pol / Gauss-Legendre 6: K = 3, the Schur complement.)
+template <class R, int S, bool TR>
+constexpr int tail_start() {
+    constexpr int M = S * (R::D - R::DQ);
+    for (int K = 0; K < M; ++K) {
+        if (M - K > 3 || M - K < 2) continue;
+        const Pat<M> p = eliminated<M>(newton_pattern<R, S, TR>(), K);
+        bool dense = true;
+        for (int r = K; r < M; ++r)
+            for (int c = K; c < M; ++c) dense = dense && p.v[r][c] == 2;
+        if (dense) return K;
+    }
+    return M;
+}
+
+// x = A^-1 b for the dense tail rows / columns K .. M-1 (2 x 2 or 3 x 3), b overwritten.  `bad` is raised when |det| is
+// tiny against the product of the row 1-norms (an upper bound of |det|): the caller then solves with row exchanges.
+template <typename T, int M, int K>
+OZ_D void solve_tail_closed(T (&a)[M][M], T (&b)[M], bool& ok, bool& bad) {
+    if constexpr (M - K == 2) {
+        const T a00 = a[K][K], a01 = a[K][K + 1], a10 = a[K + 1][K], a11 = a[K + 1][K + 1];
+        const T det = a00 * a11 - a01 * a10;
+        const T scale = (fabs(a00) + fabs(a01)) * (fabs(a10) + fabs(a11));
+        bad = bad | !(fabs(det) > T(1e-8) * scale);
+        ok = ok & (fabs(det) > T(0)) & (fabs(det) < CUDART_INF);
+        const T inv = fast_rcp(det);
+        const T x0 = a11 * b[K] - a01 * b[K + 1], x1 = a00 * b[K + 1] - a10 * b[K];
+        b[K] = x0 * inv;
+        b[K + 1] = x1 * inv;
+    } else {
+        const T a00 = a[K][K], a01 = a[K][K + 1], a02 = a[K][K + 2];
+        const T a10 = a[K + 1][K], a11 = a[K + 1][K + 1], a12 = a[K + 1][K + 2];
+        const T a20 = a[K + 2][K], a21 = a[K + 2][K + 1], a22 = a[K + 2][K + 2];
+        // adjugate, row by row of the inverse: inv(A)[i][j] = cof[j][i] / det
+        const T c00 = a11 * a22 - a12 * a21, c01 = a12 * a20 - a10 * a22, c02 = a10 * a21 - a11 * a20;
+        const T c10 = a02 * a21 - a01 * a22, c11 = a00 * a22 - a02 * a20, c12 = a01 * a20 - a00 * a21;
+        const T c20 = a01 * a12 - a02 * a11, c21 = a02 * a10 - a00 * a12, c22 = a00 * a11 - a01 * a10;
+        const T det = a00 * c00 + a01 * c01 + a02 * c02;
+        const T scale = (fabs(a00) + fabs(a01) + fabs(a02)) * (fabs(a10) + fabs(a11) + fabs(a12)) * (fabs(a20) + fabs(a21) + fabs(a22));
+        bad = bad | !(fabs(det) > T(1e-8) * scale);
+        ok = ok & (fabs(det) > T(0)) & (fabs(det) < CUDART_INF);
+        const T inv = fast_rcp(det);
+        const T b0 = b[K], b1 = b[K + 1], b2 = b[K + 2];
+        b[K] = (c00 * b0 + c10 * b1 + c20 * b2) * inv;
+        b[K + 1] = (c01 * b0 + c11 * b1 + c21 * b2) * inv;
+        b[K + 2] = (c02 * b0 + c12 * b1 + c22 * b2) * inv;
+    }
+}
+
 // EARLY: leave the elimination at the first column that fails its pivot test (one branch per tested column).
 // !EARLY: a failed test only raises `bad`, the elimination runs on and the caller discards its result.  Without the
 // branches the whole solve is one basic block, which lets the instruction scheduler overlap the columns -- this code is
@@ -126,6 +183,10 @@ struct SparseElim {
     static constexpr int M = S * (R::D - R::DQ);
     static constexpr Pat<M> P = eliminated<M>(newton_pattern<R, S, TR>(), K);
     OZ_D static void run(T (&a)[M][M], T (&b)[M], bool& ok, bool& bad) {
+        if constexpr (!EARLY && OZ_SOLVE_CLOSED_TAIL && K == tail_start<R, S, TR>()) {
+            solve_tail_closed<T, M, K>(a, b, ok, bad);
+            return;
+        }
         constexpr int pk = P.v[K][K];
         static_assert(pk != 0, "structurally zero pivot");
         if constexpr (K < M - 1) {
@@ -172,11 +233,15 @@ struct SparseElim {
     }
 };
 
-template <class R, int S, bool TR, typename T, int Rr>
+template <class R, int S, bool TR, typename T, int Rr, bool EARLY>
 struct SparseBack {
     static constexpr int M = S * (R::D - R::DQ);
     static constexpr Pat<M> P = eliminated<M>(newton_pattern<R, S, TR>(), M);
     OZ_D static void run(T (&a)[M][M], T (&b)[M]) {
+        if constexpr (!EARLY && OZ_SOLVE_CLOSED_TAIL && Rr >= tail_start<R, S, TR>()) {   // already solved in closed form
+            if constexpr (Rr > 0) SparseBack<R, S, TR, T, Rr - 1, EARLY>::run(a, b);
+            return;
+        }
         // highest column first (see RegBack): the unknown found last enters last
         T acc = b[Rr];
         static_for<0, M - 1 - Rr>([&](auto kc) {
@@ -187,7 +252,7 @@ struct SparseBack {
             b[Rr] = acc * a[Rr][Rr];
         else
             b[Rr] = acc;
-        if constexpr (Rr > 0) SparseBack<R, S, TR, T, Rr - 1>::run(a, b);
+        if constexpr (Rr > 0) SparseBack<R, S, TR, T, Rr - 1, EARLY>::run(a, b);
     }
 };
 
@@ -202,7 +267,7 @@ OZ_D int sparse_solve(T (&a)[S * (R::D - R::DQ)][S * (R::D - R::DQ)], T (&b)[S *
     if constexpr (EARLY) {
         if (bad) return 2;
     }
-    SparseBack<R, S, TR, T, M - 1>::run(a, b);
+    SparseBack<R, S, TR, T, M - 1, EARLY>::run(a, b);
     return bad ? 2 : (ok ? 0 : 1);
 }
 
