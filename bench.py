@@ -440,8 +440,8 @@ class Runner:
         elif self.kind == 'coljac':
             pl, sp = self.plan, self.spec
             n, st, d, N, P = sp.n, sp.method.num_stages, sp.d, sp.N, sp.info['P']
-            pst = self.engine.stage_parameters(sp, pl.p).reshape(n * st, P, N)
-            self.jac = self.engine.rhs_jac_eval(sp, self.Y.reshape(n * st, d, N), pst, pl.th)
+            self.jac = self.engine.rhs_jac_eval(sp, self.Y.reshape(n * st, d, N), pl.p, pl.th, compact=True, kind=self.engine.KIND_COLLOC,
+                                                stage_params=True)
             self.g = {'h': None}
         elif self.kind == 'colloc':
             pl = self.plan
@@ -489,7 +489,8 @@ class Runner:
         if self.kind == 'coljac':
             s = self.spec.method.num_stages
             fwd = w * (2 * n * s * d * N + 2 * n * d * N + (n + 1) * P * pN)          # read Y, y, p; write c1, c2
-            adj = w * n * s * N * (d + P + d + d * d + d * P)                          # read Y, p at the nodes; write f, Jy, Jp
+            jp, jpp = self.engine.rhs_jac_pattern(self.spec, self.engine.KIND_COLLOC)
+            adj = w * N * (n * s * (d + d + int(jp.sum()) + int(jpp.sum())) + (n + 1) * P)   # read Y and the raw p; write f and the structurally nonzero entries of df/dy, df/dp
             return fwd, adj
         if self.kind == 'colloc':
             s = self.spec.method.num_stages

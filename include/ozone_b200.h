@@ -162,8 +162,15 @@ OZ_API int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, co
  * of the constraint Jacobian are products of these with tableau entries and step sizes
  * (ozone/integrators/collocation.py:48-57: c1 = A hF + U y - Y, c2 = B hF + V y - y; the reference leaves the
  * differentiation to csdl, an optimiser consumes it as `dc`, ozone/paper_examples/utils/utils.py:237,273-286). */
-OZ_API int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, const void* y, const void* p, void* f,
-                           void* Jy, void* Jp);
+enum { OZ_JAC_COMPACT = 1,        /* write only the entries oz_rhs_jac_pattern marks (see below) */
+       OZ_JAC_STAGE_PARAMS = 2 }; /* blocks = steps x stages and `p` is the RAW array at the grid points, [steps+1][P][nodes] or
+                                     [steps+1][P] (p_shared): interpolated to the stage abscissae with pb->C inside the kernel */
+OZ_API int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, int32_t flags, const void* y, const void* p,
+                           void* f, void* Jy, void* Jp);
+/* Which entries of df/dy (jp [d*d], row-major) and df/dp (jpp [d*P]) the right-hand side declares possibly nonzero
+ * (1) or identically zero (0); NULL = skip.  With OZ_JAC_COMPACT, oz_rhs_jac_eval writes only the possibly-nonzero entries,
+ * in row-major order: Jy [blocks][nnz_y][nodes], Jp [blocks][nnz_p][nodes] (lunar ascent: 9 of 49 and 3 of 21). */
+OZ_API int oz_rhs_jac_pattern(int rhs_id, uint8_t* jp, uint8_t* jpp);
 
 /* TimeMarching.integrate: ozone/integrators/time_marching.py:6-59 (loop), :143-245 (stages,
  * explicit and Newton), :247-260 (update), :97-141 (outputs).  With num_inner > 0 it is

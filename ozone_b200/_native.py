@@ -60,7 +60,8 @@ SYMBOLS = {
     'oz_fma_probe': (C.c_double, [C.c_int, C.c_int, C.c_void_p, C.c_void_p]),
     'oz_rhs_eval': (C.c_int, [_PB, C.c_int64, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     'oz_rhs_out_vjp': (C.c_int, [_PB, C.c_int64] + [C.c_void_p] * 7),
-    'oz_rhs_jac_eval': (C.c_int, [_PB, C.c_int64, C.c_int64] + [C.c_void_p] * 5),
+    'oz_rhs_jac_eval': (C.c_int, [_PB, C.c_int64, C.c_int64, C.c_int32] + [C.c_void_p] * 5),
+    'oz_rhs_jac_pattern': (C.c_int, [C.c_int, C.c_void_p, C.c_void_p]),
     'oz_tm_forward_workspace_bytes': (C.c_size_t, [_PB]),
     'oz_tm_forward': (C.c_int, [_PB]),
     'oz_tm_adjoint_workspace_bytes': (C.c_size_t, [_PB]),

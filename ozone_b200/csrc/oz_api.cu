@@ -151,7 +151,7 @@ int oz_rhs_eval(const oz_problem* pb, int64_t nodes, const void* y, const void* 
     OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(nodes >= 0, "negative node count");
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
-    EvalArgs ev{nodes, y, p, dy, prof, field, nullptr, nullptr, nullptr, nullptr, nullptr, 1};
+    EvalArgs ev{nodes, y, p, dy, prof, field, nullptr, nullptr, nullptr, nullptr, nullptr, 1, 0};
     return route(pb, TM_RHS_EVAL, nullptr, &ev);
 }
 
@@ -162,18 +162,29 @@ int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, const voi
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
     OZ_REQUIRE(nodes >= 0, "negative node count");
     OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "output VJPs are defined for per-trajectory right-hand sides");
-    EvalArgs ev{nodes, y, p, nullptr, nullptr, nullptr, vprof, vfield, y_bar, p_bar, th_bar, 1};
+    EvalArgs ev{nodes, y, p, nullptr, nullptr, nullptr, vprof, vfield, y_bar, p_bar, th_bar, 1, 0};
     return route(pb, TM_OUT_VJP, nullptr, &ev);
 }
 
-int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, const void* y, const void* p, void* f, void* Jy,
-                    void* Jp) {
+int oz_rhs_jac_pattern(int rhs_id, uint8_t* jp, uint8_t* jpp) {
+    OZ_REQUIRE(known_rhs(rhs_id), "unknown rhs_id %d", rhs_id);
+    OZ_REQUIRE(plugin_of(rhs_id) || kInfo[rhs_id].kind == 0, "Jacobian patterns are defined for per-trajectory right-hand sides");
+    oz_problem pb;
+    memset(&pb, 0, sizeof(pb));
+    pb.rhs_id = rhs_id;
+    EvalArgs ev{0, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, jp, jpp, nullptr, 0, 0};
+    return route(&pb, TM_JAC_PATTERN, nullptr, &ev);
+}
+
+int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, int32_t flags, const void* y, const void* p, void* f,
+                    void* Jy, void* Jp) {
     OZ_REQUIRE(pb != nullptr, "null problem descriptor");
     OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
     OZ_REQUIRE(nodes >= 0 && blocks >= 0, "negative node / block count");
     OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "node Jacobians are defined for per-trajectory right-hand sides");
-    EvalArgs ev{nodes, y, p, f, nullptr, nullptr, nullptr, nullptr, Jy, Jp, nullptr, blocks};
+    OZ_REQUIRE(!(flags & OZ_JAC_STAGE_PARAMS) || (pb->num_stages >= 1 && pb->num_stages <= OZ_MAX_STAGES), "stage mode needs the tableau");
+    EvalArgs ev{nodes, y, p, f, nullptr, nullptr, nullptr, nullptr, Jy, Jp, nullptr, blocks, flags};
     return route(pb, TM_JAC_EVAL, nullptr, &ev);
 }
 

@@ -9,6 +9,7 @@
 // lerp-transpose of the parameter gradient (p_bar[k] gets (1-c) parts of step k and c parts of step
 // k-1) is assembled by one owner per entry -- no atomics, deterministic.
 #pragma once
+#include <cstdlib>
 #include "oz_common.cuh"
 #include "oz_tm_kernels.cuh"
 
@@ -35,6 +36,9 @@ OZ_D void col_load_p(const ColArgs<T>& a, int k, long long i, T* p) {
     for (int c = 0; c < R::P; ++c) p[c] = ld_in(a.p, (long long)k * R::P + c, a.N, i, a.p_shared);
 }
 
+#ifndef OZ_COLLOC_CHUNK   /* consecutive steps per thread of the VJP kernel (each run recomputes the step before it for p_bar) */
+#define OZ_COLLOC_CHUNK 10
+#endif
 #ifndef OZ_MB_COLLOC
 #define OZ_MB_COLLOC 3
 #endif
@@ -83,7 +87,7 @@ __global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_residual_kernel(cons
 // per-stage cotangent of hF:  W_j = sum_i a_ij mu1_ki + b_j mu2_k ;  G_j = h W_j
 template <class R, typename T, int S>
 OZ_D void col_step_vjp(const ColArgs<T>& a, int k, long long i, const T* th, const T* plo, const T* phi, T h,
-                       bool write_Y, T& hb, T* pb_lo, T* pb_hi, T* tb) {
+                       bool write_Y, T& hb, T* pb_lo, T* pb_hi, T* tb, T* mu2_prev = nullptr) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     const long long N = a.N;
@@ -95,6 +99,24 @@ OZ_D void col_step_vjp(const ColArgs<T>& a, int k, long long i, const T* th, con
         mu2[c] = __ldg(a.mu2 + ((long long)k * D + c) * N + i);
 #pragma unroll
         for (int s = 0; s < S; ++s) mu1[s][c] = __ldg(a.mu1 + (((long long)k * S + s) * D + c) * N + i);
+    }
+    // yfull[k] enters c1_k (+, every stage), c2_k (+) and c2_{k-1} (-): its gradient is formed here, while this step's
+    // multiplier rows are in registers (mu2_prev carries mu2 of step k - 1 from call to call)
+    if (mu2_prev) {
+#pragma unroll
+        for (int c = 0; c < D; ++c) {
+            T g = mu2[c];
+#pragma unroll
+            for (int s = 0; s < S; ++s) g += mu1[s][c];
+            if (write_Y) {
+                if (k == 0) {
+                    if (a.y0_bar) a.y0_bar[c * N + i] = g;
+                } else if (a.y_bar) {
+                    a.y_bar[((long long)(k - 1) * D + c) * N + i] = g - mu2_prev[c];
+                }
+            }
+            mu2_prev[c] = mu2[c];
+        }
     }
     hb = T(0);
 #pragma unroll
@@ -177,11 +199,14 @@ __global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_vjp_kernel(const Col
         for (int c = 0; c < DM::P; ++c) carry[c] = pb_hi[c];
     }
     col_load_p<R>(a, k_lo, i, plo);
+    T mu2_prev[D];   // mu2 of step k - 1: subtracted from y_bar[k - 1] (c2_{k-1} holds -yfull[k])
+#pragma unroll
+    for (int c = 0; c < D; ++c) mu2_prev[c] = k_lo > 0 ? __ldg(a.mu2 + ((long long)(k_lo - 1) * D + c) * N + i) : T(0);
     for (int k = k_lo; k < k_hi; ++k) {
         T hb;
         col_load_p<R>(a, k + 1, i, phi);
         const T h = ld_in(a.h, k, N, i, a.h_shared);
-        col_step_vjp<R, T, S>(a, k, i, th, plo, phi, h, valid, hb, pb_lo, pb_hi, tb);
+        col_step_vjp<R, T, S>(a, k, i, th, plo, phi, h, valid, hb, pb_lo, pb_hi, tb, mu2_prev);
 #pragma unroll
         for (int c = 0; c < DM::P; ++c) carry[c] += pb_lo[c];
         emit_p(k, carry);
@@ -198,28 +223,12 @@ __global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_vjp_kernel(const Col
                 a.h_bar[(long long)k * N + i] = hb;
             }
         }
-        // yfull[k] enters c1_k (+ every stage), c2_k (+) and c2_{k-1} (-)
-        if (valid) {
-#pragma unroll
-            for (int c = 0; c < D; ++c) {
-                T g = __ldg(a.mu2 + ((long long)k * D + c) * N + i);
-#pragma unroll
-                for (int s = 0; s < S; ++s) g += __ldg(a.mu1 + (((long long)k * S + s) * D + c) * N + i);
-                if (k == 0) {
-                    if (a.y0_bar) a.y0_bar[c * N + i] = g;
-                } else {
-                    g -= __ldg(a.mu2 + ((long long)(k - 1) * D + c) * N + i);
-                    if (a.y_bar) a.y_bar[((long long)(k - 1) * D + c) * N + i] = g;
-                }
-            }
-        }
     }
     if (k_hi == a.n) {
         emit_p(a.n, carry);
         if (valid && a.y_bar)  // y_n enters only c2_{n-1} (-)
 #pragma unroll
-            for (int c = 0; c < D; ++c)
-                a.y_bar[((long long)(a.n - 1) * D + c) * N + i] = -__ldg(a.mu2 + ((long long)(a.n - 1) * D + c) * N + i);
+            for (int c = 0; c < D; ++c) a.y_bar[((long long)(a.n - 1) * D + c) * N + i] = -mu2_prev[c];
     }
     if (a.th_bar) {
 #pragma unroll
@@ -255,7 +264,13 @@ template <class R>
 inline ColWs colloc_ws_layout(const oz_problem* pb) {
     ColWs w;
     const int block = 128;
-    w.chunk = 8;
+    // runs of about OZ_COLLOC_CHUNK steps, balanced so that the last run is not a short one (n = 100: 10 runs of 10;
+    // 13 runs of 8 with a ragged last one measured 3 % slower, profiles/r2_colloc_vjp_chunk_sweep.txt)
+    int target = OZ_COLLOC_CHUNK;
+    if (const char* e = getenv("OZ_COLLOC_CHUNK")) target = atoi(e) > 0 ? atoi(e) : OZ_COLLOC_CHUNK;   // experiments
+    int runs = (pb->n + target / 2) / target;
+    if (runs < 1) runs = 1;
+    w.chunk = (pb->n + runs - 1) / runs;
     w.nchunks = (pb->n + w.chunk - 1) / w.chunk;
     w.W = ((pb->N + block - 1) / block) * (block / 32);
     w.rows_h = (pb->h_shared && pb->h_bar) ? pb->n : 0;

@@ -101,6 +101,12 @@ struct RhsLunarAscent {
     static constexpr int DQ = 0;
     static constexpr double kT = 1.8335634, kVex = 3049.87, kG0 = 1.625, kR0 = 1738100.0;
     static constexpr double kSqrtG0R0 = 1680.5988516002265;  // sqrt(g0 * R0) = sqrt(2824412.5)
+    // possibly-nonzero entries of df/dy and df/dp (oz_sparse_solve.cuh; compact Jacobians for the optimiser adapter):
+    // r' = V;  V' = -r + (T/m) u  (depends on r, m and u);  m' = const
+    static constexpr unsigned char JP[49] = {0, 0, 0, 1, 0, 0, 0,   0, 0, 0, 0, 1, 0, 0,   0, 0, 0, 0, 0, 1, 0,
+                                             1, 0, 0, 0, 0, 0, 1,   0, 1, 0, 0, 0, 0, 1,   0, 0, 1, 0, 0, 0, 1,
+                                             0, 0, 0, 0, 0, 0, 0};
+    static constexpr unsigned char JPP[21] = {0, 0, 0,  0, 0, 0,  0, 0, 0,  1, 0, 0,  0, 1, 0,  0, 0, 1,  0, 0, 0};
     template <typename T>
     OZ_D static void f(const T* y, const T* p, const T*, T* dy) {
         const T Tm = T(kT) / y[6];

@@ -56,6 +56,32 @@ constexpr bool jac_nz(int r, int c) {
         return true;
 }
 
+template <class R, class = void>
+struct HasJPP : std::false_type {};
+template <class R>
+struct HasJPP<R, std::void_t<decltype(R::JPP)>> : std::true_type {};
+// may df_r / dp_c be nonzero?  (optional functor member JPP[D * P], same convention as JP)
+template <class R>
+constexpr bool jacp_nz(int r, int c) {
+    if constexpr (HasJPP<R>::value)
+        return R::JPP[r * (R::P > 0 ? R::P : 1) + c] != 0;
+    else
+        return true;
+}
+// number of possibly-nonzero entries of df/dy (row-major) before entry e, and in total: the compact Jacobian layout
+template <class R>
+constexpr int jac_nnz_before(int e) {
+    int cnt = 0;
+    for (int q = 0; q < e; ++q) cnt += jac_nz<R>(q / R::D, q % R::D) ? 1 : 0;
+    return cnt;
+}
+template <class R>
+constexpr int jacp_nnz_before(int e) {
+    int cnt = 0;
+    for (int q = 0; q < e; ++q) cnt += jacp_nz<R>(q / (R::P > 0 ? R::P : 1), q % (R::P > 0 ? R::P : 1)) ? 1 : 0;
+    return cnt;
+}
+
 template <int M>
 struct Pat {           // 0: structurally zero, 1: exactly one, 2: general
     unsigned char v[M][M];

@@ -1153,22 +1153,44 @@ __global__ void __launch_bounds__(128) rhs_out_vjp_kernel(long long nodes, int t
 //   y [blocks][D][nodes], p [blocks][P][nodes]  ->  f [blocks][D][nodes], Jy [blocks][D][D][nodes] (d f_r / d y_c at [r][c]),
 //   Jp [blocks][D][P][nodes]; th [S] or [S][nodes].  With blocks = n s and nodes = N these are the stage design variables
 // of the Collocation approach as they lie in memory.
-template <class R, typename T>
+// COMPACT: only the entries the functor's patterns JP / JPP allow are written, in row-major order of the nonzeros
+// (Jy [blocks][nnz_y][nodes], Jp [blocks][nnz_p][nodes]; oz_rhs_jac_pattern tells the caller which they are).  The lunar-ascent
+// Jacobians have 9 of 49 and 3 of 21 entries: 19 instead of 77 values per node leave the chip.
+// Stage mode (lerp.S > 0): block b is (step k, stage j) = (b / S, b % S) and `p` is the RAW parameter array at the grid
+// points, [steps + 1][P][nodes] or, shared, [steps + 1][P]; the kernel interpolates it to the stage abscissa itself
+// (ozone/collections.py:277-289), so no interpolated copy of the parameters is ever materialised.
+template <typename T>
+struct JacLerp {
+    int S, p_shared;
+    T C[kMaxS];
+};
+
+template <class R, typename T, bool COMPACT>
 __global__ void __launch_bounds__(128) rhs_jac_kernel(long long nodes, int th_shared, const T* __restrict__ y,
                                                       const T* __restrict__ p, const T* __restrict__ th, T* __restrict__ f,
-                                                      T* __restrict__ Jy, T* __restrict__ Jp) {
+                                                      T* __restrict__ Jy, T* __restrict__ Jp, const JacLerp<T> lerp) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= nodes) return;
     const long long b = blockIdx.y;
     y += b * D * nodes;
-    p += b * DM::P * nodes;
     T yy[D], pp[DM::P1], tt[DM::S1];
 #pragma unroll
     for (int c = 0; c < D; ++c) yy[c] = y[c * nodes + i];
+    if (lerp.S > 0) {
+        const long long k = b / lerp.S;
+        const T cj = lerp.C[b - k * lerp.S];
 #pragma unroll
-    for (int c = 0; c < DM::P; ++c) pp[c] = p[c * nodes + i];
+        for (int c = 0; c < DM::P; ++c) {
+            const T lo = lerp.p_shared ? p[k * DM::P + c] : p[(k * DM::P + c) * nodes + i];
+            const T hi = lerp.p_shared ? p[(k + 1) * DM::P + c] : p[((k + 1) * DM::P + c) * nodes + i];
+            pp[c] = lo + cj * (hi - lo);
+        }
+    } else {
+#pragma unroll
+        for (int c = 0; c < DM::P; ++c) pp[c] = p[(b * DM::P + c) * nodes + i];
+    }
 #pragma unroll
     for (int c = 0; c < DM::SP; ++c) tt[c] = th_shared ? th[c] : th[c * nodes + i];
     if (f) {
@@ -1180,27 +1202,43 @@ __global__ void __launch_bounds__(128) rhs_jac_kernel(long long nodes, int th_sh
     if (Jy) {
         T J[D * D];
         R::jac(yy, pp, tt, J);
+        if constexpr (COMPACT) {
+            constexpr int NNZ = jac_nnz_before<R>(D * D);
+            static_for<0, D * D>([&](auto ec) {
+                constexpr int e = decltype(ec)::value;
+                if constexpr (jac_nz<R>(e / D, e % D)) Jy[(b * NNZ + jac_nnz_before<R>(e)) * nodes + i] = J[e];
+            });
+        } else {
 #pragma unroll
-        for (int c = 0; c < D * D; ++c) Jy[(b * D * D + c) * nodes + i] = J[c];
+            for (int c = 0; c < D * D; ++c) Jy[(b * D * D + c) * nodes + i] = J[c];
+        }
     }
     if constexpr (DM::P > 0) {
         if (Jp) {
+            constexpr int NNZP = jacp_nnz_before<R>(D * DM::P);
+            static_for<0, D>([&](auto rc) {      // row r of J_p = J_p^T e_r
+                constexpr int r = decltype(rc)::value;
+                if constexpr (!COMPACT || jacp_nnz_before<R>((r + 1) * DM::P) > jacp_nnz_before<R>(r * DM::P)) {
+                    T v[D], gy[D], gp[DM::P1], gt[DM::S1];
 #pragma unroll
-            for (int r = 0; r < D; ++r) {      // row r of J_p = J_p^T e_r
-                T v[D], gy[D], gp[DM::P1], gt[DM::S1];
+                    for (int c = 0; c < D; ++c) {
+                        v[c] = c == r ? T(1) : T(0);
+                        gy[c] = T(0);
+                    }
 #pragma unroll
-                for (int c = 0; c < D; ++c) {
-                    v[c] = c == r ? T(1) : T(0);
-                    gy[c] = T(0);
+                    for (int c = 0; c < DM::P1; ++c) gp[c] = T(0);
+#pragma unroll
+                    for (int c = 0; c < DM::S1; ++c) gt[c] = T(0);
+                    R::vjp(yy, pp, tt, v, gy, gp, gt);
+                    static_for<0, DM::P>([&](auto cc) {
+                        constexpr int c = decltype(cc)::value;
+                        if constexpr (!COMPACT)
+                            Jp[((b * D + r) * DM::P + c) * nodes + i] = gp[c];
+                        else if constexpr (jacp_nz<R>(r, c))
+                            Jp[(b * NNZP + jacp_nnz_before<R>(r * DM::P + c)) * nodes + i] = gp[c];
+                    });
                 }
-#pragma unroll
-                for (int c = 0; c < DM::P1; ++c) gp[c] = T(0);
-#pragma unroll
-                for (int c = 0; c < DM::S1; ++c) gt[c] = T(0);
-                R::vjp(yy, pp, tt, v, gy, gp, gt);
-#pragma unroll
-                for (int c = 0; c < DM::P; ++c) Jp[((b * D + r) * DM::P + c) * nodes + i] = gp[c];
-            }
+            });
         }
     }
 }

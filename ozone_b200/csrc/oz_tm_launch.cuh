@@ -11,7 +11,7 @@ namespace oz {
 #define OZ_ADJ_SPEC_STAGES 4
 #endif
 
-enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3, TM_OUT_VJP = 4, TM_JAC_EVAL = 5 };
+enum TmMode { TM_FORWARD = 0, TM_ADJOINT = 1, TM_ADJOINT_WS = 2, TM_RHS_EVAL = 3, TM_OUT_VJP = 4, TM_JAC_EVAL = 5, TM_JAC_PATTERN = 6 };
 
 struct EvalArgs {
     long long nodes;
@@ -21,6 +21,7 @@ struct EvalArgs {
     const void *vprof, *vfield;
     void *yb, *pb, *tb;
     long long blocks;     // TM_JAC_EVAL: number of [D][nodes] blocks (one per (step, stage))
+    int compact;          // TM_JAC_EVAL flags: bit 0 write only the entries JP / JPP allow, bit 1 `p` is raw (interpolate to the stages)
 };
 
 template <class R, typename T, int S, bool IMPL>
@@ -127,28 +128,42 @@ int dispatch_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
 
 template <class R>
 int dispatch_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
+    if (mode == TM_JAC_PATTERN) {  // host only: which entries of df/dy and df/dp the functor declares possibly nonzero
+        unsigned char* jp = (unsigned char*)ev->yb;
+        unsigned char* jpp = (unsigned char*)ev->pb;
+        if (jp)
+            for (int e = 0; e < R::D * R::D; ++e) jp[e] = jac_nz<R>(e / R::D, e % R::D) ? 1 : 0;
+        if constexpr (R::P > 0) {
+            if (jpp)
+                for (int e = 0; e < R::D * R::P; ++e) jpp[e] = jacp_nz<R>(e / R::P, e % R::P) ? 1 : 0;
+        }
+        return 0;
+    }
     if (mode == TM_JAC_EVAL) {     // f -> ev->dy, Jy -> ev->yb, Jp -> ev->pb
         cudaStream_t stream = (cudaStream_t)pb->stream;
         const dim3 grid((unsigned)((ev->nodes + 127) / 128), (unsigned)ev->blocks);
         if (grid.x == 0 || grid.y == 0) return 0;
         OZ_REQUIRE(ev->blocks <= 65535, "at most 65535 blocks per Jacobian launch");
-        if constexpr (OZ_WANT_F64(true)) {
-            if (pb->dtype == OZ_F64) {
-                rhs_jac_kernel<R, double><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const double*)ev->y, (const double*)ev->p,
-                                                                  (const double*)pb->th, (double*)ev->dy, (double*)ev->yb,
-                                                                  (double*)ev->pb);
-                OZ_CUDA_CHECK(cudaGetLastError());
-                return 0;
-            }
-        }
-        if constexpr (OZ_WANT_F64(false)) {
-            if (pb->dtype == OZ_F32) {
-                rhs_jac_kernel<R, float><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const float*)ev->y, (const float*)ev->p,
-                                                                 (const float*)pb->th, (float*)ev->dy, (float*)ev->yb, (float*)ev->pb);
-                OZ_CUDA_CHECK(cudaGetLastError());
-                return 0;
-            }
-        }
+        auto go = [&](auto tag) -> int {
+            using T = decltype(tag);
+            JacLerp<T> lerp;
+            lerp.S = (ev->compact & 2) ? pb->num_stages : 0;      // bit 1: p is the raw grid-point array, interpolate here
+            lerp.p_shared = pb->p_shared;
+            for (int j = 0; j < kMaxS; ++j) lerp.C[j] = (T)pb->C[j];
+            if (lerp.S > 0) OZ_REQUIRE(ev->blocks % lerp.S == 0, "stage mode: the block count must be a multiple of the stage count");
+            if (ev->compact & 1)
+                rhs_jac_kernel<R, T, true><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const T*)ev->y, (const T*)ev->p,
+                                                                    (const T*)pb->th, (T*)ev->dy, (T*)ev->yb, (T*)ev->pb, lerp);
+            else
+                rhs_jac_kernel<R, T, false><<<grid, 128, 0, stream>>>(ev->nodes, pb->th_shared, (const T*)ev->y, (const T*)ev->p,
+                                                                     (const T*)pb->th, (T*)ev->dy, (T*)ev->yb, (T*)ev->pb, lerp);
+            OZ_CUDA_CHECK(cudaGetLastError());
+            return 0;
+        };
+        if constexpr (OZ_WANT_F64(true))
+            if (pb->dtype == OZ_F64) return go(double{});
+        if constexpr (OZ_WANT_F64(false))
+            if (pb->dtype == OZ_F32) return go(float{});
         set_error("no Jacobian kernel for dtype %d in this build", pb->dtype);
         return -1;
     }

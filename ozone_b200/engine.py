@@ -268,7 +268,7 @@ def time_march(spec: SolveSpec, y0, h, p=None, th=None):
 
 def rhs_eval(spec: SolveSpec, y, p=None, th=None):
     """oz_rhs_eval: f and the outputs at `nodes` points; y (d, nodes), p (P, nodes)."""
-    pb = make_problem(replace(spec, N=1) if False else spec)
+    pb = make_problem(spec)
     nodes = y.shape[1]
     info = spec.info
     dev = y.device
@@ -523,10 +523,25 @@ def rhs_out_vjp(spec: SolveSpec, y, p, th, vprof, vfield):
     return yb, pbar, tbar
 
 
-def rhs_jac_eval(spec: SolveSpec, y, p=None, th=None, want_f=True, want_p=True):
+def rhs_jac_pattern(spec: SolveSpec, kind: int = KIND_TM):
+    """oz_rhs_jac_pattern: boolean arrays (d, d) and (d, P) of the entries of df/dy, df/dp that may be nonzero."""
+    import numpy as np
+    pb = make_problem(spec, kind)
+    d, P = spec.info['d'], spec.info['P']
+    jp = (C.c_uint8 * (d * d))()
+    jpp = (C.c_uint8 * max(d * P, 1))()
+    nat.check(nat.lib.oz_rhs_jac_pattern(pb.rhs_id, jp, jpp), 'oz_rhs_jac_pattern')
+    return (np.frombuffer(jp, dtype=np.uint8).reshape(d, d).astype(bool),
+            np.frombuffer(jpp, dtype=np.uint8)[:d * P].reshape(d, P).astype(bool))
+
+
+def rhs_jac_eval(spec: SolveSpec, y, p=None, th=None, want_f=True, want_p=True, compact=False, kind: int = KIND_TM,
+                 stage_params=False):
     """oz_rhs_jac_eval on y (blocks, d, nodes), p (blocks, P, nodes) -> f (blocks, d, nodes), Jy (blocks, d, d, nodes),
-    Jp (blocks, d, P, nodes) | None.  th (S,) or (S, nodes)."""
-    pb = make_problem(spec)
+    Jp (blocks, d, P, nodes) | None.  th (S,) or (S, nodes).  compact: Jy (blocks, nnz_y, nodes), Jp (blocks, nnz_p, nodes)
+    hold only the entries rhs_jac_pattern() marks, in row-major order.  stage_params: blocks = n s and `p` is the RAW
+    packed parameter array (n + 1, P, N) | (n + 1, P): the kernel interpolates it to the stage abscissae itself."""
+    pb = make_problem(spec, kind)
     info, dev = spec.info, y.device
     blocks, _, nodes = y.shape
     y = y.contiguous()
@@ -535,10 +550,16 @@ def rhs_jac_eval(spec: SolveSpec, y, p=None, th=None, want_f=True, want_p=True):
     pb.th = _ptr(th)
     pb.th_shared = int(th is None or th.dim() == 1)
     d, P = info['d'], info['P']
+    ny, npp = d * d, d * P
+    if compact:
+        jp, jpp = rhs_jac_pattern(spec, kind)
+        ny, npp = int(jp.sum()), int(jpp.sum())
     f = torch.empty((blocks, d, nodes), dtype=spec.dtype, device=dev) if want_f else None
-    Jy = torch.empty((blocks, d, d, nodes), dtype=spec.dtype, device=dev)
-    Jp = torch.empty((blocks, d, P, nodes), dtype=spec.dtype, device=dev) if (P and want_p) else None
-    nat.check(nat.lib.oz_rhs_jac_eval(C.byref(pb), nodes, blocks, _ptr(y), _ptr(p), _ptr(f), _ptr(Jy), _ptr(Jp)), 'oz_rhs_jac_eval')
+    Jy = torch.empty((blocks, ny, nodes) if compact else (blocks, d, d, nodes), dtype=spec.dtype, device=dev)
+    Jp = torch.empty((blocks, npp, nodes) if compact else (blocks, d, P, nodes), dtype=spec.dtype, device=dev) if (P and want_p) else None
+    nat.check(nat.lib.oz_rhs_jac_eval(C.byref(pb), nodes, blocks, int(compact) | (2 if stage_params else 0), _ptr(y), _ptr(p), _ptr(f),
+                                      _ptr(Jy), _ptr(Jp)),
+              'oz_rhs_jac_eval')
     return f, Jy, Jp
 
 

@@ -129,9 +129,10 @@ class CollocationBlocks:
                           c2[k]   = h_k sum_j b_j  f(Y[k,j], p_kj) + yfull[k] - yfull[k+1]          (collocation.py:48-50)
     with yfull = [y0; y] and p_kj = p[k] (1 - c_j) + p[k+1] c_j (collections.py:277-289).  Every block of dc is a product
     of a tableau entry, a step size and a node Jacobian, so only those are stored (one kernel launch, HBM-lean):
-        F  [n, s, d, N]       f at the stage nodes            (d c / d h_k)
-        Jy [n, s, d, d, N]    df/dy at the stage nodes        (d c / d Y)
-        Jp [n, s, d, P, N]    df/dp at the stage nodes        (d c / d p[k], d p[k+1])
+        F     [n, s, d, N]        f at the stage nodes                               (d c / d h_k)
+        Jy_nz [n, s, nnz_y, N]    possibly-nonzero entries of df/dy (pattern_y, row-major)  (d c / d Y)
+        Jp_nz [n, s, nnz_p, N]    possibly-nonzero entries of df/dp (pattern_p)             (d c / d p[k], d p[k+1])
+    (`Jy`, `Jp` expand them to dense [n, s, d, d | P, N] on demand.)
     ``dense(i)`` expands one design's Jacobian; ``rmatvec`` is the transposed product through the VJP kernel."""
 
     def __init__(self, integ, Y, y):
@@ -146,18 +147,38 @@ class CollocationBlocks:
         Cc = torch.as_tensor(spec.method.C, dtype=spec.dtype, device=Y.device).reshape(-1)
         self.A, self.B, self.C = A, B, Cc
         self.h = h if not spec.h_shared else h.unsqueeze(-1).expand(n, N)
-        pst = engine.stage_parameters(spec, p).reshape(n * s, P, N) if P else None
-        F, Jy, Jp = engine.rhs_jac_eval(spec, Y.detach().reshape(n * s, d, N), pst, th)     # ONE launch, no re-layout
+        # ONE launch over the stage variables as they lie in memory; only the entries the right-hand side's sparsity
+        # patterns allow leave the chip (lunar ascent: 9 of 49 and 3 of 21)
+        self.pattern_y, self.pattern_p = engine.rhs_jac_pattern(spec, engine.KIND_COLLOC)
+        F, Jy, Jp = engine.rhs_jac_eval(spec, Y.detach().reshape(n * s, d, N), p, th, compact=True, kind=engine.KIND_COLLOC,
+                                        stage_params=True)       # the kernel interpolates p to the stage abscissae
         self.F = F.reshape(n, s, d, N)
-        self.Jy = Jy.reshape(n, s, d, d, N)
-        self.Jp = Jp.reshape(n, s, d, P, N) if Jp is not None else None
+        self.Jy_nz = Jy.reshape(n, s, -1, N)                     # nonzeros of df/dy in row-major order
+        self.Jp_nz = Jp.reshape(n, s, -1, N) if Jp is not None else None
+
+    def _expand(self, nz, pattern):
+        """(n, s, nnz, N) -> (n, s, rows, cols, N) with the structural zeros filled in"""
+        n, s, _, N = nz.shape
+        full = torch.zeros((n, s) + pattern.shape + (N,), dtype=nz.dtype, device=nz.device)
+        idx = torch.as_tensor(np.argwhere(pattern), device=nz.device)
+        full[:, :, idx[:, 0], idx[:, 1], :] = nz
+        return full
+
+    @property
+    def Jy(self):
+        return self._expand(self.Jy_nz, self.pattern_y)
+
+    @property
+    def Jp(self):
+        return self._expand(self.Jp_nz, self.pattern_p) if self.Jp_nz is not None else None
 
     # ---- one design, dense: rows [c1 (n s d), c2 (n d)], columns [Y (n s d), y (n d), y0 (d), h (n), p ((n+1) P)]
     def dense(self, i):
         n, s, d, P = self.n, self.s, self.d, self.P
         A, B, Cc = (t.cpu().numpy() for t in (self.A, self.B, self.C))
-        F, Jy = self.F[..., i].cpu().numpy(), self.Jy[..., i].cpu().numpy()
-        Jp = self.Jp[..., i].cpu().numpy() if self.Jp is not None else None
+        F = self.F[..., i].cpu().numpy()
+        Jy = self._expand(self.Jy_nz[..., i:i + 1], self.pattern_y)[..., 0].cpu().numpy()
+        Jp = self._expand(self.Jp_nz[..., i:i + 1], self.pattern_p)[..., 0].cpu().numpy() if self.Jp_nz is not None else None
         h = self.h[:, i].cpu().numpy()
         nY, ny = n * s * d, n * d
         cols = dict(Y=(0, nY), y=(nY, ny), y0=(nY + ny, d), h=(nY + ny + d, n), p=(nY + ny + d + n, (n + 1) * P))

@@ -311,7 +311,6 @@ def solve_grid_emulated(method, nx, n, num_inner, world, y0_global, h, u, rhs_cf
     if peer_halos and world > 1:
         halo = 2 * method.num_stages * num_inner
         arena = peer.LocalArena(4096 + 4 * halo * (8 if dtype == torch.float64 else 4), device, world)
-        offs = None
         for r in range(world):
             view = arena.view(r)
             view._cursor = 0

@@ -593,6 +593,10 @@ class TracedRHS:
         ov_body = block([(f'yb[{j}]', e) for j, e in enumerate(self.ovjp_y)] + [(f'pb[{j}]', e) for j, e in enumerate(self.ovjp_p)]
                         + [(f'tb[{j}]', e) for j, e in enumerate(self.ovjp_th)], accumulate=True)
         jp = ', '.join('0' if self.J[i][j].is_const(0.0) else '1' for i in range(D) for j in range(D))
+        memo = {}
+        pl = [leaf('p', j) for j in range(P)]
+        jpp = ', '.join('0' if diff(self.f_exprs[i], pl[j], memo).is_const(0.0) else '1' for i in range(D) for j in range(P))
+        jpp_line = (f'    static constexpr unsigned char JPP[{D * P}] = {{{jpp}}};   // the same for df_r/dp_c\n' if P else '')
         return f'''// generated by ozone_b200/trace.py from a Python right-hand side callback
 #include "oz_common.cuh"
 namespace oz {{
@@ -600,7 +604,7 @@ struct RhsTraced {{
     static constexpr int ID = OZ_RHS_PLUGIN_BASE, D = {D}, P = {P}, S = {S}, NPROF = {NP}, NFIELD = {NF};
     static constexpr int DQ = {self.DQ};
     static constexpr unsigned char JP[{D * D}] = {{{jp}}};   // which df_r/dy_c are not identically zero (oz_sparse_solve.cuh)
-    template <typename T>
+{jpp_line}    template <typename T>
     OZ_D static void f(const T* y, const T* p, const T* th, T* dy) {{
 {f_body}
     }}

@@ -130,3 +130,29 @@ def test_ascent_optimisation_problem_f_c_df_dc_for_64_designs():
     fd = np.concatenate([np_((cp['stage_c'] - cm['stage_c'])[..., i]).reshape(-1),
                          np_((cp['state_c'] - cm['state_c'])[..., i]).reshape(-1)]) / (2 * e)
     assert np.allclose(dcdtf, fd, rtol=1e-6, atol=1e-8)
+
+
+def test_compact_node_jacobians_equal_the_dense_ones_and_follow_the_declared_patterns():
+    """oz_rhs_jac_eval with compact = 1 writes only the entries oz_rhs_jac_pattern marks; the dense output must be zero
+    everywhere else (i.e. the functor's JP / JPP declarations are truthful) and equal on the marked entries."""
+    from ozone_b200.glms import get_integration_method
+    rng = np.random.default_rng(2)
+    for rhs_name, d, P in (('lunar_ascent', 7, 3), ('van_der_pol', 3, 1), ('lotka_volterra', 2, 1)):
+        spec = engine.SolveSpec(rhs_name=rhs_name, method=get_integration_method('RK4'), N=50, n=3)
+        S = spec.info['S']
+        y = torch.tensor(rng.uniform(0.5, 2.0, (6, d, 50)), dtype=torch.float64, device='cuda')
+        p = torch.tensor(rng.uniform(-1.0, 1.0, (6, P, 50)), dtype=torch.float64, device='cuda')
+        th = torch.tensor(rng.uniform(0.4, 0.6, (S, 50)), dtype=torch.float64, device='cuda') if S else None
+        jp, jpp = engine.rhs_jac_pattern(spec)
+        f0, Jy, Jp = engine.rhs_jac_eval(spec, y, p, th)
+        f1, Jyc, Jpc = engine.rhs_jac_eval(spec, y, p, th, compact=True)
+        assert torch.equal(f0, f1)
+        assert tuple(Jyc.shape) == (6, int(jp.sum()), 50) and tuple(Jpc.shape) == (6, int(jpp.sum()), 50)
+        iy, ip = np.argwhere(jp), np.argwhere(jpp)
+        assert torch.equal(Jy[:, iy[:, 0], iy[:, 1], :], Jyc) and torch.equal(Jp[:, ip[:, 0], ip[:, 1], :], Jpc)
+        mask_y = torch.tensor(~jp, device='cuda')
+        mask_p = torch.tensor(~jpp, device='cuda')
+        assert float(Jy[:, mask_y, :].abs().max()) == 0.0 if mask_y.any() else True
+        assert float(Jp[:, mask_p, :].abs().max()) == 0.0 if mask_p.any() else True
+    jp, jpp = engine.rhs_jac_pattern(engine.SolveSpec(rhs_name='lunar_ascent', method=get_integration_method('RK4'), N=1, n=1))
+    assert int(jp.sum()) == 9 and int(jpp.sum()) == 3
