@@ -563,14 +563,6 @@ def rhs_jac_eval(spec: SolveSpec, y, p=None, th=None, want_f=True, want_p=True, 
     return f, Jy, Jp
 
 
-def stage_parameters(spec: SolveSpec, p):
-    """Dynamic parameters at the stage abscissae, (n, s, P, N): p[k] (1 - c_j) + p[k+1] c_j (collections.py:277-289)."""
-    n, N, P = spec.n, spec.N, spec.info['P']
-    Cc = torch.as_tensor(spec.method.C, dtype=spec.dtype, device=p.device).reshape(1, -1, 1, 1)
-    pf = p.unsqueeze(-1).expand(n + 1, P, N) if spec.p_shared else p
-    return (pf[:-1].unsqueeze(1) * (1.0 - Cc) + pf[1:].unsqueeze(1) * Cc).contiguous()
-
-
 class _OutputsOnHistory(torch.autograd.Function):
     """Profile outputs at every grid point of a history and field outputs summed over time, on the tape
     (the reference's are csdl graph nodes, vector_based.py:33-49): backward is one oz_rhs_out_vjp launch."""
