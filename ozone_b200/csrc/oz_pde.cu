@@ -534,19 +534,21 @@ static PdeLayout pde_layout(const oz_problem* pb) {
     // -> 3.26 + 8.31 us per forward / reverse step, 500k cells 8.05 + 20.76 -> 7.34 + 18.76; 10^6 cells are best at 4 / 2).
     // OZ_PDE_FUSE_F / OZ_PDE_FUSE_A (environment) override for experiments.
     const bool small = L.nx <= (long long)OZ_PDE_SMALL_CELLS;
-    L.fuse_f = small ? OZ_PDE_FUSE_SMALL : kPdeFuse;
-    L.fuse_a = small ? OZ_PDE_FUSE_ADJ_SMALL : kPdeFuseAdj;
+    const bool tiny = L.nx <= (long long)OZ_PDE_TINY_CELLS;
+    L.fuse_f = tiny ? 8 : (small ? OZ_PDE_FUSE_SMALL : kPdeFuse);
+    L.fuse_a = tiny ? 4 : (small ? OZ_PDE_FUSE_ADJ_SMALL : kPdeFuseAdj);
     if (const char* e = getenv("OZ_PDE_FUSE_F")) L.fuse_f = atoi(e);
     if (const char* e = getenv("OZ_PDE_FUSE_A")) L.fuse_a = atoi(e);
     if (L.fuse_f < 1) L.fuse_f = 1;
     if (L.fuse_a < 1) L.fuse_a = 1;
     // Cells per thread (tile = 256 x cpt cells including halos).  4 is best from 250k cells up, also for the reverse
     // kernel although it spills 152 B there (3 cells per thread do not spill but lose more to halos: 34.8 vs 33.7 us per
-    // reverse step at 10^6 cells); a grid of about one wave of CTAs (<= OZ_PDE_TINY_CELLS, the slab of an 8-GPU shard)
-    // gains 6-8 % from 3 (profiles/r2_pde_cells_per_thread_sweep.txt).
-    const bool tiny = L.nx <= (long long)OZ_PDE_TINY_CELLS;
-    L.cpt_f = tiny ? 3 : kPdeCpt;
-    L.cpt_a = tiny ? 3 : kPdeCpt;
+    // reverse step at 10^6 cells).  A grid of about one wave of 1024-cell tiles (<= OZ_PDE_TINY_CELLS, the slab of an
+    // 8-GPU shard) takes 2 cells per thread AND the shallower fusion 8 / 4: ~280 CTAs of 512 cells, two per SM, so that one
+    // computes while the other waits at a stage barrier (125.5k cells: 3.16 + 7.54 -> 2.65 + 6.52 us per forward / reverse
+    // step; with 16 / 8 fused steps the halos eat the gain: profiles/r2_pde_cells_per_thread_sweep.txt, r2_pde_tiny_sweep.txt).
+    L.cpt_f = tiny ? 2 : kPdeCpt;
+    L.cpt_a = tiny ? 2 : kPdeCpt;
     if (const char* e = getenv("OZ_PDE_CPT_F")) L.cpt_f = atoi(e);
     if (const char* e = getenv("OZ_PDE_CPT_A")) L.cpt_a = atoi(e);
     if (L.cpt_f != 2 && L.cpt_f != 3) L.cpt_f = 4;

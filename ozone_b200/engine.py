@@ -291,6 +291,8 @@ GRID_REVERSE_STEPS_PER_LAUNCH = 2   # OZ_PDE_FUSE_ADJ
 def grid_fusion(nx):
     """(forward, reverse) steps fused per launch for a grid of nx cells: mirrors pde_layout() in csrc/oz_pde.cu
     (launch counting only)."""
+    if nx <= 160000:
+        return 8, 4
     return (16, 8) if nx <= 600000 else (GRID_STEPS_PER_LAUNCH, GRID_REVERSE_STEPS_PER_LAUNCH)
 
 
