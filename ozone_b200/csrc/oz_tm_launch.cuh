@@ -74,11 +74,13 @@ int run_tm(const oz_problem* pb, int mode, size_t* ws_bytes) {
     wp.th = a.ws + w.off_th;
     wp.seg = a.ws + w.off_seg;
     wp.W = w.W;
-    // the specialised reverse sweeps (see tm_adjoint_kernel): RK4-shaped tableau, final-state cotangent only
+    // the specialised reverse sweeps (see tm_adjoint_kernel): final-state cotangent only, shared step vector with h_bar,
+    // p_bar wanted, full history; explicit methods additionally need the RK4-shaped tableau the specialisation pins
+    constexpr bool kSpecOk = R::P > 0 && ((!IMPL && S == OZ_ADJ_SPEC_STAGES) || (IMPL && use_reg_solve<R, S, T>()));
     int spec = 0;
-    if constexpr (!IMPL && S == OZ_ADJ_SPEC_STAGES && R::P > 0) {
-        if (a.chain && pb->hist && pb->final_bar && !pb->hist_bar && !pb->prof_bar && !pb->field_bar && pb->h_shared && pb->h_bar &&
-            pb->p_bar)
+    if constexpr (kSpecOk) {
+        if ((IMPL || a.chain) && pb->hist && pb->final_bar && !pb->hist_bar && !pb->prof_bar && !pb->field_bar && pb->h_shared &&
+            pb->h_bar && pb->p_bar)
             spec = pb->p_shared ? 1 : 2;
     }
     auto launch = [&](auto kern) -> int {
@@ -89,7 +91,7 @@ int run_tm(const oz_problem* pb, int mode, size_t* ws_bytes) {
         return 0;
     };
     int rc = 0;
-    if constexpr (!IMPL && S == OZ_ADJ_SPEC_STAGES && R::P > 0) {
+    if constexpr (kSpecOk) {
         if (spec == 1)
             rc = launch(tm_adjoint_kernel<R, T, S, IMPL, 1>);
         else if (spec == 2)
