@@ -86,3 +86,33 @@ def test_world_size_2_gloo_sharding_and_halo_exchange():
     for p in procs:
         p.join(timeout=60)
     assert sorted(res) == [(0, 'ok'), (1, 'ok')], res
+
+
+def test_peer_arena_layout_without_a_gpu():
+    """Address arithmetic of the peer-memory channels (ozone_b200/peer.py) on CPU buffers: every rank computes the same
+    offsets, slots of different (parity, side) do not overlap, flags and slots stay inside the arena, 8-byte aligned."""
+    from ozone_b200 import peer
+    world, count = 4, 96
+    arena = peer.LocalArena(4096 + 4 * count * 8, 'cpu', world)
+    chans = []
+    for r in range(world):
+        v = arena.view(r)
+        v._cursor = 0
+        chans.append(peer.HaloChannel(v, count, torch.float64))
+    assert len({(c.off_ctl, c.off_slots) for c in chans}) == 1            # same layout on every rank
+    c = chans[1]
+    spans = []
+    for par in (0, 1):
+        for side in (0, 1):
+            a = c._slot(2, par, side) - arena.ptrs[2]
+            spans.append((a, a + count * 8))
+            assert a % 8 == 0 and 0 <= a and a + count * 8 <= arena.nbytes
+    spans.sort()
+    assert all(hi <= lo2 for (_, hi), (lo2, _) in zip(spans, spans[1:]))   # no overlap
+    flags = [c._flag(2, s) - arena.ptrs[2] for s in (0, 1)]
+    assert flags[0] != flags[1] and all(f % 8 == 0 and f + 8 <= c.off_slots for f in flags)
+    with pytest.raises(ValueError):
+        arena.view(0).region(1 << 30)                                      # the arena refuses to overflow
+    v = arena.view(0)
+    v._cursor = 0
+    assert v.region(8 * world) == 0 and v.region(64) % 256 == 0
