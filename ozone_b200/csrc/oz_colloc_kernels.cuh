@@ -39,11 +39,17 @@ OZ_D void col_load_p(const ColArgs<T>& a, int k, long long i, T* p) {
 #ifndef OZ_COLLOC_CHUNK   /* consecutive steps per thread of the VJP kernel (each run recomputes the step before it for p_bar) */
 #define OZ_COLLOC_CHUNK 10
 #endif
+// resident blocks the residual kernel is compiled for: its live state is the S x D accumulators of c1 (lunar ascent, measured:
+// RK4 S D = 28 -> 3 blocks 0.180 ms / 4 blocks 0.188 ms; GL6 S D = 21 -> 0.146 / 0.134 ms)
+template <class R, int S>
+constexpr int colloc_res_blocks() {
+    return S * R::D <= 21 ? 4 : 3;
+}
 #ifndef OZ_MB_COLLOC
 #define OZ_MB_COLLOC 3
 #endif
 template <class R, typename T, int S>
-__global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_residual_kernel(const ColArgs<T> a) {
+__global__ void __launch_bounds__(128, (colloc_res_blocks<R, S>())) colloc_residual_kernel(const ColArgs<T> a) {
     using DM = Dims<R>;
     constexpr int D = DM::D;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -51,36 +57,45 @@ __global__ void __launch_bounds__(128, OZ_MB_COLLOC) colloc_residual_kernel(cons
     if (i >= a.N) return;
     const long long N = a.N;
     const Tableau<T>& tab = a.tab;
-    T th[DM::S1], plo[DM::P1], phi[DM::P1], ps[S][DM::P1], Y[S][D], F[S][D], yk[D], yk1[D];
+    // c1 / c2 are accumulated stage by stage: once F_j is known it is added to every c1_s (weight h a_sj) and to c2
+    // (weight h b_j), so only ONE stage's Y and F are live at a time instead of all S of them
+    T th[DM::S1], plo[DM::P1], phi[DM::P1], c1[S][D], c2[D];
 #pragma unroll
     for (int c = 0; c < DM::SP; ++c) th[c] = ld_in(a.th, c, N, i, a.th_shared);
     col_load_p<R>(a, k, i, plo);
     col_load_p<R>(a, k + 1, i, phi);
-    stage_params<R, T, S>(tab, plo, phi, ps);
     const T h = ld_in(a.h, k, N, i, a.h_shared);
 #pragma unroll
     for (int c = 0; c < D; ++c) {
-        yk[c] = (k == 0) ? __ldg(a.y0 + c * N + i) : __ldg(a.y + ((long long)(k - 1) * D + c) * N + i);
-        yk1[c] = __ldg(a.y + ((long long)k * D + c) * N + i);
+        const T yk = (k == 0) ? __ldg(a.y0 + c * N + i) : __ldg(a.y + ((long long)(k - 1) * D + c) * N + i);
+        c2[c] = yk - __ldg(a.y + ((long long)k * D + c) * N + i);
+#pragma unroll
+        for (int s = 0; s < S; ++s) c1[s][c] = yk;
     }
 #pragma unroll
-    for (int s = 0; s < S; ++s) {
+    for (int j = 0; j < S; ++j) {
+        T Yj[D], Fj[D], pj[DM::P1];
 #pragma unroll
-        for (int c = 0; c < D; ++c) Y[s][c] = __ldg(a.Y + (((long long)k * S + s) * D + c) * N + i);
-        R::f(Y[s], ps[s], th, F[s]);
+        for (int c = 0; c < DM::P; ++c) pj[c] = plo[c] + tab.C[j] * (phi[c] - plo[c]);
+#pragma unroll
+        for (int c = 0; c < D; ++c) {
+            Yj[c] = __ldg(a.Y + (((long long)k * S + j) * D + c) * N + i);
+            c1[j][c] -= Yj[c];
+        }
+        R::f(Yj, pj, th, Fj);
+#pragma unroll
+        for (int c = 0; c < D; ++c) {
+            const T hf = h * Fj[c];
+            c2[c] += tab.B[j] * hf;
+#pragma unroll
+            for (int s = 0; s < S; ++s) c1[s][c] += tab.a(s, j) * hf;
+        }
     }
 #pragma unroll
     for (int c = 0; c < D; ++c) {
-        T accb = T(0);
 #pragma unroll
-        for (int s = 0; s < S; ++s) {
-            accb += tab.B[s] * F[s][c];
-            T acca = T(0);
-#pragma unroll
-            for (int j = 0; j < S; ++j) acca += tab.a(s, j) * F[j][c];
-            a.c1[(((long long)k * S + s) * D + c) * N + i] = h * acca + yk[c] - Y[s][c];
-        }
-        a.c2[((long long)k * D + c) * N + i] = h * accb + yk[c] - yk1[c];
+        for (int s = 0; s < S; ++s) a.c1[(((long long)k * S + s) * D + c) * N + i] = c1[s][c];
+        a.c2[((long long)k * D + c) * N + i] = c2[c];
     }
 }
 
