@@ -42,6 +42,8 @@ WORKLOADS = {
     'lotka_volterra_rk4_picard_jacobi_adjoint_N1M_nt101': dict(kind='picard', rhs='lotka_volterra', method='RK4', N=1 << 20, nt=101, T=0.9, jacobi=True),
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32),
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024_fp32': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, fp32=True),
+    # the same solve with the whole history kept (approach TimeMarching, 8.2 GB): what the checkpoint recompute costs
+    'diffusion_reaction_rk4_tm_history_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=0),
     # the same grid cut into spatial slabs over the ranks (strong scaling: the 10^6 cells are shared out)
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024_sharded': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, sharded=True),
     'lunar_ascent_rk4_collocation_N16384_nt101': dict(kind='colloc', rhs='lunar_ascent', method='RK4', N=16384, nt=101, T=0.1),
@@ -355,7 +357,7 @@ class Runner:
         if self.kind == 'grid':
             nx = wl['nx']
             extra = dict(d_override=nx, rhs_cfg=(np.pi / nx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx))),
-                         num_inner=self.n // wl['nc'], store_history=False)
+                         num_inner=(self.n // wl['nc']) if wl.get('nc') else 0, store_history=not wl.get('nc'))
         if self.kind == 'picard':
             extra = dict(state_blocks=(0, 2) if wl.get('jacobi') else (0, 1, 2))
         self.spec = spec = engine.SolveSpec(
@@ -485,7 +487,7 @@ class Runner:
         P = self.spec.info['P']
         pN = 1 if self.p_shared else N
         if self.kind == 'grid':       # per cell-step: fwd 2w; replay 2w; adjoint step 3w  
-            return 2 * w * d * n, 5 * w * d * n
+            return 2 * w * d * n, (5 if self.wl.get('nc') else 3) * w * d * n
         if self.kind == 'coljac':
             s = self.spec.method.num_stages
             fwd = w * (2 * n * s * d * N + 2 * n * d * N + (n + 1) * P * pN)          # read Y, y, p; write c1, c2
@@ -536,7 +538,8 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
              'coljac': ('rhs_jac_kernel', 'colloc_residual_kernel')}[run.kind]
     traffic = {}
     try:
-        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(workload.replace('_sharded', ''), {})
+        traffic = json.load(open(os.path.join(ROOT, 'profiles', 'traffic.json'))).get(
+            workload.replace('_sharded', '').replace('rk4_tm_history', 'rk4_checkpoints'), {})
     except Exception:
         pass
 
@@ -550,13 +553,15 @@ def roofline_of(run, workload, fwd_s, adj_s, torch, dev, probe=True):
         if run.kind == 'grid':
             nx = run.shard.slab.n_ext if hasattr(run, 'shard') else run.d
             K, KR = run.engine.grid_fusion(nx)
-            n, ni = run.n, run.n // run.wl['nc']
+            n = run.n
+            ni = n // run.wl['nc'] if run.wl.get('nc') else n               # no checkpoints: one segment, nothing replayed
             nseg = n // ni
             up = lambda a, b: -(-a // b)
             if key == 'pde_step_kernel':
                 return v * nseg * up(ni, K)
             step = table.get('pde_step_kernel') or 0
-            return v * nseg * up(ni, KR) + step * nseg * up(ni - 1, K)       # reverse launches + the replayed forward ones
+            replay = step * nseg * up(ni - 1, K) if run.wl.get('nc') else 0
+            return v * nseg * up(ni, KR) + replay                            # reverse launches + the replayed forward ones
         if run.kind == 'picard' and key == 'picard_kernel':
             return v * run.wl['N'] / 131072.0
         return v
