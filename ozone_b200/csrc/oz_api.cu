@@ -70,6 +70,11 @@ static const oz_plugin_info* plugin_of(int rhs_id) {
     return &g_plugins[slot];
 }
 static bool known_rhs(int rhs_id) { return (rhs_id >= 0 && rhs_id < OZ_RHS_COUNT) || plugin_of(rhs_id) != nullptr; }
+// 0: one ODE per trajectory, 1: grid (only valid for a known rhs_id)
+static int rhs_kind(int rhs_id) {
+    if (const oz_plugin_info* pl = plugin_of(rhs_id)) return pl->kind;
+    return kInfo[rhs_id].kind;
+}
 static int plugin_rc(const oz_plugin_info* pl, int rc) {
     if (rc < 0 && pl->last_error) set_error("%s", pl->last_error());
     return rc;
@@ -126,7 +131,8 @@ int oz_register_rhs_plugin(const char* so_path) {
     describe(&info);
     OZ_REQUIRE(info.abi == OZ_PLUGIN_ABI, "plugin %s was built for plugin ABI %d, this library speaks %d", so_path, info.abi,
                OZ_PLUGIN_ABI);
-    OZ_REQUIRE(info.tm && info.picard && info.colloc && info.d >= 1, "plugin %s is incomplete", so_path);
+    OZ_REQUIRE(info.tm && info.picard && info.colloc && info.d >= 1 && (info.kind == 0 || info.kind == 1), "plugin %s is incomplete",
+               so_path);
     g_plugins[slot] = info;
     g_num_plugins.store(slot + 1, std::memory_order_release);
     return OZ_RHS_PLUGIN_BASE + slot;
@@ -135,7 +141,7 @@ int oz_register_rhs_plugin(const char* so_path) {
 int oz_rhs_info(int rhs_id, int* d, int* P, int* S, int* nprof, int* nfield, int* kind) {
     OZ_REQUIRE(known_rhs(rhs_id), "unknown rhs_id %d", rhs_id);
     RhsInfo plug;
-    if (const oz_plugin_info* pl = plugin_of(rhs_id)) plug = RhsInfo{pl->d, pl->P, pl->S, pl->nprof, pl->nfield, 0};
+    if (const oz_plugin_info* pl = plugin_of(rhs_id)) plug = RhsInfo{pl->d, pl->P, pl->S, pl->nprof, pl->nfield, pl->kind};
     const RhsInfo& r = plugin_of(rhs_id) ? plug : kInfo[rhs_id];
     if (d) *d = r.d;
     if (P) *P = r.P;
@@ -161,14 +167,14 @@ int oz_rhs_out_vjp(const oz_problem* pb, int64_t nodes, const void* y, const voi
     OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
     OZ_REQUIRE(nodes >= 0, "negative node count");
-    OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "output VJPs are defined for per-trajectory right-hand sides");
+    OZ_REQUIRE(rhs_kind(pb->rhs_id) == 0, "output VJPs are defined for per-trajectory right-hand sides");
     EvalArgs ev{nodes, y, p, nullptr, nullptr, nullptr, vprof, vfield, y_bar, p_bar, th_bar, 1, 0};
     return route(pb, TM_OUT_VJP, nullptr, &ev);
 }
 
 int oz_rhs_jac_pattern(int rhs_id, uint8_t* jp, uint8_t* jpp) {
     OZ_REQUIRE(known_rhs(rhs_id), "unknown rhs_id %d", rhs_id);
-    OZ_REQUIRE(plugin_of(rhs_id) || kInfo[rhs_id].kind == 0, "Jacobian patterns are defined for per-trajectory right-hand sides");
+    OZ_REQUIRE(rhs_kind(rhs_id) == 0, "Jacobian patterns are defined for per-trajectory right-hand sides");
     oz_problem pb;
     memset(&pb, 0, sizeof(pb));
     pb.rhs_id = rhs_id;
@@ -182,7 +188,7 @@ int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, int32_t
     OZ_REQUIRE(known_rhs(pb->rhs_id), "unknown rhs_id %d", pb->rhs_id);
     OZ_REQUIRE(pb->dtype == OZ_F64 || pb->dtype == OZ_F32, "unknown dtype %d", pb->dtype);
     OZ_REQUIRE(nodes >= 0 && blocks >= 0, "negative node / block count");
-    OZ_REQUIRE(plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0, "node Jacobians are defined for per-trajectory right-hand sides");
+    OZ_REQUIRE(rhs_kind(pb->rhs_id) == 0, "node Jacobians are defined for per-trajectory right-hand sides");
     OZ_REQUIRE(!(flags & OZ_JAC_STAGE_PARAMS) || (pb->num_stages >= 1 && pb->num_stages <= OZ_MAX_STAGES), "stage mode needs the tableau");
     EvalArgs ev{nodes, y, p, f, nullptr, nullptr, nullptr, nullptr, Jy, Jp, nullptr, blocks, flags};
     return route(pb, TM_JAC_EVAL, nullptr, &ev);
@@ -190,9 +196,9 @@ int oz_rhs_jac_eval(const oz_problem* pb, int64_t nodes, int64_t blocks, int32_t
 
 size_t oz_tm_forward_workspace_bytes(const oz_problem* pb) {
     if (check_problem(pb)) return (size_t)-1;
-    if (plugin_of(pb->rhs_id) || kInfo[pb->rhs_id].kind == 0) return 0;
+    if (rhs_kind(pb->rhs_id) == 0) return 0;
     size_t bytes = 0;
-    if (pde_dispatch(pb, 100, &bytes, nullptr)) return (size_t)-1;
+    if (route(pb, 100, &bytes, nullptr)) return (size_t)-1;      // a grid right-hand side (built in or plugin): mode 100 = forward scratch
     return bytes;
 }
 

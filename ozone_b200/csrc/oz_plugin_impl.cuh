@@ -37,4 +37,5 @@ extern "C" __attribute__((visibility("default"))) void oz_plugin_describe(oz_plu
     out->picard = oz::picard_plugin;
     out->colloc = oz::colloc_plugin;
     out->last_error = []() -> const char* { return oz::g_plugin_err; };
+    out->kind = 0;
 }

@@ -43,7 +43,10 @@ class SolveSpec:
         if self.traced is not None:
             t = self.traced
             self.rhs_id = None          # resolved per (stages, implicit, dtype, approach) in make_problem
-            self.info = dict(d=t.D, P=t.P, S=t.S, nprof=len(t.prof_exprs), nfield=len(t.field_exprs), kind=0)
+            if t.kind == 'grid':           # trace_grid.TracedGridRHS: the cells come with the problem, coefficient fields as th
+                self.info = t.spec_info(self.d_override)
+            else:
+                self.info = dict(d=t.D, P=t.P, S=t.S, nprof=len(t.prof_exprs), nfield=len(t.field_exprs), kind=0)
         else:
             self.rhs_id = nat.RHS_IDS[self.rhs_name]
         if not self.info:

@@ -6,6 +6,7 @@ arguments (``ozone/integrators/integrator.py:14-34``), ``integrate()`` runs the 
 """
 from __future__ import annotations
 
+import numpy as np
 import torch
 
 from . import engine
@@ -107,8 +108,21 @@ class IntegratorBase(object):
         """Run the Python callback once on symbolic inputs (two nodes, so shapes are checked the way the
         reference checks them with num_nodes > 1) and turn it into a device functor (trace.py).  Malformed
         callbacks raise the reference's KeyError / ValueError / TypeError (ozone/func_wrapper.py:28-53)."""
-        from .trace import TracedRHS, _norm_shape
+        from .trace import TracedRHS, _norm_shape, MAX_STATE
         batched = bool(self.options.get('batched', False))
+        f = self.ode_func
+        st = self.states.states
+        if not batched and len(st) == 1:
+            # ONE state that is a long vector: a 1-D grid (pde_control.py:11-81), compiled into the fused stencil kernels
+            (name, s), = st.items()
+            shp = tuple(s.shape)
+            if len(shp) == 1 and shp[0] > MAX_STATE:
+                from .trace_grid import TracedGridRHS
+                for pn, dp in self.dynamic_parameters.d_params.items():
+                    if int(np.prod(tuple(dp.point_shape) or (1,))) != 1:
+                        raise ValueError(f'dynamic parameter \'{pn}\' of a grid right-hand side must be one scalar per time point, '
+                                         f'got point shape {tuple(dp.point_shape)}')
+                return TracedGridRHS(f.f, f.args, f.kwargs, name, shp[0], list(self.dynamic_parameters.d_params))
         N = 1
         state_shapes, param_shapes = {}, {}
         for n, s in self.states.states.items():

@@ -5,11 +5,13 @@ import numpy as np
 import torch
 
 from .trace import TVar, _arr
+from . import trace_grid as _grid
+from .trace_grid import GridVar
 
 
 def _unary(name, tfn):
     def fn(x):
-        if isinstance(x, TVar):
+        if isinstance(x, (TVar, GridVar)):
             return x.map(name)
         return tfn(torch.as_tensor(x))
     fn.__name__ = name
@@ -28,12 +30,21 @@ arctan = _unary('arctan', torch.atan)
 
 def sum(x, axes=None, axis=None):
     ax = axes if axes is not None else axis
+    if isinstance(x, GridVar):
+        return x.sum()
     if isinstance(x, TVar):
         return x.sum(axis=tuple(ax) if isinstance(ax, (list, tuple)) else ax)
     return torch.sum(x) if ax is None else torch.sum(x, dim=ax)
 
 
 def expand(x, shape, action=None):
+    tr = _grid.active_grid_tracer()
+    if tr is not None and not isinstance(x, GridVar) and int(np.prod(shape)) == tr.nx and tr.nx > 1:
+        # a scalar spread over the cells of a traced grid right-hand side
+        v = x.a.reshape(-1) if isinstance(x, TVar) else np.asarray(x, dtype=object).reshape(-1)
+        if v.size != 1:
+            raise ValueError('only scalars can be expanded over the grid')
+        return GridVar(tr, _grid.Expr.wrap(v[0]), shape)
     if isinstance(x, TVar):
         return x.expand(shape, action)
     if isinstance(x, torch.Tensor):
@@ -46,6 +57,8 @@ def reshape(x, shape):
 
 
 def concatenate(xs, axis=0):
+    if any(isinstance(x, GridVar) for x in xs):
+        return _grid.concatenate(xs, axis)
     if any(isinstance(x, TVar) for x in xs):
         return TVar(np.concatenate([_arr(x) for x in xs], axis=axis))
     return torch.cat(list(xs), dim=axis)

@@ -108,6 +108,10 @@ class Expr:
             return o
         if o.is_const(1.0):
             return self
+        if o.is_const():
+            self, o = o, self                     # constants first, so that nested constant factors fold
+        if self.is_const() and o.op == 'mul' and o.args[0].is_const():
+            return Expr.const(self.val * o.args[0].val) * o.args[1]
         return Expr('mul', (self, o))
 
     __rmul__ = lambda self, o: Expr.wrap(o).__mul__(self)

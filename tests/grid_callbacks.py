@@ -1,0 +1,109 @@
+"""Grid right-hand sides written as ordinary Python callbacks, for the traced-grid tests.
+
+``pde_control`` follows the reference's example line by line (ozone/paper_examples/pde_control/pde_control.py:11-81) with
+``csdl`` replaced by ``ozone_b200.ops``; ``advection_diffusion`` is a second system that exercises what the first does
+not: an asymmetric stencil (upwind advection), a variable diffusivity (per-cell neighbour weights), a per-cell source
+weight, a nonlinear reaction without an exponential and a field output with a per-cell weight.  Each comes with a numpy
+restatement in the oracle's conventions (oracle.rhs.Rhs, derivatives by complex step)."""
+import numpy as np
+
+from ozone_b200 import ops as csdl
+from oracle.rhs import Rhs
+
+
+def pde_control(ozone_vars, dx, nx, zero_bc, pi_bc, beta_t, beta_u, gamma):
+    beta_t_g = beta_t * (np.exp(-gamma))
+    heaviside_array = np.zeros((nx, 1))
+    heaviside_array[round(0.3 * nx):round(0.7 * nx)] = 1.0
+    x = ozone_vars.states['x']
+    u = ozone_vars.dynamic_parameters['u']
+    nn = ozone_vars.num_nodes
+    dx_dts = []
+    for node in range(nn):
+        x_vec = csdl.reshape(x[node, :], (nx, 1))
+        zeros = np.zeros((1, 1))
+        x_vec0 = csdl.concatenate((zeros, x_vec[:-1, :]))
+        x_vec1 = csdl.concatenate((x_vec[1:, :], zeros))
+        dxdz2_without_bc_new = x_vec0 + (-2.0) * x_vec + x_vec1
+        dxdz2_without_bc = dxdz2_without_bc_new / (dx ** 2)
+        dx_dz2 = csdl.reshape(dxdz2_without_bc, (1, nx))
+        exp_term = -gamma * 1 * ((1 + x_vec) ** (-1))
+        reaction_src_b4_reshape = beta_t * (np.exp(1) ** exp_term) + (-1 * beta_t_g)
+        reaction_src = csdl.reshape(reaction_src_b4_reshape, (1, nx))
+        t_sub_term = (-beta_u) * x_vec
+        control_input = csdl.reshape(u[node], (1,))
+        t_src_term = (csdl.expand(control_input, (nx, 1))) * (beta_u * heaviside_array)
+        transfer_src_b4_reshape = t_src_term + t_sub_term
+        transfer_src = csdl.reshape(transfer_src_b4_reshape, (1, nx))
+        dx_dts.append((dx_dz2 + reaction_src + transfer_src).reshape(1, -1))
+    if nn == 1:
+        ozone_vars.d_states['x'] = dx_dts[0]
+    else:
+        ozone_vars.d_states['x'] = csdl.concatenate(dx_dts)
+    dx = 1.0 / nx
+    xnn = x
+    unn = u
+    Jss = []
+    for n in range(nn):
+        x = csdl.reshape(xnn[n, :], (nx,))
+        u = csdl.reshape(unn[n, :], (1,))
+        x2 = x * 1 * x
+        u2 = u * 1 * u
+        x_term = (dx * 100) * csdl.sum(x2)
+        u_term = (dx * nx * 20) * (u2)
+        Jss.append((x_term + u_term).reshape(1, 1))
+    if nn == 1:
+        ozone_vars.field_outputs['J_space'] = Jss[0]
+    else:
+        ozone_vars.field_outputs['J_space'] = csdl.concatenate(Jss)
+
+
+def advection_fields(nx):
+    z = (np.arange(nx) + 0.5) / nx
+    return dict(diffusivity=0.6 + 0.4 * np.sin(2 * np.pi * z), source=np.exp(-40.0 * (z - 0.35) ** 2),
+                weight=1.0 + z * z)
+
+
+def advection_diffusion(ozone_vars, nx, dz, speed, rate):
+    """c' = D(z) (c[k-1] - 2 c[k] + c[k+1]) / dz^2 - speed (c[k] - c[k-1]) / dz + rate c (1 - c) + s(z) q(t)"""
+    fl = advection_fields(nx)
+    c = ozone_vars.states['c'][0, :]
+    q = ozone_vars.dynamic_parameters['q']
+    zero = np.zeros(1)
+    left = csdl.concatenate((zero, c[:-1]))
+    right = csdl.concatenate((c[1:], zero))
+    diffusion = fl['diffusivity'] * (left - 2.0 * c + right) / dz ** 2
+    advection = -speed * (c - left) / dz
+    reaction = rate * c * (1.0 - c)
+    source = csdl.expand(q[0], (nx,)) * fl['source']
+    ozone_vars.d_states['c'] = (diffusion + advection + reaction + source).reshape(1, nx)
+    ozone_vars.field_outputs['cost'] = (dz * csdl.sum(fl['weight'] * c ** 2) + 0.3 * q[0] * q[0] + 0.1 * q[0]).reshape(1, 1)
+
+
+class AdvectionDiffusionOracle(Rhs):
+    name = 'advection_diffusion'
+    P, S, NFIELD = 1, 0, 1
+
+    def __init__(self, nx, dz, speed, rate):
+        self.D = self.nx = nx
+        self.dz, self.speed, self.rate = dz, speed, rate
+        self.fl = advection_fields(nx)
+
+    def _col(self, a, like):
+        return a.reshape((self.nx,) + (1,) * (like.ndim - 1))
+
+    def f(self, y, p, th):
+        c, q = y, p[0]
+        left = np.zeros_like(c)
+        left[1:] = c[:-1]
+        right = np.zeros_like(c)
+        right[:-1] = c[1:]
+        D, s = self._col(self.fl['diffusivity'], c), self._col(self.fl['source'], c)
+        return (D * (left - 2.0 * c + right) / self.dz ** 2 - self.speed * (c - left) / self.dz
+                + self.rate * c * (1.0 - c) + s * q)
+
+    def out(self, y, p, th):
+        q = p[0]
+        J = self.dz * np.sum(self._col(self.fl['weight'], y) * y * y, axis=0) + 0.3 * q * q + 0.1 * q
+        shp = np.broadcast_shapes(y.shape[1:], q.shape)
+        return np.zeros((0,) + shp), np.broadcast_to(J, shp)[None]

@@ -1,0 +1,137 @@
+"""Grid right-hand sides given as Python callbacks (VERDICT "missing" item 4; SURVEY section 8 row f2, grid form): the
+callback is traced over a symbolic grid (ozone_b200/trace_grid.py), compiled into the fused stencil kernels and run
+through the drop-in API.  Checked against the hand-written device model of the same PDE and against the numpy oracle."""
+import numpy as np
+import pytest
+import torch
+
+import ozone_b200 as ozone
+from ozone_b200.approaches import TimeMarching, TimeMarchingCheckpoints
+from tests import grid_callbacks as G
+
+pytestmark = pytest.mark.gpu
+DEV = 'cuda'
+
+
+def var(value, requires_grad=True, dtype=np.float64):
+    return torch.tensor(np.asarray(value, dtype=dtype), device=DEV, requires_grad=requires_grad)
+
+
+def _solve_pde(function, nx, n, approach, u_np, **kw):
+    dx = np.pi / nx
+    dt = 0.4 * dx * dx
+    h_vec, x_0, u = var(np.ones(n) * dt), var(np.ones(nx) * 0.5), var(u_np)
+    prob = ozone.ODEProblem(ozone.methods.RK4(), approach, verbose=False)
+    prob.add_state('x', x_0, store_final=True, **kw)
+    prob.add_dynamic_parameter('u', u)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h_vec))
+    prob.set_function(function, dx=dx, nx=nx, zero_bc=0, pi_bc=0, beta_t=16.0, beta_u=2.0, gamma=2.0)
+    out = prob.solve()
+    J = out.field_outputs['J_space'].sum() + 3.0 * (out.final_states['x'] ** 2).sum()
+    return out, J, torch.autograd.grad(J, [u, h_vec, x_0]), prob
+
+
+@pytest.mark.parametrize('approach', ['history', 'checkpoints'])
+def test_the_reference_pde_callback_runs_like_the_built_in_model(approach):
+    # pde_control.py:84-143 scaled down; the callback is the reference's own text with csdl -> ozone_b200.ops
+    nx, n = 1500, 36
+    u_np = np.random.default_rng(3).uniform(-0.6, 0.0, size=n + 1)
+    mk = (lambda: TimeMarching()) if approach == 'history' else (lambda: TimeMarchingCheckpoints())
+    kw = dict(store_history=True) if approach == 'history' else {}
+    out_t, J_t, g_t, prob = _solve_pde(G.pde_control, nx, n, mk(), u_np, **kw)
+    out_b, J_b, g_b, _ = _solve_pde(ozone.rhs.diffusion_reaction, nx, n, mk(), u_np, **kw)
+    assert prob.integrator.rhs.kind == 'grid' and prob.integrator.spec.info['kind'] == 1
+    assert torch.allclose(out_t.final_states['x'], out_b.final_states['x'], rtol=1e-12, atol=1e-14)
+    if approach == 'history':
+        assert torch.allclose(out_t.states['x'], out_b.states['x'], rtol=1e-12, atol=1e-14)
+    assert float(J_t) == pytest.approx(float(J_b), rel=1e-12)
+    for a, b in zip(g_t, g_b):
+        assert float((a - b).abs().max()) <= 1e-10 * float(b.abs().max())
+
+
+@pytest.mark.parametrize('method,nx,n', [('RK4', 150, 12), ('ForwardEuler', 90, 7), ('RK6', 700, 9), ('RK4', 2300, 10)])
+def test_advection_diffusion_callback_matches_the_oracle_states_and_gradients(method, nx, n):
+    from oracle import integrators as I, adjoint as Adj
+    dz, speed, rate = 1.0 / nx, 0.7, 1.3
+    rng = np.random.default_rng(nx)
+    c0_np = 0.3 + 0.2 * np.sin(3 * np.pi * (np.arange(nx) + 0.5) / nx) ** 2
+    q_np = rng.uniform(0.0, 2.0, size=n + 1)
+    h_np = 0.2 * dz * dz * rng.uniform(0.8, 1.2, size=n)
+    c0, q, h = var(c0_np), var(q_np), var(h_np)
+    prob = ozone.ODEProblem(getattr(ozone.methods, method)(), TimeMarching(), verbose=False)
+    prob.add_state('c', c0, store_history=True, store_final=True)
+    prob.add_dynamic_parameter('q', q)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(G.advection_diffusion, nx=nx, dz=dz, speed=speed, rate=rate)
+    out = prob.solve()
+
+    rhs = G.AdvectionDiffusionOracle(nx, dz, speed, rate)
+    ref = I.time_marching(rhs, method, c0_np[:, None], h_np, q_np.reshape(n + 1, 1, 1), None)
+    hist = out.states['c'].detach().cpu().numpy()
+    assert np.abs(hist - ref['history'][:, :, 0]).max() <= 1e-12 * np.abs(ref['history']).max()
+    assert float(out.field_outputs['cost'].sum()) == pytest.approx(float(ref['field'][0, 0]), rel=1e-12)
+
+    rngb = np.random.default_rng(7)
+    hb, fb = rngb.standard_normal(hist.shape), rngb.standard_normal(nx)
+    loss = (out.states['c'] * var(hb, False)).sum() + (out.final_states['c'] * var(fb, False)).sum() + 0.7 * out.field_outputs['cost'].sum()
+    g_q, g_h, g_c0 = torch.autograd.grad(loss, [q, h, c0])
+    g = Adj.tm_adjoint(rhs, method, c0_np[:, None], h_np, q_np.reshape(n + 1, 1, 1), None, history=ref['history'],
+                       hist_bar=hb[:, :, None], final_bar=fb[:, None], field_bar=np.full((1, 1), 0.7))
+    for mine, theirs in ((g_q, g['p']), (g_h, g['h']), (g_c0, g['y0'])):
+        assert np.abs(mine.cpu().numpy().ravel() - np.ravel(theirs)).max() <= 1e-10 * np.abs(theirs).max()
+
+
+def test_traced_grid_with_checkpoints_and_in_single_precision():
+    nx, n = 1200, 16
+    dz = 1.0 / nx
+    rng = np.random.default_rng(5)
+    c0_np = 0.3 + 0.2 * np.cos(2 * np.pi * np.arange(nx) / nx) ** 2
+    q_np, h_np = rng.uniform(0.0, 2.0, size=n + 1), np.full(n, 0.2 * dz * dz)
+    res = {}
+    for key, dtype, approach in (('f64', np.float64, TimeMarching()), ('ckpt', np.float64, TimeMarchingCheckpoints(num_checkpoints=4)),
+                                 ('f32', np.float32, TimeMarching())):
+        c0, q, h = var(c0_np, dtype=dtype), var(q_np, dtype=dtype), var(h_np, dtype=dtype)
+        prob = ozone.ODEProblem(ozone.methods.RK4(), approach, verbose=False)
+        prob.add_state('c', c0, store_final=True)
+        prob.add_dynamic_parameter('q', q)
+        prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+        prob.set_function(G.advection_diffusion, nx=nx, dz=dz, speed=0.7, rate=1.3)
+        out = prob.solve()
+        loss = out.field_outputs['cost'].sum() + (out.final_states['c'] ** 2).sum()
+        res[key] = [float(loss)] + [t.double().cpu().numpy() for t in torch.autograd.grad(loss, [q, c0, h])]
+    for a, b in zip(res['ckpt'], res['f64']):
+        assert np.abs(np.asarray(a) - np.asarray(b)).max() <= 1e-12 * np.abs(b).max()
+    for a, b in zip(res['f32'], res['f64']):
+        assert np.abs(np.asarray(a) - np.asarray(b)).max() <= 2e-4 * np.abs(b).max()
+
+
+def test_grid_callback_without_parameters_or_outputs_and_refusals_at_run_time():
+    nx, n = 400, 8
+    dz = 1.0 / nx
+
+    def heat(ov, kappa):
+        x = ov.states['T'][0, :]
+        z = np.zeros(1)
+        ov.d_states['T'] = (kappa * (ozone.ops.concatenate((z, x[:-1])) - 2.0 * x + ozone.ops.concatenate((x[1:], z)))).reshape(1, -1)
+    T0_np = np.sin(np.pi * (np.arange(nx) + 0.5) / nx)
+    T0, h = var(T0_np), var(np.full(n, 0.2 * dz * dz))
+    prob = ozone.ODEProblem(ozone.methods.RK4(), TimeMarching(), verbose=False)
+    prob.add_state('T', T0, store_final=True)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(heat, 1.0 / dz ** 2)
+    out = prob.solve()
+    # linear problem: final = R(hL)^n T0 with the RK4 stability polynomial of the second-difference matrix
+    L = (np.diag(-2.0 * np.ones(nx)) + np.diag(np.ones(nx - 1), 1) + np.diag(np.ones(nx - 1), -1)) / dz ** 2
+    Z = 0.2 * dz * dz * L
+    R = np.eye(nx) + Z + Z @ Z / 2 + Z @ Z @ Z / 6 + Z @ Z @ Z @ Z / 24
+    want = np.linalg.matrix_power(R, n) @ T0_np
+    assert np.abs(out.final_states['T'].detach().cpu().numpy() - want).max() < 1e-13
+    g, = torch.autograd.grad(out.final_states['T'].sum(), [T0])
+    assert np.abs(g.cpu().numpy() - np.linalg.matrix_power(R, n).T @ np.ones(nx)).max() < 1e-12
+
+    prob = ozone.ODEProblem(ozone.methods.ImplicitMidpoint(), TimeMarching(), verbose=False)
+    prob.add_state('T', T0, store_final=True)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(heat, 1.0 / dz ** 2)
+    with pytest.raises(ValueError, match='explicit methods only'):
+        prob.solve()

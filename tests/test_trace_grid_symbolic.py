@@ -1,0 +1,159 @@
+"""trace_grid.py without a GPU: what a grid callback is turned into, and what is refused (with the reason)."""
+import numpy as np
+import pytest
+import torch
+
+from ozone_b200 import ops
+from ozone_b200.trace import diff, leaf
+from ozone_b200.trace_grid import TracedGridRHS, leaves_of
+from tests import grid_callbacks as G
+
+
+def _evaluate(e, env):
+    """numeric value of an expression DAG; env maps (op, idx) of the leaves to numbers"""
+    import math
+    memo = {}
+
+    def go(x):
+        if id(x) in memo:
+            return memo[id(x)]
+        if x.op == 'const':
+            r = x.val
+        elif not x.args:
+            r = env[(x.op, x.idx)]
+        else:
+            a = [go(y) for y in x.args]
+            r = {'add': lambda: a[0] + a[1], 'sub': lambda: a[0] - a[1], 'mul': lambda: a[0] * a[1], 'div': lambda: a[0] / a[1],
+                 'neg': lambda: -a[0], 'powc': lambda: a[0] ** x.val, 'exp': lambda: math.exp(a[0])}[x.op]()
+        memo[id(x)] = r
+        return r
+    return go(e)
+
+
+def test_the_reference_pde_callback_becomes_a_three_point_model_with_one_coefficient_field():
+    nx = 120
+    dx = np.pi / nx
+    t = TracedGridRHS(G.pde_control, (), dict(dx=dx, nx=nx, zero_bc=0, pi_bc=0, beta_t=16.0, beta_u=2.0, gamma=2.0), 'x', nx, ['u'])
+    assert {(l.op, l.idx) for l in leaves_of(t.f)} == {('gx', -1), ('gx', 0), ('gx', 1), ('gc', 0), ('p', 0)}
+    tab = t.tracer.coefficient_table()
+    H = np.zeros(nx)
+    H[round(0.3 * nx):round(0.7 * nx)] = 2.0                       # beta_u * heaviside (pde_control.py:15-16,50)
+    assert tab.shape == (1, nx) and np.array_equal(tab[0], H)
+    # the recorded expression IS the reference formula (:27-55), cell by cell
+    rng = np.random.default_rng(0)
+    for _ in range(5):
+        xl, x, xr, c, u = rng.uniform(0.1, 1.0, 5)
+        env = {('gx', -1): xl, ('gx', 0): x, ('gx', 1): xr, ('gc', 0): c, ('p', 0): u}
+        want = (xl - 2 * x + xr) / dx ** 2 + 16.0 * np.exp(-2.0 / (1 + x)) - 16.0 * np.exp(-2.0) + u * c - 2.0 * x
+        assert _evaluate(t.f, env) == pytest.approx(want, rel=1e-14)
+        assert _evaluate(t.dg, env) == pytest.approx(-2 / dx ** 2 + 16.0 * np.exp(-2.0 / (1 + x)) * 2.0 / (1 + x) ** 2 - 2.0, rel=1e-13)
+        assert _evaluate(t.q, env) == pytest.approx(100.0 / nx * x * x, rel=1e-14)       # the rebound dx = 1 / nx (:62-76)
+        assert _evaluate(t.r, env) == pytest.approx(20.0 * u * u, rel=1e-14)
+    assert t.wr_of_left.is_const() and t.wr_of_left.val == pytest.approx(1 / dx ** 2)
+    assert t.spec_info(nx) == dict(d=nx, P=1, S=nx, nprof=0, nfield=1, kind=1)
+    src = t.cuda_source()
+    assert 'pde_exp(' in src and 'struct GridTraced' in src and 'NCOEF = 1' in src
+
+
+def test_neighbour_weights_that_vary_from_cell_to_cell_are_shifted_for_the_transposed_stencil():
+    nx = 64
+    t = TracedGridRHS(G.advection_diffusion, (), dict(nx=nx, dz=1.0 / nx, speed=0.7, rate=1.3), 'c', nx, ['q'])
+    fl = G.advection_fields(nx)
+    tr = t.tracer
+    tab = tr.coefficient_table()
+    # (J^T G)_k needs the right-neighbour weight of cell k-1 and the left-neighbour weight of cell k+1: D shifted both ways
+    shifts = {sh for base, sh in tr.coefs if np.array_equal(tr.bases[base], fl['diffusivity'])}
+    assert shifts == {-1, 0, 1}
+    for q, (base, sh) in enumerate(tr.coefs):
+        want = np.zeros(nx)
+        src = tr.bases[base]
+        for k in range(nx):
+            if 0 <= k + sh < nx:
+                want[k] = src[k + sh]
+        assert np.array_equal(tab[q], want)
+
+
+def _trace(f, nx=50, params=('u',)):
+    return TracedGridRHS(f, (), {}, 'x', nx, list(params))
+
+
+def test_what_the_stencil_kernels_cannot_express_is_refused_with_the_reason():
+    z1 = np.zeros(1)
+
+    def five_point(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = (ops.concatenate((np.zeros(2), x[:-2])) + ops.concatenate((x[2:], np.zeros(2))) - 2.0 * x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='three-point stencil'):
+        _trace(five_point)
+
+    def nonlinear_neighbour(ov):
+        x = ov.states['x'][0, :]
+        left = ops.concatenate((z1, x[:-1]))
+        ov.d_states['x'] = (left * left - x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='neighbour cells must enter linearly'):
+        _trace(nonlinear_neighbour)
+
+    def shifted_nonlinear(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = ops.concatenate((z1, ops.exp(x)[:-1])).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='ghost cells'):
+        _trace(shifted_nonlinear)
+
+    def wrong_side(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = ops.concatenate((z1, x[1:])).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='ghost cells'):
+        _trace(wrong_side)
+
+    def nonzero_boundary(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = (ops.concatenate((np.ones(1), x[:-1])) - x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='only zeros'):
+        _trace(nonzero_boundary)
+
+    def single_cell(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = (x * x[3]).reshape(1, -1)
+    with pytest.raises(TypeError, match='single cells'):
+        _trace(single_cell)
+
+    def parameter_squared(ov):
+        x = ov.states['x'][0, :]
+        u = ov.dynamic_parameters['u']
+        ov.d_states['x'] = (ops.expand(u[0] * u[0], (50,)) - x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='parameter must enter'):
+        _trace(parameter_squared)
+
+    def captured_tensor(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = (x * torch.ones(50)).reshape(1, -1)
+    with pytest.raises(TypeError, match='tensors'):
+        _trace(captured_tensor)
+
+    def with_profile(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = (-x).reshape(1, -1)
+        ov.profile_outputs['x2'] = (x * x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='profile outputs'):
+        _trace(with_profile)
+
+    def missing_derivative(ov):
+        pass
+    with pytest.raises(KeyError):                         # the reference's own check (func_wrapper.py:28-53)
+        _trace(missing_derivative)
+
+    with pytest.raises(NotImplementedError, match='at most one'):
+        _trace(lambda ov: None, params=('u', 'v'))
+
+
+def test_generated_grid_model_compiles_and_registers_without_a_gpu():
+    from ozone_b200 import _native as nat
+    nx = 80
+    t = TracedGridRHS(G.advection_diffusion, (), dict(nx=nx, dz=1.0 / nx, speed=0.7, rate=1.3), 'c', nx, ['q'])
+    rid = t.plugin_id(4, False, True, 0)
+    assert rid >= 1000
+    info = nat.rhs_info(rid)
+    assert info['kind'] == 1 and info['P'] == 1 and info['nfield'] == 1 and info['S'] == len(t.tracer.coefs)
+    assert t.plugin_id(4, False, True, 0) == rid                       # cached per (stages, dtype)
+    with pytest.raises(ValueError, match='explicit methods only'):
+        t.plugin_id(2, True, True, 0)
