@@ -43,6 +43,8 @@ WORKLOADS = {
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32),
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024_fp32': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, fp32=True),
     # the same solve with the whole history kept (approach TimeMarching, 8.2 GB): what the checkpoint recompute costs
+    # the same PDE given as a Python callback written like the reference's (pde_control.py:11-81) and compiled by trace_grid.py
+    'diffusion_reaction_rk4_checkpoints_nx1M_n1024_traced': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, traced=True),
     'diffusion_reaction_rk4_tm_history_nx1M_n1024': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=0),
     # the same grid cut into spatial slabs over the ranks (strong scaling: the 10^6 cells are shared out)
     'diffusion_reaction_rk4_checkpoints_nx1M_n1024_sharded': dict(kind='grid', rhs='diffusion_reaction', method='RK4', N=1, nt=1025, nx=1000000, nc=32, sharded=True),
@@ -75,6 +77,22 @@ def workload_config(name, wl, world, newton_tol):
 
 ASCENT_IC = np.array([0.061663494666509, 0.055249439788994, -1.004110522066614, -0.465976472038572,
                       -0.416909510597800, -0.084973690970470, 11846.599614336959 / 15103.])
+
+
+def pde_control_callback(ozone_vars, dx, nx, beta_t, beta_u, gamma):
+    """The reference's PDE right-hand side as a user would write it against ozone_b200.ops (pde_control.py:11-81)."""
+    from ozone_b200 import ops
+    heaviside = np.zeros((nx, 1))
+    heaviside[round(0.3 * nx):round(0.7 * nx)] = 1.0
+    x = ops.reshape(ozone_vars.states['x'][0, :], (nx, 1))
+    u = ozone_vars.dynamic_parameters['u']
+    zeros = np.zeros((1, 1))
+    lap = (ops.concatenate((zeros, x[:-1, :])) + (-2.0) * x + ops.concatenate((x[1:, :], zeros))) / dx ** 2
+    reaction = beta_t * (np.exp(1) ** (-gamma * ((1 + x) ** (-1)))) + (-1 * beta_t * np.exp(-gamma))
+    transfer = ops.expand(ops.reshape(u[0], (1,)), (nx, 1)) * (beta_u * heaviside) + (-beta_u) * x
+    ozone_vars.d_states['x'] = (lap + reaction + transfer).reshape(1, -1)
+    xs, us = ops.reshape(x, (nx,)), ops.reshape(u[0, :], (1,))
+    ozone_vars.field_outputs['J_space'] = ((100.0 / nx) * ops.sum(xs * xs) + 20.0 * (us * us)).reshape(1, 1)
 
 
 def synth_inputs(wl, N, seed):
@@ -360,9 +378,17 @@ class Runner:
                          num_inner=(self.n // wl['nc']) if wl.get('nc') else 0, store_history=not wl.get('nc'))
         if self.kind == 'picard':
             extra = dict(state_blocks=(0, 2) if wl.get('jacobi') else (0, 1, 2))
+        traced = None
+        if wl.get('traced'):      # the callback goes through the symbolic grid tracer; its coefficient field travels as th
+            from ozone_b200.trace_grid import TracedGridRHS
+            nx = wl['nx']
+            traced = TracedGridRHS(pde_control_callback, (), dict(dx=np.pi / nx, nx=nx, beta_t=16.0, beta_u=2.0, gamma=2.0), 'x', nx, ['u'])
+            extra.pop('rhs_cfg')
+            case['th'] = traced.tracer.coefficient_table().reshape(-1)
         self.spec = spec = engine.SolveSpec(
-            rhs_name=wl['rhs'], method=get_integration_method(wl['method']), N=N, n=self.n, dtype=self.dtype,
-            h_shared=True, p_shared=self.p_shared, th_shared=False, newton_tol=args.newton_tol,
+            rhs_name='traced' if traced is not None else wl['rhs'], traced=traced, method=get_integration_method(wl['method']),
+            N=N, n=self.n, dtype=self.dtype,
+            h_shared=True, p_shared=self.p_shared, th_shared=traced is not None, newton_tol=args.newton_tol,
             **({'store_history': True} if self.kind != 'grid' else {}), **extra)
         self.d = spec.d
         self.units = N * self.d * self.n
