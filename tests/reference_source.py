@@ -19,6 +19,7 @@ RHS_SOURCES = {   # problem -> (file under REFERENCE, function name)
     'van_der_pol': ('ozone/paper_examples/van_der_pol/main_model.py', 'ode_func'),
     'lunar_ascent': ('ozone/paper_examples/ascent_system/main_model.py', 'ode_func'),
     'lotka_volterra': ('examples/simple_examples/lotka_volterra.py', 'ode_function'),
+    'pde_control': ('ozone/paper_examples/pde_control/pde_control.py', 'ode_function'),
 }
 
 
@@ -49,8 +50,9 @@ def reference_glms():
                 del sys.modules[k]
 
 
-def reference_callback(problem):
-    """The reference's right-hand side callback for `problem`, compiled from its own source text."""
+def reference_callback(problem, namespace=None):
+    """The reference's right-hand side callback for `problem`, compiled from its own source text.  `namespace`: names the
+    function body expects from its module (``csdl`` for the callbacks that call csdl functions)."""
     import numpy as np
     path, name = RHS_SOURCES[problem]
     tree = ast.parse(open(os.path.join(REFERENCE, path)).read())
@@ -59,5 +61,6 @@ def reference_callback(problem):
         a.annotation = None               # ozone.ODEVars / csdl.Variable hints: names that need not exist here
     mod = ast.Module(body=[node], type_ignores=[])
     ns = {'np': np}
+    ns.update(namespace or {})
     exec(compile(ast.fix_missing_locations(mod), os.path.join(REFERENCE, path), 'exec'), ns)
     return ns[name]

@@ -6,7 +6,9 @@ The reference as a whole cannot run here (csdl_alpha is not installable), but tw
   * the right-hand side callbacks of the examples are ordinary Python functions of ``ozone_vars``: they are
     traced by ``ozone_b200.trace`` exactly like a user callback, and (a) the generated device functor must be
     identical to the one generated from the re-typed copy the GPU tests run (``tests/reference_callbacks.py``),
-    (b) their values and Jacobians must equal the oracle's restatement (``oracle/rhs.py``) at random points.
+    (b) their values and Jacobians must equal the oracle's restatement (``oracle/rhs.py``) at random points;
+  * the PDE example's callback (``pde_control.py:11-81``, written with csdl functions over the whole grid) goes through
+    ``ozone_b200.trace_grid`` with ``csdl`` bound to ``ozone_b200.ops``: same two checks.
 ``/root/reference`` exists only in the build container: where it is absent the live comparisons are skipped and the
 committed fixture ``tests/golden/reference_tableaux.json`` (written by ``tools/make_reference_goldens.py`` from the
 reference's module) carries the tableau pin.
@@ -109,3 +111,46 @@ def test_oracle_right_hand_sides_equal_the_traced_reference_callbacks(problem):
             prof, fld = orc.out(Y, Pm, Th)
             assert np.allclose(np.asarray(prof)[:, 0], [evaluate(e, env) for e in t.prof_exprs], rtol=1e-14)
             assert np.allclose(np.asarray(fld)[:, 0], [evaluate(e, env) for e in t.field_exprs], rtol=1e-14)
+
+
+# ---------------------------------------------------------------- the grid callback (pde_control.py:11-81)
+PDE_KW = dict(zero_bc=0, pi_bc=0, beta_t=16.0, beta_u=2.0, gamma=2.0)
+
+
+def _trace_grid(f, nx):
+    from ozone_b200.trace_grid import TracedGridRHS
+    return TracedGridRHS(f, (), dict(dx=np.pi / nx, nx=nx, **PDE_KW), 'x', nx, ['u'])
+
+
+@needs_reference
+def test_reference_pde_callback_and_its_test_copy_generate_the_same_grid_model():
+    from ozone_b200 import ops
+    from tests import grid_callbacks as G
+    nx = 90
+    ref = _trace_grid(RS.reference_callback('pde_control', {'csdl': ops}), nx)
+    ours = _trace_grid(G.pde_control, nx)
+    assert ref.cuda_source() == ours.cuda_source()
+    assert np.array_equal(ref.tracer.coefficient_table(), ours.tracer.coefficient_table())
+
+
+@needs_reference
+def test_oracle_pde_equals_the_traced_reference_callback_cell_by_cell():
+    from ozone_b200 import ops
+    nx = 40
+    t = _trace_grid(RS.reference_callback('pde_control', {'csdl': ops}), nx)
+    orc = oracle_rhs.DiffusionReaction(nx)
+    tab = t.tracer.coefficient_table()
+    rng = np.random.default_rng(11)
+    for _ in range(3):
+        x, u = rng.uniform(0.1, 1.0, size=nx), float(rng.uniform(-0.6, 0.0))
+        f_or = orc.f(x[:, None], np.array([[u]]), None)[:, 0]
+        J_or = float(orc.out(x[:, None], np.array([[u]]), None)[1][0, 0])
+        xe = np.concatenate(([0.0], x, [0.0]))                     # zero ghost cells (:32-35)
+        f_tr, q_sum = np.empty(nx), 0.0
+        for k in range(nx):
+            env = {('gx', -1): xe[k], ('gx', 0): xe[k + 1], ('gx', 1): xe[k + 2], ('p', 0): u}
+            env.update({('gc', q): tab[q, k] for q in range(tab.shape[0])})
+            f_tr[k] = evaluate(t.f, env)
+            q_sum += evaluate(t.q, env)
+        assert np.allclose(f_tr, f_or, rtol=1e-13, atol=1e-12)
+        assert q_sum + evaluate(t.r, {('p', 0): u}) == pytest.approx(J_or, rel=1e-13)
