@@ -8,7 +8,7 @@ its "make the state bigger" idiom becomes on an 8-GPU box.
    batch-SHARED inputs (step sizes, shared parameters) are sums over trajectories, so they -- and
    nothing else -- are all-reduced (a few hundred scalars).
 
-2. Spatial slabs of the diffusion-reaction grid (config C3): each rank owns a contiguous slab of
+2. Spatial slabs of a grid right-hand side (config C3: the diffusion-reaction system; a traced grid callback works the same): each rank owns a contiguous slab of
    cells and carries a halo on either side.  An RK step with s stages moves information s cells
    (forward) / 2 s cells (reverse step, which re-derives the stages and then runs the transposed
    stage chain), so instead of exchanging one cell per stage the ranks exchange a halo of
@@ -130,7 +130,9 @@ class GridShard:
     the gloo path on CPU tensors) the exchange is a batched isend / irecv per segment."""
 
     def __init__(self, method, nx, n, num_inner, rank, world, y0_global, h, u, rhs_cfg, dtype=torch.float64,
-                 device='cuda', channel=None):
+                 device='cuda', channel=None, traced=None):
+        """traced: a trace_grid.TracedGridRHS instead of the built-in model (rhs_cfg is then unused); its coefficient
+        fields are indexed by the GLOBAL cell, so every rank keeps the whole table."""
         import ctypes as C
         if n % num_inner:
             raise ValueError(f'Number of timesteps ({n}) must be divisible by the segment length {num_inner}')
@@ -140,8 +142,11 @@ class GridShard:
         self.dtype, self.device = dtype, torch.device(device)
         self.h = h.to(self.device, dtype).contiguous()
         self.u = u.to(self.device, dtype).reshape(n + 1, 1).contiguous()
-        self.rhs_cfg = tuple(rhs_cfg)
+        self.rhs_cfg = tuple(rhs_cfg or ())
         self.channel = channel
+        self.traced, self.coef = traced, None
+        if traced is not None and traced.tracer.coefs:
+            self.coef = torch.from_numpy(traced.tracer.coefficient_table().reshape(-1)).to(self.device, dtype).contiguous()
         ne, ni, nseg = sl.n_ext, num_inner, self.nseg
         new = lambda *shape: torch.zeros(shape, dtype=dtype, device=self.device)
         self.ckpts = new(nseg + 1, ne, 1)
@@ -158,6 +163,8 @@ class GridShard:
             for adjoint in (False, True):
                 pb = engine.make_problem(self._spec(seg, adjoint))
                 pb.y0, pb.h, pb.p = self.ckpts[seg].data_ptr(), self.h[k0:].data_ptr(), self.u[k0:].data_ptr()
+                if self.coef is not None:
+                    pb.th, pb.th_shared = self.coef.data_ptr(), 1
                 if adjoint:
                     pb.ckpt = self.ckpts[seg].data_ptr()                 # rows seg, seg + 1: the segment's two checkpoints
                     pb.final_bar, pb.y0_bar = None, None                 # set per call (ping-pong)
@@ -185,9 +192,10 @@ class GridShard:
             flags |= nat.GRID_SKIP_IC_FIELD
         if adjoint and seg < self.nseg - 1:
             flags |= nat.GRID_SKIP_TERMINAL_FIELD
-        return engine.SolveSpec(rhs_name='diffusion_reaction', method=self.method, N=1, n=self.ni, dtype=self.dtype,
+        return engine.SolveSpec(rhs_name='traced' if self.traced is not None else 'diffusion_reaction', traced=self.traced,
+                                method=self.method, N=1, n=self.ni, dtype=self.dtype,
                                 h_shared=True, p_shared=True, th_shared=True, num_inner=self.ni, store_history=False,
-                                d_override=sl.n_ext, rhs_cfg=self.rhs_cfg,
+                                d_override=sl.n_ext, rhs_cfg=() if self.traced is not None else self.rhs_cfg,
                                 grid_slab=(sl.ext_lo, self.nx, a, b, flags))
 
     # ---- halo exchange of an extended-slab vector (after a segment: owned cells exact, halo zones stale)
@@ -281,14 +289,14 @@ def make_channel(method, nx, num_inner, dtype, device, group=None):
 
 
 def solve_grid_sharded(method, nx, n, num_inner, y0_global, h, u, rhs_cfg, field_bar=1.0, dtype=torch.float64,
-                       device=None, group=None, peer_halos=True):
+                       device=None, group=None, peer_halos=True, traced=None):
     """Distributed driver (call from every rank): forward + reverse sweep of the diffusion-reaction grid
     cut into slabs.  Returns dict(field, y0_bar_owned, own_range, h_bar, u_bar, final_owned)."""
     rank = dist.get_rank(group) if dist.is_initialized() else 0
     world = dist.get_world_size(group) if dist.is_initialized() else 1
     device = device or torch.device('cuda', torch.cuda.current_device())
     channel = make_channel(method, nx, num_inner, dtype, device, group) if peer_halos else None
-    sh = GridShard(method, nx, n, num_inner, rank, world, y0_global, h, u, rhs_cfg, dtype, device, channel=channel)
+    sh = GridShard(method, nx, n, num_inner, rank, world, y0_global, h, u, rhs_cfg, dtype, device, channel=channel, traced=traced)
     sh.run(group, field_bar)
     res = sh.results()
     if channel is not None:
@@ -302,7 +310,7 @@ def solve_grid_sharded(method, nx, n, num_inner, y0_global, h, u, rhs_cfg, field
 
 
 def solve_grid_emulated(method, nx, n, num_inner, world, y0_global, h, u, rhs_cfg, field_bar=1.0,
-                        dtype=torch.float64, device='cuda', peer_halos=True):
+                        dtype=torch.float64, device='cuda', peer_halos=True, traced=None):
     """The same algorithm with all ``world`` ranks emulated in ONE process on one GPU (their kernels run
     one after another).  With peer_halos the exchange goes through the oz_peer_* kernels over a LocalArena --
     every rank pushes, then every rank waits -- else it is a tensor copy.  Tests the slab logic without N GPUs."""
@@ -315,7 +323,8 @@ def solve_grid_emulated(method, nx, n, num_inner, world, y0_global, h, u, rhs_cf
             view = arena.view(r)
             view._cursor = 0
             channels[r] = peer.HaloChannel(view, halo, dtype)
-    shards = [GridShard(method, nx, n, num_inner, r, world, y0_global, h, u, rhs_cfg, dtype, device, channel=channels[r])
+    shards = [GridShard(method, nx, n, num_inner, r, world, y0_global, h, u, rhs_cfg, dtype, device, channel=channels[r],
+                        traced=traced)
               for r in range(world)]
 
     def swap(get):
