@@ -22,6 +22,7 @@ FAMILIES = {   # report name -> (workload, {kernel-name regex: key in traffic.js
     'lv32': ('lotka_volterra_rk4_tm_adjoint_N1M_nt101_fp32', {'tm_forward_kernel': 'tm_forward_kernel', 'tm_adjoint_kernel': 'tm_adjoint_kernel'}),
     'pde': ('diffusion_reaction_rk4_checkpoints_nx1M_n1024', {'pde_step_kernel': 'pde_step_kernel', 'pde_adjoint_step_kernel': 'pde_adjoint_step_kernel'}),
     'pde32': ('diffusion_reaction_rk4_checkpoints_nx1M_n1024_fp32', {'pde_step_kernel': 'pde_step_kernel', 'pde_adjoint_step_kernel': 'pde_adjoint_step_kernel'}),
+    'pdetr': ('diffusion_reaction_rk4_checkpoints_nx1M_n1024_traced', {'pde_step_kernel': 'pde_step_kernel', 'pde_adjoint_step_kernel': 'pde_adjoint_step_kernel'}),
     'colloc': ('lunar_ascent_rk4_collocation_N16384_nt101', {'colloc_residual_kernel': 'colloc_residual_kernel', 'colloc_vjp_kernel': 'colloc_vjp_kernel'}),
     'coljac': ('lunar_ascent_rk4_optimizer_eval_N16384_nt101', {'colloc_residual_kernel': 'colloc_residual_kernel', 'rhs_jac_kernel': 'rhs_jac_kernel'}),
     'picard': ('lotka_volterra_rk4_picard_adjoint_N1M_nt101', {'picard_kernel': 'picard_kernel'}),
