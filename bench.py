@@ -72,7 +72,7 @@ def workload_config(name, wl, world, newton_tol):
         par = f'trajectory-batch x{world}'
     return {'workload': name, 'rhs': wl['rhs'], 'method': wl['method'], 'approach': wl['kind'],
             'trajectories_per_gpu': wl['N'], 'num_times': wl['nt'], 'state_size': d, 'newton_tol': newton_tol,
-            'l2': 'GPU arm: flushed (256 MiB write) between timed steps', 'parallelism': par}
+            'l2': 'GPU arm: flushed (256 MiB write) between timed steps; e2e with several solves in flight: every step\'s inputs arrive over PCIe', 'parallelism': par}
 
 
 ASCENT_IC = np.array([0.061663494666509, 0.055249439788994, -1.004110522066614, -0.465976472038572,
@@ -419,21 +419,30 @@ class Runner:
             fr = [float(x) for x in args.e2e_fractions.split(',')] if args.e2e_fractions else None
             self.pipe = engine.PipelinedTmSolve(spec, slices=args.e2e_slices, device=dev, grads=want, cotangents=cot,
                                                 upload=self.e2e_inputs, fractions=fr)
-            self.pipe.set_host_inputs(**self.host)
-            if args.world > 1:
-                import torch.distributed as dist
-                self.pipe.reduce_shared = dist.all_reduce
-            for pl in self.pipe.plans:
-                pl.final_bar.copy_(plan.final_bar[:, :pl.spec.N])
+            # steps of the end-to-end leg are independent solves of host-resident batches: `depth` of them are in flight, each with
+            # its own device + pinned buffers and streams, so that step k + 1 uploads while step k computes and downloads
+            depth = max(1, int(getattr(args, 'e2e_depth', 1)))
+            self.pipes = [self.pipe] + [engine.PipelinedTmSolve(spec, slices=args.e2e_slices, device=dev, grads=want, cotangents=cot,
+                                                                upload=self.e2e_inputs, fractions=fr) for _ in range(depth - 1)]
+            self.pipe_streams = [torch.cuda.Stream(device=dev) for _ in self.pipes]
+            for pipe in self.pipes:
+                pipe.set_host_inputs(**self.host)
+                if args.world > 1:
+                    import torch.distributed as dist
+                    pipe.reduce_shared = dist.all_reduce
+                for pl in pipe.plans:
+                    pl.final_bar.copy_(plan.final_bar[:, :pl.spec.N])
             self.h2d, self.d2h = self.pipe.bytes_per_run()
             self.e2e_launches = self.pipe.launches
             self.e2e_graph = False
             if not args.no_e2e_graph:
                 try:                       # replay the slice pipeline as one CUDA graph (host enqueue cost off the path)
-                    self.pipe.capture()
+                    for pipe in self.pipes:
+                        pipe.capture()
                     self.e2e_graph = True
                 except Exception as exc:   # noqa: BLE001 -- fall back to eager enqueue, and say so in the bench line
-                    self.pipe.graph = None
+                    for pipe in self.pipes:
+                        pipe.graph = None
                     self.e2e_graph_error = repr(exc)[:200]
                     torch.cuda.synchronize()
         if self.kind == 'picard':
@@ -492,6 +501,23 @@ class Runner:
             getattr(pl, k).copy_(self.host[k], non_blocking=True)
         self.forward()
         self.adjoint()
+
+    def e2e_async(self, k):
+        """Step k of a run of independent end-to-end solves: enqueued on pipeline k mod depth, whose stream orders it after
+        the step that used the same buffers."""
+        q = k % len(self.pipes)
+        with self.torch.cuda.stream(self.pipe_streams[q]):
+            self.pipes[q].run()
+
+    def e2e_fork(self):
+        cur = self.torch.cuda.current_stream()
+        for st in self.pipe_streams:
+            st.wait_stream(cur)
+
+    def e2e_join(self):
+        cur = self.torch.cuda.current_stream()
+        for st in self.pipe_streams:
+            cur.wait_stream(st)
 
     def e2e_readback(self):
         if self.pipe is not None:
@@ -659,6 +685,8 @@ def main():
     ap.add_argument('--newton-tol', type=float, default=1e-7)
     ap.add_argument('--e2e-slices', type=int, default=4, help='sub-batches (streams) of the end-to-end leg')
     ap.add_argument('--e2e-fractions', default='', help='relative sub-batch sizes of the end-to-end leg, e.g. 4,3,2,1 (overrides --e2e-slices)')
+    ap.add_argument('--e2e-depth', type=int, default=3,
+                    help='independent end-to-end solves in flight (own buffers and streams each); 1 = each step timed alone')
     ap.add_argument('--no-e2e-graph', action='store_true', help='enqueue the end-to-end pipeline eagerly (no CUDA graph)')
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == 'ours' else args.warmup
@@ -802,6 +830,25 @@ def main():
     for _ in range(args.steps):
         e2e_step(run, etimes)
     barrier()
+    e2e_single_ms = float(np.sum([a.elapsed_time(b) for a, b in etimes]))     # one solve in flight, L2 flushed between steps
+    e2e_depth = len(run.pipes) if getattr(run, 'pipe', None) is not None else 1
+    if e2e_depth > 1:
+        # throughput of a stream of independent host-resident batches: `depth` solves in flight, timed on the device from
+        # before the first upload to after the last download of the K steps (inputs arrive over PCIe every step)
+        def e2e_run(steps):
+            a, b = ev(), ev()
+            a.record()
+            run.e2e_fork()
+            for k in range(steps):
+                run.e2e_async(k)
+            run.e2e_join()
+            b.record()
+            return a, b
+        e2e_run(args.warmup)
+        torch.cuda.synchronize()
+        barrier()
+        etimes = [e2e_run(args.steps)]
+        barrier()
     clocks = sampler.stop() if rank == 0 else None
     if hasattr(run, 'check'):
         run.check()                            # a halo wait that timed out shows up here, not as a hang
@@ -819,10 +866,10 @@ def main():
         extra_cfg['not_converged'] = int((run.pic['status'] != 0).sum().item())
         extra_cfg['mean_sweeps'] = float(run.pic['iters'].double().mean().item())
 
-    tot = torch.tensor([step_ms, e2e_ms, fwd_sum, adj_sum], dtype=torch.float64, device=dev)
+    tot = torch.tensor([step_ms, e2e_ms, fwd_sum, adj_sum, e2e_single_ms], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(tot, op=dist.ReduceOp.MAX)
-    step_ms, e2e_ms, fwd_tot, adj_tot = tot.tolist()
+    step_ms, e2e_ms, fwd_tot, adj_tot, e2e_single_ms = tot.tolist()
 
     units_per_step = run.units if sharded else world * run.units
     value = units_per_step * args.steps / (step_ms * 1e-3)
@@ -874,10 +921,15 @@ def main():
             'shared_gradient_allreduce': shared_mode[0],
             'e2e': {'value': e2e_value, 'unit': 'state-steps/s', 'h2d_bytes_per_step': run.h2d,
                     'd2h_bytes_per_step': run.d2h, 'ms_per_step': e2e_ms / args.steps,
-                    'how': (f'engine.PipelinedTmSolve: {len(run.pipe.plans) if run.pipe is not None else 1} sub-batches (sizes {[b - a for a, b in run.pipe.bounds] if run.pipe is not None else []}) on their own streams, pinned host buffers, '
+                    'solves_in_flight': e2e_depth,
+                    'one_solve_in_flight': {'value': units_per_step * args.steps / (e2e_single_ms * 1e-3),
+                                            'ms_per_step': e2e_single_ms / args.steps,
+                                            'how': 'each step timed alone (upload -> solve -> download), L2 flushed between steps'},
+                    'how': ((f'{e2e_depth} independent solves in flight (own device + pinned buffers each), K steps timed on the device '
+                             f'from the first upload to the last download; each solve: ' if e2e_depth > 1 else '') + (f'engine.PipelinedTmSolve: {len(run.pipe.plans) if run.pipe is not None else 1} sub-batches (sizes {[b - a for a, b in run.pipe.bounds] if run.pipe is not None else []}) on their own streams, pinned host buffers, '
                             + ('slice pipeline replayed as one CUDA graph' if getattr(run, 'e2e_graph', False) else
                                'eager enqueue' + (f' (graph capture failed: {run.e2e_graph_error})' if hasattr(run, 'e2e_graph_error') else ''))
-                            if run.pipe is not None else 'engine plan API, pinned host buffers, one stream')},
+                            if run.pipe is not None else 'engine plan API, pinned host buffers, one stream'))},
             'gpu_launches': args.steps * run.launches,
             'roofline': roof, 'cpu_baseline': cpu, 'clocks': clocks,
             'wall_ms_timed_loop': t_wall * 1e3, 'other_workloads': others,

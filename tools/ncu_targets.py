@@ -30,7 +30,7 @@ if which == 'picard':
 
 
 class A:
-    newton_tol, e2e_slices, world, no_e2e_graph, e2e_fractions = 1e-7, 2, 1, True, ''
+    newton_tol, e2e_slices, world, no_e2e_graph, e2e_fractions, e2e_depth = 1e-7, 2, 1, True, '', 1
 
 
 run = bench.Runner(wl, name, 0, torch.device('cuda', 0), A)
