@@ -422,9 +422,10 @@ class Runner:
             # steps of the end-to-end leg are independent solves of host-resident batches: `depth` of them are in flight, each with
             # its own device + pinned buffers and streams, so that step k + 1 uploads while step k computes and downloads
             depth = max(1, int(getattr(args, 'e2e_depth', 1)))
-            self.pipes = [self.pipe] + [engine.PipelinedTmSolve(spec, slices=args.e2e_slices, device=dev, grads=want, cotangents=cot,
-                                                                upload=self.e2e_inputs, fractions=fr) for _ in range(depth - 1)]
-            self.pipe_streams = [torch.cuda.Stream(device=dev) for _ in self.pipes]
+            self.queue = engine.SolveStream(spec, depth=depth, device=dev, slices=args.e2e_slices, grads=want, cotangents=cot,
+                                            upload=self.e2e_inputs, fractions=fr)
+            self.pipes = [self.pipe] + self.queue.pipes[1:]      # slot 0 is the solve that is also timed alone
+            self.queue.pipes = self.pipes
             for pipe in self.pipes:
                 pipe.set_host_inputs(**self.host)
                 if args.world > 1:
@@ -503,21 +504,14 @@ class Runner:
         self.adjoint()
 
     def e2e_async(self, k):
-        """Step k of a run of independent end-to-end solves: enqueued on pipeline k mod depth, whose stream orders it after
-        the step that used the same buffers."""
-        q = k % len(self.pipes)
-        with self.torch.cuda.stream(self.pipe_streams[q]):
-            self.pipes[q].run()
+        """Step k of a run of independent end-to-end solves (engine.SolveStream: slot k mod depth)."""
+        self.queue.submit()
 
     def e2e_fork(self):
-        cur = self.torch.cuda.current_stream()
-        for st in self.pipe_streams:
-            st.wait_stream(cur)
+        self.queue.begin()
 
     def e2e_join(self):
-        cur = self.torch.cuda.current_stream()
-        for st in self.pipe_streams:
-            cur.wait_stream(st)
+        self.queue.end()
 
     def e2e_readback(self):
         if self.pipe is not None:
@@ -925,7 +919,7 @@ def main():
                     'one_solve_in_flight': {'value': units_per_step * args.steps / (e2e_single_ms * 1e-3),
                                             'ms_per_step': e2e_single_ms / args.steps,
                                             'how': 'each step timed alone (upload -> solve -> download), L2 flushed between steps'},
-                    'how': ((f'{e2e_depth} independent solves in flight (own device + pinned buffers each), K steps timed on the device '
+                    'how': ((f'engine.SolveStream: {e2e_depth} independent solves in flight (own device + pinned buffers each), K steps timed on the device '
                              f'from the first upload to the last download; each solve: ' if e2e_depth > 1 else '') + (f'engine.PipelinedTmSolve: {len(run.pipe.plans) if run.pipe is not None else 1} sub-batches (sizes {[b - a for a, b in run.pipe.bounds] if run.pipe is not None else []}) on their own streams, pinned host buffers, '
                             + ('slice pipeline replayed as one CUDA graph' if getattr(run, 'e2e_graph', False) else
                                'eager enqueue' + (f' (graph capture failed: {run.e2e_graph_error})' if hasattr(run, 'e2e_graph_error') else ''))

@@ -735,6 +735,59 @@ class PipelinedTmSolve:
         return sum(pl.launches_forward + pl.launches_adjoint for pl in self.plans)
 
 
+class SolveStream:
+    """A stream of INDEPENDENT host-resident batches of the same shape (an optimiser evaluating several designs, a service
+    working through a queue): `depth` PipelinedTmSolve instances, each with its own device + pinned buffers and streams, used
+    round-robin, so that solve k + 1 uploads while solve k computes and downloads and both copy engines stay busy.
+    One solve alone is bound by the chain upload -> last sub-batch's kernels -> download; a stream of them by the link.
+
+        q = SolveStream(spec, depth=3, slices=4, grads=('h', 'p'))
+        q.set_host_inputs(slot, y0=..., h=..., p=...)        # for every slot, or slot=None for all
+        q.begin();  slots = [q.submit() for _ in range(K)];  q.end()       # enqueue only; results after a synchronisation
+        final, grads = q.gather(slot)                          # of the LAST solve submitted to that slot
+    """
+
+    def __init__(self, spec: SolveSpec, depth=3, device='cuda', **pipeline_args):
+        self.pipes = [PipelinedTmSolve(spec, device=device, **pipeline_args) for _ in range(max(1, int(depth)))]
+        self.streams = [torch.cuda.Stream(device=torch.device(device)) for _ in self.pipes]
+        self._next = 0
+
+    depth = property(lambda self: len(self.pipes))
+
+    def set_host_inputs(self, slot=None, **arrays):
+        for q, pipe in enumerate(self.pipes):
+            if slot is None or q == slot:
+                pipe.set_host_inputs(**arrays)
+
+    def capture(self):
+        for pipe in self.pipes:
+            pipe.capture()
+        return self
+
+    def begin(self):
+        """Order every slot after the work already enqueued on the current stream."""
+        cur = torch.cuda.current_stream()
+        for st in self.streams:
+            st.wait_stream(cur)
+
+    def submit(self):
+        """Enqueue the next solve on the next slot (after the solve that used that slot before); returns the slot."""
+        q = self._next
+        self._next = (q + 1) % len(self.pipes)
+        with torch.cuda.stream(self.streams[q]):
+            self.pipes[q].run()
+        return q
+
+    def end(self):
+        """Make the current stream wait for everything submitted."""
+        cur = torch.cuda.current_stream()
+        for st in self.streams:
+            cur.wait_stream(st)
+
+    def gather(self, slot):
+        return self.pipes[slot].gather()
+
+
 def measure_fma_peak(dtype=torch.float64, device='cuda', iters=20000, repeats=3):
     """Measured vector FMA peak of this GPU in TFLOP/s (oz_fma_probe timed with CUDA events, best of `repeats`)."""
     out = torch.zeros(1, dtype=dtype, device=device)

@@ -236,3 +236,41 @@ def test_pipelined_host_batch_equals_the_single_launch_solve():
         assert torch.equal(final, plan.final.cpu())
         assert torch.equal(grads['p'], plan.grad['p'].cpu())
         assert relerr(np_(grads['h']), np_(plan.grad['h'])) < 1e-13
+
+
+def test_stream_of_independent_host_batches_keeps_several_solves_in_flight():
+    # engine.SolveStream (the bench's e2e leg): three slots with DIFFERENT inputs, used round-robin twice, eagerly and as
+    # CUDA graphs; every slot must hold exactly what a plain single-launch solve of its inputs gives
+    from ozone_b200 import engine
+    from tests.gpu_util import make_spec, dev_inputs
+    c = cases.van_der_pol_inputs(N=700, nt=21)
+    spec = make_spec(c, 'GaussLegendre4', tol=1e-12)
+    y0, h, p, th = dev_inputs(c, spec)
+    plan = engine.TmPlan(spec, grads=('h', 'p'), cotangents=('final',))
+    plan.y0.copy_(y0); plan.h.copy_(h)
+    plan.final_bar.zero_(); plan.final_bar[-1].fill_(1.0)
+    q = engine.SolveStream(spec, depth=3, slices=2, grads=('h', 'p'), cotangents=('final',), upload=('h', 'p'))
+    assert q.depth == 3
+    scale = (1.0, 0.5, -0.25)
+    want = []
+    for slot, f in enumerate(scale):
+        q.set_host_inputs(slot, y0=y0.cpu(), h=h.cpu(), p=(p * f).cpu())
+        for pl in q.pipes[slot].plans:
+            pl.final_bar.zero_(); pl.final_bar[-1].fill_(1.0)
+        plan.p.copy_(p * f)
+        plan.forward(); plan.adjoint()
+        torch.cuda.synchronize()
+        want.append((plan.final.cpu().clone(), plan.grad['p'].cpu().clone(), plan.grad['h'].cpu().clone()))
+    for graphs in (False, True):
+        if graphs:
+            q.capture()
+        q.begin()
+        slots = [q.submit() for _ in range(6)]
+        q.end()
+        assert slots == [0, 1, 2, 0, 1, 2]
+        torch.cuda.synchronize()
+        for slot in range(3):
+            final, grads = q.gather(slot)
+            assert torch.equal(final, want[slot][0])
+            assert torch.equal(grads['p'], want[slot][1])
+            assert relerr(np_(grads['h']), np_(want[slot][2])) < 1e-13
