@@ -164,3 +164,37 @@ def test_spatial_slabs_of_a_traced_grid_match_the_single_slab_solve():
     assert relerr(np_(res['y0_bar']), np_(g['y0'][:, 0])) < 1e-12
     assert relerr(np_(res['h_bar']), np_(g['h'])) < 1e-12
     assert relerr(np_(res['u_bar']), np_(g['p'])) < 1e-12
+
+
+def test_traced_callback_equals_the_built_in_model_at_the_full_grid_size():
+    # BASELINE config C3's grid (10^6 cells), 64 steps in 8 checkpointed segments: field output and every gradient of the
+    # traced callback against the hand-written model of the same PDE
+    from ozone_b200 import engine
+    from ozone_b200.glms import get_integration_method
+    from ozone_b200.trace_grid import TracedGridRHS
+    from tests.gpu_util import relerr, np_
+    import bench
+    nx, n, ni = 1_000_000, 64, 8
+    dx = np.pi / nx
+    m = get_integration_method('RK4')
+    rng = np.random.default_rng(4)
+    t = lambda a: torch.tensor(np.ascontiguousarray(a), dtype=torch.float64, device='cuda')
+    y0 = t(0.5 + 0.1 * np.sin(np.arange(nx) * (7 * np.pi / nx))).reshape(-1, 1)
+    h, u = t(np.full(n, 0.4 * dx * dx)), t(rng.uniform(-0.6, 0.0, size=n + 1)).reshape(-1, 1)
+    one = torch.ones(1, 1, dtype=torch.float64, device='cuda')
+    common = dict(method=m, N=1, n=n, h_shared=True, p_shared=True, th_shared=True, num_inner=ni, store_history=False, d_override=nx)
+    res = {}
+    for key in ('built_in', 'traced'):
+        if key == 'traced':
+            tr = TracedGridRHS(bench.pde_control_callback, (), dict(dx=dx, nx=nx, beta_t=16.0, beta_u=2.0, gamma=2.0), 'x', nx, ['u'])
+            spec = engine.SolveSpec(rhs_name='traced', traced=tr, **common)
+            th = t(tr.tracer.coefficient_table().reshape(-1))
+        else:
+            spec = engine.SolveSpec(rhs_name='diffusion_reaction', rhs_cfg=(dx, 16.0, 2.0, 2.0, float(round(0.3 * nx)), float(round(0.7 * nx))),
+                                    **common)
+            th = None
+        fwd = engine.tm_forward(spec, y0, h, u, th, keep_history=False)
+        g = engine.tm_adjoint(spec, y0, h, u, th, ckpt=fwd['ckpt'], field_bar=one, need=('y0', 'h', 'p'))
+        res[key] = (np_(fwd['final']), np_(fwd['field']), np_(g['y0']), np_(g['h']), np_(g['p']))
+    for a, b, tol in zip(res['traced'], res['built_in'], (1e-13, 1e-13, 1e-11, 1e-10, 1e-11)):
+        assert relerr(a, b) < tol
