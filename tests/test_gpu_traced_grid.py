@@ -129,6 +129,24 @@ def test_grid_callback_without_parameters_or_outputs_and_refusals_at_run_time():
     g, = torch.autograd.grad(out.final_states['T'].sum(), [T0])
     assert np.abs(g.cpu().numpy() - np.linalg.matrix_power(R, n).T @ np.ones(nx)).max() < 1e-12
 
+    # a field output without any dynamic parameter: sum over time of dz * sum(T^2), differentiated w.r.t. the initial grid
+    def heat_with_energy(ov, kappa):
+        heat(ov, kappa)
+        x = ov.states['T'][0, :]
+        ov.field_outputs['energy'] = (dz * ozone.ops.sum(x * x)).reshape(1, 1)
+    T0b = var(T0_np)
+    prob = ozone.ODEProblem(ozone.methods.RK4(), TimeMarching(), verbose=False)
+    prob.add_state('T', T0b, store_final=True)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(heat_with_energy, 1.0 / dz ** 2)
+    out = prob.solve()
+    powers = [np.linalg.matrix_power(R, k) for k in range(n + 1)]
+    want_E = dz * sum(float((Pk @ T0_np) @ (Pk @ T0_np)) for Pk in powers)
+    assert float(out.field_outputs['energy'].sum().detach()) == pytest.approx(want_E, rel=1e-12)
+    gE, = torch.autograd.grad(out.field_outputs['energy'].sum(), [T0b])
+    want_g = 2.0 * dz * sum(Pk.T @ (Pk @ T0_np) for Pk in powers)
+    assert np.abs(gE.cpu().numpy() - want_g).max() < 1e-12 * np.abs(want_g).max()
+
     prob = ozone.ODEProblem(ozone.methods.ImplicitMidpoint(), TimeMarching(), verbose=False)
     prob.add_state('T', T0, store_final=True)
     prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
