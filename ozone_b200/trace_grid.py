@@ -19,7 +19,7 @@ system, ``exp`` and reciprocals through the same fast device routines -- and com
 
 What the kernels can express, and what is refused with an error that says so:
   * one state (the grid), at most one scalar dynamic parameter, explicit methods, TimeMarching / TimeMarchingCheckpoints;
-  * a three-point stencil with zero ghost cells whose NEIGHBOUR terms are linear, with weights that are constants or
+  * a three-point stencil with constant (zero or non-zero) boundary values whose NEIGHBOUR terms are linear, with weights that are constants or
     coefficient fields (variable diffusivity, upwind advection); the cell's own value may enter in any smooth way;
   * the dynamic parameter enters linearly (its weight may be a coefficient field);
   * at most one field output of the form  const * sum_cells q(x, coefficients) + r(parameter); no profile outputs;
@@ -332,13 +332,16 @@ class GridVar:
 
 
 def concatenate(pieces, axis=0):
-    """Zero ghost cells: ``concatenate((zeros, x[:-1]))`` / ``concatenate((x[1:], zeros))``."""
+    """Ghost cells: ``concatenate((zeros, x[:-1]))`` / ``concatenate((x[1:], zeros))``.  Constant NON-zero boundary values
+    (Dirichlet data) are allowed too: the kernels' ghost cells are zero, so the constants become a coefficient field that is
+    non-zero at the padded positions only and is added to the shifted state."""
     grid = [p for p in pieces if isinstance(p, GridVar)]
     if len(grid) != 1:
         raise NotImplementedError('a grid right-hand side may concatenate ONE slice of a grid quantity with zeros (ghost cells)')
     g = grid[0]
     front = back = 0
     seen = False
+    front_vals, back_vals = [], []
     for p in pieces:
         if p is g:
             seen = True
@@ -348,10 +351,9 @@ def concatenate(pieces, axis=0):
         try:
             vals = a.astype(np.float64)
         except (TypeError, ValueError):
-            raise NotImplementedError('only zeros can be concatenated to a grid quantity (zero ghost cells)') from None
-        if np.any(vals != 0.0):
-            raise NotImplementedError('only zeros can be concatenated to a grid quantity: the kernels implement zero ghost '
-                                      'cells (pde_control.py:32-35)')
+            raise NotImplementedError('only constants can be concatenated to a grid quantity (boundary values); a traced '
+                                      'quantity cannot be a ghost cell') from None
+        (back_vals if seen else front_vals).append(vals.reshape(-1))
         if seen:
             back += vals.size
         else:
@@ -369,6 +371,13 @@ def concatenate(pieces, axis=0):
             if l.op == 'gx' and ((front and l.idx > -front) or (back and l.idx < back)):
                 raise NotImplementedError('the padded cells would not be ghost cells: a slice x[a:] goes with zeros at the END, '
                                           'x[:-a] with zeros at the FRONT')
+        pad = np.zeros(n)
+        if front:
+            pad[:front] = np.concatenate(front_vals)
+        if back:
+            pad[n - back:] = np.concatenate(back_vals)
+        if np.any(pad != 0.0):            # Dirichlet data: zero ghost cell + a constant that only the boundary cells see
+            expr = expr + tr.field(pad)
     shape = list(g.shape)
     cell_axis = next((i for i, s in enumerate(shape) if s != 1), axis if axis < len(shape) else 0) if shape else 0
     if not shape:

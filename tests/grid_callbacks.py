@@ -107,3 +107,27 @@ class AdvectionDiffusionOracle(Rhs):
         J = self.dz * np.sum(self._col(self.fl['weight'], y) * y * y, axis=0) + 0.3 * q * q + 0.1 * q
         shp = np.broadcast_shapes(y.shape[1:], q.shape)
         return np.zeros((0,) + shp), np.broadcast_to(J, shp)[None]
+
+
+def dirichlet_heat(ozone_vars, kappa, left, right):
+    """T' = kappa (T[k-1] - 2 T[k] + T[k+1]) - 0.5 T^3 with constant boundary values T[-1] = left, T[nx] = right."""
+    T = ozone_vars.states['T'][0, :]
+    lo = csdl.concatenate((np.full(1, left), T[:-1]))
+    hi = csdl.concatenate((T[1:], np.full(1, right)))
+    ozone_vars.d_states['T'] = (kappa * (lo - 2.0 * T + hi) - 0.5 * T ** 3).reshape(1, -1)
+
+
+class DirichletHeatOracle(Rhs):
+    name = 'dirichlet_heat'
+    P = S = NFIELD = 0
+
+    def __init__(self, nx, kappa, left, right):
+        self.D = self.nx = nx
+        self.kappa, self.left, self.right = kappa, left, right
+
+    def f(self, y, p, th):
+        lo = np.full_like(y, self.left)
+        lo[1:] = y[:-1]
+        hi = np.full_like(y, self.right)
+        hi[:-1] = y[1:]
+        return self.kappa * (lo - 2.0 * y + hi) - 0.5 * y ** 3

@@ -69,7 +69,7 @@ def test_advection_diffusion_callback_matches_the_oracle_states_and_gradients(me
     ref = I.time_marching(rhs, method, c0_np[:, None], h_np, q_np.reshape(n + 1, 1, 1), None)
     hist = out.states['c'].detach().cpu().numpy()
     assert np.abs(hist - ref['history'][:, :, 0]).max() <= 1e-12 * np.abs(ref['history']).max()
-    assert float(out.field_outputs['cost'].sum()) == pytest.approx(float(ref['field'][0, 0]), rel=1e-12)
+    assert float(out.field_outputs['cost'].sum().detach()) == pytest.approx(float(ref['field'][0, 0]), rel=1e-12)
 
     rngb = np.random.default_rng(7)
     hb, fb = rngb.standard_normal(hist.shape), rngb.standard_normal(nx)
@@ -216,3 +216,28 @@ def test_traced_callback_equals_the_built_in_model_at_the_full_grid_size():
         res[key] = (np_(fwd['final']), np_(fwd['field']), np_(g['y0']), np_(g['h']), np_(g['p']))
     for a, b, tol in zip(res['traced'], res['built_in'], (1e-13, 1e-13, 1e-11, 1e-10, 1e-11)):
         assert relerr(a, b) < tol
+
+
+def test_constant_non_zero_boundary_values_against_the_oracle():
+    from oracle import integrators as I, adjoint as Adj
+    nx, n = 160, 11
+    dz = 1.0 / nx
+    kappa, left, right = 1.0 / dz ** 2, 0.8, -0.3
+    T0_np = 0.2 * np.cos(5 * np.pi * np.arange(nx) / nx)
+    h_np = np.full(n, 0.2 * dz * dz)
+    T0, h = var(T0_np), var(h_np)
+    prob = ozone.ODEProblem(ozone.methods.RK4(), TimeMarching(), verbose=False)
+    prob.add_state('T', T0, store_history=True, store_final=True)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(G.dirichlet_heat, kappa, left, right)
+    out = prob.solve()
+    rhs = G.DirichletHeatOracle(nx, kappa, left, right)
+    ref = I.time_marching(rhs, 'RK4', T0_np[:, None], h_np, None, None)
+    hist = out.states['T'].detach().cpu().numpy()
+    assert np.abs(hist - ref['history'][:, :, 0]).max() <= 1e-12 * np.abs(ref['history']).max()
+    assert abs(hist[-1, 0] - left) < abs(hist[0, 0] - left)          # the boundary value pulls the first cell towards it
+    fb = np.random.default_rng(9).standard_normal(nx)
+    g_T0, g_h = torch.autograd.grad((out.final_states['T'] * var(fb, False)).sum(), [T0, h])
+    g = Adj.tm_adjoint(rhs, 'RK4', T0_np[:, None], h_np, None, None, history=ref['history'], final_bar=fb[:, None])
+    assert np.abs(g_T0.cpu().numpy() - g['y0'][:, 0]).max() <= 1e-10 * np.abs(g['y0']).max()
+    assert np.abs(g_h.cpu().numpy() - g['h']).max() <= 1e-10 * np.abs(g['h']).max()

@@ -105,11 +105,11 @@ def test_what_the_stencil_kernels_cannot_express_is_refused_with_the_reason():
     with pytest.raises(NotImplementedError, match='ghost cells'):
         _trace(wrong_side)
 
-    def nonzero_boundary(ov):
+    def traced_boundary(ov):
         x = ov.states['x'][0, :]
-        ov.d_states['x'] = (ops.concatenate((np.ones(1), x[:-1])) - x).reshape(1, -1)
-    with pytest.raises(NotImplementedError, match='only zeros'):
-        _trace(nonzero_boundary)
+        ov.d_states['x'] = (ops.concatenate((ov.dynamic_parameters['u'][0], x[:-1])) - x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='only constants'):
+        _trace(traced_boundary)
 
     def single_cell(ov):
         x = ov.states['x'][0, :]
@@ -157,3 +157,28 @@ def test_generated_grid_model_compiles_and_registers_without_a_gpu():
     assert t.plugin_id(4, False, True, 0) == rid                       # cached per (stages, dtype)
     with pytest.raises(ValueError, match='explicit methods only'):
         t.plugin_id(2, True, True, 0)
+
+
+def test_constant_boundary_values_become_a_coefficient_field_at_the_boundary_cells():
+    nx = 40
+
+    def dirichlet(ov, left, right):
+        x = ov.states['x'][0, :]
+        lo = ops.concatenate((np.full(1, left), x[:-1]))
+        hi = ops.concatenate((x[1:], np.full(1, right)))
+        ov.d_states['x'] = (3.0 * (lo - 2.0 * x + hi)).reshape(1, -1)
+    t = TracedGridRHS(dirichlet, (0.7, -1.2), {}, 'x', nx, [])
+    tab = t.tracer.coefficient_table()
+    want_l, want_r = np.zeros(nx), np.zeros(nx)
+    want_l[0], want_r[-1] = 0.7, -1.2
+    rows = {tuple(r) for r in tab}
+    assert tuple(want_l) in rows and tuple(want_r) in rows
+    # cell 0 sees 3 (0.7 - 2 x0 + x1), the last cell 3 (x_{n-2} - 2 x_{n-1} - 1.2), interior cells no constant
+    x = np.random.default_rng(3).uniform(-1, 1, nx)
+    xe = np.concatenate(([0.0], x, [0.0]))
+    for k in (0, 1, nx - 1):
+        env = {('gx', -1): xe[k], ('gx', 0): xe[k + 1], ('gx', 1): xe[k + 2]}
+        env.update({('gc', q): tab[q, k] for q in range(tab.shape[0])})
+        left = 0.7 if k == 0 else x[k - 1]
+        right = -1.2 if k == nx - 1 else x[k + 1]
+        assert _evaluate(t.f, env) == pytest.approx(3.0 * (left - 2.0 * x[k] + right), rel=1e-14)
