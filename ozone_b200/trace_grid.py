@@ -19,7 +19,7 @@ system, ``exp`` and reciprocals through the same fast device routines -- and com
 
 What the kernels can express, and what is refused with an error that says so:
   * one state (the grid), at most one scalar dynamic parameter, explicit methods, TimeMarching / TimeMarchingCheckpoints;
-  * a three-point stencil with constant (zero or non-zero) boundary values whose NEIGHBOUR terms are linear, with weights that are constants or
+  * a three-point stencil with constant (zero or non-zero) or reflecting boundary values whose NEIGHBOUR terms are linear, with weights that are constants or
     coefficient fields (variable diffusivity, upwind advection); the cell's own value may enter in any smooth way;
   * the dynamic parameter enters linearly (its weight may be a coefficient field);
   * at most one field output of the form  const * sum_cells q(x, coefficients) + r(parameter); no profile outputs;
@@ -332,52 +332,58 @@ class GridVar:
 
 
 def concatenate(pieces, axis=0):
-    """Ghost cells: ``concatenate((zeros, x[:-1]))`` / ``concatenate((x[1:], zeros))``.  Constant NON-zero boundary values
-    (Dirichlet data) are allowed too: the kernels' ghost cells are zero, so the constants become a coefficient field that is
-    non-zero at the padded positions only and is added to the shifted state."""
+    """Ghost cells: ``concatenate((zeros, x[:-1]))`` / ``concatenate((x[1:], zeros))``.
+
+    The longest grid piece is the shifted state; the kernels evaluate it with ZERO ghost cells, so what is concatenated to it
+    is added on top as coefficient fields that only the padded cells see: constants (Dirichlet data) as their values, other
+    grid pieces -- ``x[:1]`` in front for a reflecting boundary -- as (0/1 indicator) x (that piece's expression)."""
     grid = [p for p in pieces if isinstance(p, GridVar)]
-    if len(grid) != 1:
-        raise NotImplementedError('a grid right-hand side may concatenate ONE slice of a grid quantity with zeros (ghost cells)')
-    g = grid[0]
-    front = back = 0
-    seen = False
-    front_vals, back_vals = [], []
-    for p in pieces:
-        if p is g:
-            seen = True
-            continue
-        a = p.a if isinstance(p, TVar) else p
-        a = np.asarray(a.detach().cpu() if isinstance(a, torch.Tensor) else a)
-        try:
-            vals = a.astype(np.float64)
-        except (TypeError, ValueError):
-            raise NotImplementedError('only constants can be concatenated to a grid quantity (boundary values); a traced '
-                                      'quantity cannot be a ghost cell') from None
-        (back_vals if seen else front_vals).append(vals.reshape(-1))
-        if seen:
-            back += vals.size
-        else:
-            front += vals.size
+    if not grid:
+        raise TypeError('internal: grid concatenation without a grid quantity')
+    g = max(grid, key=lambda p: p.n)                      # the shifted state; everything else is boundary data
     tr = g.tr
-    n = front + g.n + back
+    offsets, n = [], 0
+    for p in pieces:
+        offsets.append(n)
+        if isinstance(p, GridVar):
+            n += p.n
+        else:
+            a = p.a if isinstance(p, TVar) else p
+            a = np.asarray(a.detach().cpu() if isinstance(a, torch.Tensor) else a)
+            try:
+                n += a.astype(np.float64).size
+            except (TypeError, ValueError):
+                raise NotImplementedError('only constants or slices of the state can be concatenated to a grid quantity '
+                                          '(boundary values); a traced scalar cannot be a ghost cell') from None
+    front = next(o for p, o in zip(pieces, offsets) if p is g)
+    back = n - front - g.n
     expr = tr.shift(g.expr, -front)
     if front or back:
         if n != tr.nx:
-            raise NotImplementedError('padding with zeros must restore the full grid length')
+            raise NotImplementedError('padding must restore the full grid length')
         if not _zero_when_state_is_zero(expr):
-            raise NotImplementedError('a zero-padded slice must vanish where the state vanishes (it stands for ghost cells): '
+            raise NotImplementedError('a padded slice must vanish where the state vanishes (it stands for ghost cells): '
                                       'shift the state itself, then apply nonlinear functions')
         for l in leaves_of(expr):
             if l.op == 'gx' and ((front and l.idx > -front) or (back and l.idx < back)):
-                raise NotImplementedError('the padded cells would not be ghost cells: a slice x[a:] goes with zeros at the END, '
-                                          'x[:-a] with zeros at the FRONT')
+                raise NotImplementedError('the padded cells would not be ghost cells: a slice x[a:] goes with padding at the END, '
+                                          'x[:-a] with padding at the FRONT')
         pad = np.zeros(n)
-        if front:
-            pad[:front] = np.concatenate(front_vals)
-        if back:
-            pad[n - back:] = np.concatenate(back_vals)
+        for p, o in zip(pieces, offsets):
+            if p is g:
+                continue
+            if isinstance(p, GridVar):                    # e.g. x[:1] in front: the ghost cell mirrors the boundary cell
+                ind = np.zeros(n)
+                ind[o:o + p.n] = 1.0
+                expr = expr + tr.field(ind) * tr.shift(p.expr, -o)
+            else:
+                a = p.a if isinstance(p, TVar) else p
+                a = np.asarray(a.detach().cpu() if isinstance(a, torch.Tensor) else a).astype(np.float64).reshape(-1)
+                pad[o:o + a.size] = a
         if np.any(pad != 0.0):            # Dirichlet data: zero ghost cell + a constant that only the boundary cells see
             expr = expr + tr.field(pad)
+    elif len(pieces) != 1:
+        raise NotImplementedError('empty pieces in a grid concatenation')
     shape = list(g.shape)
     cell_axis = next((i for i, s in enumerate(shape) if s != 1), axis if axis < len(shape) else 0) if shape else 0
     if not shape:

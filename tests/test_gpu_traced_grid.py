@@ -98,7 +98,7 @@ def test_traced_grid_with_checkpoints_and_in_single_precision():
         prob.set_function(G.advection_diffusion, nx=nx, dz=dz, speed=0.7, rate=1.3)
         out = prob.solve()
         loss = out.field_outputs['cost'].sum() + (out.final_states['c'] ** 2).sum()
-        res[key] = [float(loss)] + [t.double().cpu().numpy() for t in torch.autograd.grad(loss, [q, c0, h])]
+        res[key] = [float(loss.detach())] + [t.double().cpu().numpy() for t in torch.autograd.grad(loss, [q, c0, h])]
     for a, b in zip(res['ckpt'], res['f64']):
         assert np.abs(np.asarray(a) - np.asarray(b)).max() <= 1e-12 * np.abs(b).max()
     for a, b in zip(res['f32'], res['f64']):
@@ -241,3 +241,33 @@ def test_constant_non_zero_boundary_values_against_the_oracle():
     g = Adj.tm_adjoint(rhs, 'RK4', T0_np[:, None], h_np, None, None, history=ref['history'], final_bar=fb[:, None])
     assert np.abs(g_T0.cpu().numpy() - g['y0'][:, 0]).max() <= 1e-10 * np.abs(g['y0']).max()
     assert np.abs(g_h.cpu().numpy() - g['h']).max() <= 1e-10 * np.abs(g['h']).max()
+
+
+def test_reflecting_boundaries_conserve_the_total_and_give_the_transposed_propagator():
+    nx, n = 300, 9
+    dz = 1.0 / nx
+    kappa = 1.0 / dz ** 2
+
+    def neumann_heat(ov, kappa):
+        x = ov.states['T'][0, :]
+        lo = ozone.ops.concatenate((x[:1], x[:-1]))
+        hi = ozone.ops.concatenate((x[1:], x[-1:]))
+        ov.d_states['T'] = (kappa * (lo - 2.0 * x + hi)).reshape(1, -1)
+    T0_np = np.random.default_rng(8).uniform(0.0, 1.0, nx)
+    T0, h = var(T0_np), var(np.full(n, 0.2 * dz * dz))
+    prob = ozone.ODEProblem(ozone.methods.RK4(), TimeMarching(), verbose=False)
+    prob.add_state('T', T0, store_final=True)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(neumann_heat, kappa)
+    out = prob.solve()
+    final = out.final_states['T'].detach().cpu().numpy()
+    L = np.diag(-2.0 * np.ones(nx)) + np.diag(np.ones(nx - 1), 1) + np.diag(np.ones(nx - 1), -1)
+    L[0, 0] = L[-1, -1] = -1.0
+    Z = 0.2 * L
+    R = np.eye(nx) + Z + Z @ Z / 2 + Z @ Z @ Z / 6 + Z @ Z @ Z @ Z / 24
+    Rn = np.linalg.matrix_power(R, n)
+    assert np.abs(final - Rn @ T0_np).max() < 1e-13
+    assert abs(final.sum() - T0_np.sum()) < 1e-11 * T0_np.sum()                    # no flux through the ends
+    w = np.random.default_rng(9).standard_normal(nx)
+    g, = torch.autograd.grad((out.final_states['T'] * var(w, False)).sum(), [T0])
+    assert np.abs(g.cpu().numpy() - Rn.T @ w).max() < 1e-12

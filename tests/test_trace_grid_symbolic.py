@@ -108,7 +108,7 @@ def test_what_the_stencil_kernels_cannot_express_is_refused_with_the_reason():
     def traced_boundary(ov):
         x = ov.states['x'][0, :]
         ov.d_states['x'] = (ops.concatenate((ov.dynamic_parameters['u'][0], x[:-1])) - x).reshape(1, -1)
-    with pytest.raises(NotImplementedError, match='only constants'):
+    with pytest.raises(NotImplementedError, match='only constants or slices'):
         _trace(traced_boundary)
 
     def single_cell(ov):
@@ -182,3 +182,31 @@ def test_constant_boundary_values_become_a_coefficient_field_at_the_boundary_cel
         left = 0.7 if k == 0 else x[k - 1]
         right = -1.2 if k == nx - 1 else x[k + 1]
         assert _evaluate(t.f, env) == pytest.approx(3.0 * (left - 2.0 * x[k] + right), rel=1e-14)
+
+
+def test_reflecting_boundaries_are_an_indicator_field_times_the_boundary_cell_and_periodic_ones_are_refused():
+    nx = 30
+
+    def neumann(ov, kappa):
+        x = ov.states['x'][0, :]
+        lo = ops.concatenate((x[:1], x[:-1]))             # ghost = first cell
+        hi = ops.concatenate((x[1:], x[-1:]))             # ghost = last cell
+        ov.d_states['x'] = (kappa * (lo - 2.0 * x + hi)).reshape(1, -1)
+    t = TracedGridRHS(neumann, (2.5,), {}, 'x', nx, [])
+    tab = t.tracer.coefficient_table()
+    x = np.random.default_rng(5).uniform(-1, 1, nx)
+    xe = np.concatenate(([0.0], x, [0.0]))
+    for k in (0, 1, nx - 2, nx - 1):
+        env = {('gx', -1): xe[k], ('gx', 0): xe[k + 1], ('gx', 1): xe[k + 2]}
+        env.update({('gc', q): tab[q, k] for q in range(tab.shape[0])})
+        left = x[0] if k == 0 else x[k - 1]
+        right = x[-1] if k == nx - 1 else x[k + 1]
+        assert _evaluate(t.f, env) == pytest.approx(2.5 * (left - 2.0 * x[k] + right), rel=1e-13, abs=1e-14)
+        # the diagonal the reverse sweep uses sees the mirror term: -2 kappa inside, -kappa at the two ends
+        assert _evaluate(t.dg, env) == pytest.approx(-2.5 if k in (0, nx - 1) else -5.0, rel=1e-13)
+
+    def periodic(ov):
+        x = ov.states['x'][0, :]
+        ov.d_states['x'] = (ops.concatenate((x[-1:], x[:-1])) - x).reshape(1, -1)
+    with pytest.raises(NotImplementedError, match='three-point stencil'):
+        TracedGridRHS(periodic, (), {}, 'x', nx, [])
