@@ -44,7 +44,7 @@ static int grid_plugin_no_colloc(const oz_problem*, int, size_t*, const void*, c
 extern "C" __attribute__((visibility("default"))) void oz_plugin_describe(oz_plugin_info* out) {
     out->abi = OZ_PLUGIN_ABI;
     out->d = 1;
-    out->P = oz::GridTraced<double>::HAS_U ? 1 : 0;
+    out->P = oz::GridTraced<double>::P;
     out->S = oz::GridTraced<double>::NCOEF;
     out->nprof = 0;
     out->nfield = oz::GridTraced<double>::NFIELD;

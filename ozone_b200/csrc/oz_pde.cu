@@ -13,7 +13,8 @@ template <typename T_>
 struct DiffusionReaction {
     using T = T_;
     static constexpr int NCOEF = 0;
-    static constexpr bool WINDOW = true, HAS_U = true;
+    static constexpr int P = 1;
+    static constexpr bool WINDOW = true;
     T inv_dx2, beta_t, beta_u, gamma, bt_emg;
     long long h_lo, h_hi;  // global cell range where the control acts
 
@@ -32,19 +33,20 @@ struct DiffusionReaction {
     OZ_D T stage_u(T ulo, T du, T c) const { return beta_u * (ulo + c * du); }   // beta_U * u at the stage abscissa
     // x_j' and d(reaction + transfer)/dx from ONE exponential (the reverse step needs both at every stage)
     template <bool WITH_DIAG>
-    OZ_D T f(T xl, T x, T xr, T mask, const T*, T bu_ui, const T* etab, T& dg) const {
+    OZ_D T f(T xl, T x, T xr, T mask, const T*, const T* bu_u, const T* etab, T& dg) const {
+        const T bu_ui = bu_u[0];
         const T q = pde_rcp(T(1) + x);
         const T ex = beta_t * pde_exp(-gamma * q, etab);
         if constexpr (WITH_DIAG) dg = ex * gamma * q * q - beta_u;
         return (xl - T(2) * x + xr) * inv_dx2 + ex - bt_emg + (mask * bu_ui - beta_u * x);
     }
     OZ_D T jt(T gl, T g, T gr, T dg, const T*) const { return (gl - T(2) * g + gr) * inv_dx2 + dg * g; }   // the stencil is symmetric
-    OZ_D T du(T mask, const T*) const { return mask; }
+    OZ_D T du(T mask, const T*, int) const { return mask; }
     OZ_D T du_scale() const { return beta_u; }
     OZ_D T q(T y, const T*) const { return y * y; }
     OZ_D T dq(T y, const T*) const { return y; }
-    OZ_D T ucost(T own, T u) const { return own * T(20) * u * u; }
-    OZ_D T ducost(T fb, T u) const { return T(40) * fb * u; }
+    OZ_D T ucost(T own, const T* u) const { return own * T(20) * u[0] * u[0]; }
+    OZ_D T ducost(T fb, const T* u, int) const { return T(40) * fb * u[0]; }
 };
 
 int pde_dispatch(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {

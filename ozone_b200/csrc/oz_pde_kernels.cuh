@@ -40,6 +40,7 @@ constexpr int kPdeCpt = OZ_PDE_CPT;                // cells per thread
 constexpr int kPdeExt = kPdeBlock * kPdeCpt;      // cells per CTA including halos
 constexpr int kPdeLine = kPdeExt + 2;             // one shared-memory line: the tile plus a zero cell at either end
 constexpr int kPdeFuse = OZ_PDE_FUSE;
+constexpr int kPdeMaxP = 4;                       // controls of a grid model
 #ifndef OZ_PDE_FUSE_ADJ   /* reverse steps per launch */
 #define OZ_PDE_FUSE_ADJ 2
 #endif
@@ -64,13 +65,13 @@ constexpr int kPdeFuseAdj = OZ_PDE_FUSE_ADJ;
 //   using T;                                        arithmetic type
 //   static constexpr int NCOEF;                     per-cell coefficient fields read from HBM (a.coef, [NCOEF][nx_global])
 //   static constexpr bool WINDOW;                   the control acts on the index window [h_lo, h_hi) (members of M)
-//   static constexpr bool HAS_U;                    there is a (scalar, batch-shared) dynamic parameter
-//   T stage_u(ulo, du, c)                           the control at a stage abscissa (CTA-uniform)
-//   template <bool WITH_DIAG> T f(xl, x, xr, mask, coef, us, etab, dg)    x_j' and (WITH_DIAG) dg = what jt() needs
+//   static constexpr int P;                         scalar, batch-shared dynamic parameters (controls), 0 .. kPdeMaxP
+//   T stage_u(ulo, du, c)                           one control at a stage abscissa (CTA-uniform)
+//   template <bool WITH_DIAG> T f(xl, x, xr, mask, coef, us, etab, dg)    x_j' and (WITH_DIAG) dg = what jt() needs; us[P]
 //   T jt(gl, g, gr, dg, coef)                       (J^T G)_j from G_{j-1}, G_j, G_{j+1}
-//   T du(mask, coef), T du_scale()                  d x_j' / d u = du * du_scale (must not depend on the state)
+//   T du(mask, coef, q), T du_scale()               d x_j' / d u_q = du * du_scale (must not depend on the state)
 //   T q(y, coef), T dq(y, coef)                     integrand of the field output and its derivative
-//   T ucost(own, u), T ducost(fb, u)                the control's own term in the field output and its derivative
+//   T ucost(own, u), T ducost(fb, u, q)             the controls' own term in the field output (u[P]) and its derivative
 template <class M>
 struct PdeArgs {
     using T = typename M::T;
@@ -91,7 +92,7 @@ struct PdeArgs {
     T* rows_out;         // optional: state after fused step j goes to rows_out + j * row_stride
     long long row_stride;
     const T* h;          // &h[k]: fused step j uses h[j]
-    const T* u_lo;       // &p[k], &p[k+1]: fused step j uses u_lo[j], u_hi[j]
+    const T* u_lo;       // &p[k][0], &p[k+1][0] (rows of P controls): fused step j uses u_lo[j * P + q], u_hi[j * P + q]
     const T* u_hi;
     T* part_sq;          // partial sums of the new state squared over owned cells, row j (of sq_stride) per fused step, or nullptr
     long long sq_stride;
@@ -105,8 +106,9 @@ struct PdeArgs {
     const T* field_bar;  // device scalar (or nullptr): cotangent of the field output
     T fb_scale;          // d field / d y_j = field_bar * fb_scale * dq(y_j)
     T* part_h;           // [ncta]
-    T* part_ulo;         // [ncta]
-    T* part_uhi;         // [ncta]
+    T* part_ulo;         // [P][part_pstride]: control q's partials of this launch start at q * part_pstride
+    T* part_uhi;
+    long long part_pstride;
 };
 
 template <typename T>
@@ -188,17 +190,22 @@ struct PdeTile {
 // `line2` holds two lines used alternately: stage i+1 may overwrite its line while slower warps still read
 // stage i's, so one barrier per stencil application is enough.
 template <class M, int S, bool WITH_DIAG, bool EDGE, int CPT>
-OZ_D void pde_stages(const PdeArgs<M>& a, const PdeTile<M, EDGE, CPT>& tl, typename M::T h, typename M::T ulo,
-                     typename M::T uhi, const typename M::T* yv, typename M::T (*F)[CPT], typename M::T (*Dg)[CPT],
+OZ_D void pde_stages(const PdeArgs<M>& a, const PdeTile<M, EDGE, CPT>& tl, typename M::T h, const typename M::T* ulo,
+                     const typename M::T* uhi, const typename M::T* yv, typename M::T (*F)[CPT], typename M::T (*Dg)[CPT],
                      typename M::T* line2, const typename M::T* etab, int phase = 0) {
     using T = typename M::T;
+    constexpr int P1 = M::P > 0 ? M::P : 1;
     const Tableau<T>& tab = a.tab;
-    const T du = uhi - ulo;
+    T du[P1];
+#pragma unroll
+    for (int q = 0; q < P1; ++q) du[q] = uhi[q] - ulo[q];
 #pragma unroll
     for (int i = 0; i < S; ++i) {
         T* line = line2 + ((i + phase) & 1) * (kPdeBlock * CPT + 2);   // phase: stages done before this call (keeps the lines alternating)
         T Yi[CPT];
-        const T bu_ui = a.rhs.stage_u(ulo, du, tab.C[i]);   // the control at the stage abscissa (times beta_U for the built-in model)
+        T bu_ui[P1];                                       // the controls at the stage abscissa (times beta_U for the built-in model)
+#pragma unroll
+        for (int q = 0; q < P1; ++q) bu_ui[q] = a.rhs.stage_u(ulo[q], du[q], tab.C[i]);
 #pragma unroll
         for (int m = 0; m < CPT; ++m) Yi[m] = yv[m];
 #pragma unroll
@@ -282,7 +289,14 @@ OZ_D void pde_step_body(const PdeArgs<M>& a, long long base, typename M::T* line
 #pragma unroll
     for (int m = 0; m < CPT; ++m) yv[m] = tl.in(m) ? __ldg(a.y_in + base + threadIdx.x + m * kPdeBlock) : T(0);
     for (int j = 0; j < a.nsub; ++j) {
-        const T h = __ldg(a.h + j), ulo = M::HAS_U ? __ldg(a.u_lo + j) : T(0), uhi = M::HAS_U ? __ldg(a.u_hi + j) : T(0);
+        const T h = __ldg(a.h + j);
+        T ulo[M::P > 0 ? M::P : 1], uhi[M::P > 0 ? M::P : 1];
+        ulo[0] = uhi[0] = T(0);
+#pragma unroll
+        for (int q = 0; q < M::P; ++q) {
+            ulo[q] = __ldg(a.u_lo + j * M::P + q);
+            uhi[q] = __ldg(a.u_hi + j * M::P + q);
+        }
         pde_stages<M, S, false, EDGE, CPT>(a, tl, h, ulo, uhi, yv, F, nullptr, line2, etab, j * S);
         const bool last = j == a.nsub - 1;
         T* dst = a.rows_out ? a.rows_out + j * a.row_stride : (last ? a.y_out : nullptr);
@@ -375,12 +389,22 @@ OZ_D void pde_adjoint_body(const PdeArgs<M>& a, long long base, typename M::T* l
         const T* yrow = a.y_in - j * a.row_stride;
 #pragma unroll
         for (int m = 0; m < CPT; ++m) yv[m] = tl.in(m) ? __ldg(yrow + base + threadIdx.x + m * kPdeBlock) : T(0);
-        const T h = __ldg(a.h - j), ulo = M::HAS_U ? __ldg(a.u_lo - j) : T(0), uhi = M::HAS_U ? __ldg(a.u_hi - j) : T(0);
+        const T h = __ldg(a.h - j);
+        constexpr int P1 = M::P > 0 ? M::P : 1;
+        T ulo[P1], uhi[P1];
+        ulo[0] = uhi[0] = T(0);
+#pragma unroll
+        for (int q = 0; q < M::P; ++q) {
+            ulo[q] = __ldg(a.u_lo - j * M::P + q);
+            uhi[q] = __ldg(a.u_hi - j * M::P + q);
+        }
         pde_stages<M, S, true, EDGE, CPT>(a, tl, h, ulo, uhi, yv, F, Dg, line2, etab);
 
         // transposed stage chain:  W_i = b_i lam + sum_{j>i} a_ji Ybar_j,  G_i = h W_i,  Ybar_i = J(Y_i)^T G_i
         // h_bar = sum_i W_i . F_i (no division by h);  u_bar parts from beta_U H . G_i
-        T u_lo_acc = T(0), u_hi_acc = T(0), h_acc = T(0);
+        T u_lo_acc[P1], u_hi_acc[P1], h_acc = T(0);
+#pragma unroll
+        for (int q = 0; q < P1; ++q) u_lo_acc[q] = u_hi_acc[q] = T(0);
 #pragma unroll
         for (int i = S - 1; i >= 0; --i) {
             T* line = line2 + ((S + (S - 1 - i)) & 1) * (kPdeBlock * CPT + 2);   // keeps alternating after the S forward stages
@@ -395,12 +419,16 @@ OZ_D void pde_adjoint_body(const PdeArgs<M>& a, long long base, typename M::T* l
                     for (int m = 0; m < CPT; ++m) G[m] += aqi * Yb[q][m];
                 }
             }
-            T usum = T(0);
+            T usum[P1];
+#pragma unroll
+            for (int q = 0; q < P1; ++q) usum[q] = T(0);
 #pragma unroll
             for (int m = 0; m < CPT; ++m) {
                 if (owned[m]) h_acc += G[m] * F[i][m];
                 G[m] = (EDGE && !tl.inside[m]) ? T(0) : h * G[m];
-                if (owned[m]) usum += a.rhs.du(tl.mask(m), tl.coef[m]) * G[m];
+                if (owned[m])
+#pragma unroll
+                    for (int q = 0; q < M::P; ++q) usum[q] += a.rhs.du(tl.mask(m), tl.coef[m], q) * G[m];
                 line[1 + threadIdx.x + m * kPdeBlock] = G[m];
             }
             __syncthreads();
@@ -410,9 +438,12 @@ OZ_D void pde_adjoint_body(const PdeArgs<M>& a, long long base, typename M::T* l
                 const T v = a.rhs.jt(line[e], G[m], line[e + 2], Dg[i][m], tl.coef[m]);
                 Yb[i][m] = (EDGE && !tl.inside[m]) ? T(0) : v;
             }
-            usum *= a.rhs.du_scale();
-            u_hi_acc += tab.C[i] * usum;
-            u_lo_acc += usum - tab.C[i] * usum;
+#pragma unroll
+            for (int q = 0; q < M::P; ++q) {
+                usum[q] *= a.rhs.du_scale();
+                u_hi_acc[q] += tab.C[i] * usum[q];
+                u_lo_acc[q] += usum[q] - tab.C[i] * usum[q];
+            }
         }
         const bool last = j == a.nsub - 1;
         const T* hb = a.hist_bar_k ? a.hist_bar_k - j * a.nx : nullptr;
@@ -431,10 +462,13 @@ OZ_D void pde_adjoint_body(const PdeArgs<M>& a, long long base, typename M::T* l
         const long long row = -(long long)j * a.adj_stride + blockIdx.x;
         T s = block_sum(h_acc, red);
         if (threadIdx.x == 0) a.part_h[row] = s;
-        s = block_sum(u_lo_acc, red);
-        if (threadIdx.x == 0) a.part_ulo[row] = s;
-        s = block_sum(u_hi_acc, red);
-        if (threadIdx.x == 0) a.part_uhi[row] = s;
+#pragma unroll
+        for (int q = 0; q < M::P; ++q) {
+            s = block_sum(u_lo_acc[q], red);
+            if (threadIdx.x == 0) a.part_ulo[q * a.part_pstride + row] = s;
+            s = block_sum(u_hi_acc[q], red);
+            if (threadIdx.x == 0) a.part_uhi[q * a.part_pstride + row] = s;
+        }
     }
 }
 
@@ -484,8 +518,8 @@ __global__ void __launch_bounds__(256) pde_field_kernel(const M rhs, const typen
     T acc = T(0);
     for (long long q = (long long)k0 * ncta + threadIdx.x; q < (long long)nt * ncta; q += blockDim.x) acc += part_sq[q];
     acc *= scale;
-    if (M::HAS_U)
-        for (int k = k0 + threadIdx.x; k < nt; k += blockDim.x) acc += rhs.ucost(own_u, u[k]);
+    if (M::P > 0)
+        for (int k = k0 + threadIdx.x; k < nt; k += blockDim.x) acc += rhs.ucost(own_u, u + (long long)k * M::P);
     const T s = block_sum(acc, red);
     if (threadIdx.x == 0) field[0] = s;
 }
@@ -497,22 +531,29 @@ __global__ void __launch_bounds__(256) pde_grads_kernel(const M rhs, int n, long
                                                         const typename M::T* __restrict__ part_uhi,
                                                         const typename M::T* __restrict__ u,
                                                         const typename M::T* __restrict__ field_bar, int k_cost_end,
-                                                        typename M::T* __restrict__ h_bar, typename M::T* __restrict__ u_bar) {
+                                                        long long pstride, typename M::T* __restrict__ h_bar,
+                                                        typename M::T* __restrict__ u_bar) {
     using T = typename M::T;
     __shared__ T red[32];
     const int k = blockIdx.x;  // 0..n
+    const int q = blockIdx.y;  // control (one row of blocks when the model has none: h_bar only)
+    constexpr int P1 = M::P > 0 ? M::P : 1;
+    part_ulo += q * pstride;
+    part_uhi += q * pstride;
     T ah = T(0), au = T(0);
     for (long long c = threadIdx.x; c < ncta; c += blockDim.x) {
         if (k < n) {
             ah += part_h[(long long)k * ncta + c];
-            au += part_ulo[(long long)k * ncta + c];
+            if (M::P > 0) au += part_ulo[(long long)k * ncta + c];
         }
-        if (k > 0) au += part_uhi[(long long)(k - 1) * ncta + c];
+        if (M::P > 0 && k > 0) au += part_uhi[(long long)(k - 1) * ncta + c];
     }
     T s = block_sum(ah, red);
-    if (threadIdx.x == 0 && k < n && h_bar) h_bar[k] = s;
+    if (threadIdx.x == 0 && k < n && h_bar && q == 0) h_bar[k] = s;
     s = block_sum(au, red);
-    if (threadIdx.x == 0 && u_bar) u_bar[k] = s + ((field_bar && k < k_cost_end) ? rhs.ducost(field_bar[0], u[k]) : T(0));
+    if (M::P > 0)
+        if (threadIdx.x == 0 && u_bar)
+            u_bar[(long long)k * P1 + q] = s + ((field_bar && k < k_cost_end) ? rhs.ducost(field_bar[0], u + (long long)k * P1, q) : T(0));
 }
 
 template <class M, int S>
@@ -543,7 +584,7 @@ struct PdeLayout {
 };
 
 template <int S>
-static PdeLayout pde_layout(const oz_problem* pb) {
+static PdeLayout pde_layout(const oz_problem* pb, int P) {
     PdeLayout L;
     L.nx = pb->d_override;
     // Full tiles; the hardware scheduler backfills the ragged last wave better than equalised smaller
@@ -606,8 +647,8 @@ static PdeLayout pde_layout(const oz_problem* pb) {
     L.off_lam1 = L.off_lam0 + vec;
     L.off_ph = L.off_lam1 + vec;
     L.off_pulo = L.off_ph + (size_t)pb->n * L.ncta_a;
-    L.off_puhi = L.off_pulo + (size_t)pb->n * L.ncta_a;
-    L.total_adj = L.off_puhi + (size_t)pb->n * L.ncta_a;
+    L.off_puhi = L.off_pulo + (size_t)P * pb->n * L.ncta_a;
+    L.total_adj = L.off_puhi + (size_t)P * pb->n * L.ncta_a;
     return L;
 }
 
@@ -635,7 +676,8 @@ template <class M, int S>
 static int pde_forward(const oz_problem* pb) {
     using T = typename M::T;
     OZ_REQUIRE(M::NCOEF == 0 || pb->th, "this grid right-hand side needs its coefficient fields (th)");
-    const PdeLayout L = pde_layout<S>(pb);
+    OZ_REQUIRE(M::P == 0 || pb->p, "this grid right-hand side needs its dynamic parameters (p)");
+    const PdeLayout L = pde_layout<S>(pb, M::P);
     OZ_REQUIRE((size_t)L.total_fwd * sizeof(T) <= pb->ws_bytes && pb->ws, "grid forward workspace too small: need %zu bytes, got %zu",
                (size_t)L.total_fwd * sizeof(T), pb->ws_bytes);
     cudaStream_t st = (cudaStream_t)pb->stream;
@@ -680,8 +722,8 @@ static int pde_forward(const oz_problem* pb) {
         a.y_out = hist ? nullptr : out;
         a.rows_out = hist ? hist + (size_t)(k + 1) * nx : nullptr;   // history: every fused step is a row
         a.h = h + k;
-        a.u_lo = u + k;
-        a.u_hi = u + k + 1;
+        a.u_lo = u + (size_t)k * M::P;
+        a.u_hi = u + (size_t)(k + 1) * M::P;
         a.part_sq = part_sq ? part_sq + (size_t)(k + 1) * L.ncta_f : nullptr;
         launch_pde_step<M, S>(L.cpt_f, (unsigned)L.ncta_f, st, a);
         if (hist && at_ckpt)
@@ -708,7 +750,7 @@ template <class M, int S>
 static int pde_adjoint(const oz_problem* pb) {
     using T = typename M::T;
     OZ_REQUIRE(M::NCOEF == 0 || pb->th, "this grid right-hand side needs its coefficient fields (th)");
-    const PdeLayout L = pde_layout<S>(pb);
+    const PdeLayout L = pde_layout<S>(pb, M::P);
     OZ_REQUIRE((size_t)L.total_adj * sizeof(T) <= pb->ws_bytes && pb->ws, "grid adjoint workspace too small: need %zu bytes, got %zu",
                (size_t)L.total_adj * sizeof(T), pb->ws_bytes);
     OZ_REQUIRE(pb->hist || pb->ckpt, "adjoint needs hist or ckpt");
@@ -756,8 +798,8 @@ static int pde_adjoint(const oz_problem* pb) {
                 f.rows_out = seg + (size_t)(q + 1) * vec;
                 f.row_stride = (long long)vec;
                 f.h = h + lo + q;
-                f.u_lo = u + lo + q;
-                f.u_hi = u + lo + q + 1;
+                f.u_lo = u + (size_t)(lo + q) * M::P;
+                f.u_hi = u + (size_t)(lo + q + 1) * M::P;
                 f.part_sq = nullptr;
                 launch_pde_step<M, S>(L.cpt_f, (unsigned)L.ncta_f, st, f);
                 q += nsub;
@@ -775,8 +817,9 @@ static int pde_adjoint(const oz_problem* pb) {
             a.lam_out = (kl == 0 && pb->y0_bar) ? (T*)pb->y0_bar : lam[cur ^ 1];
             a.hist_bar_k = hist_bar ? hist_bar + (size_t)k * nx : nullptr;
             a.h = h + k;
-            a.u_lo = u + k;
-            a.u_hi = u + k + 1;
+            a.u_lo = u + (size_t)k * M::P;
+            a.u_hi = u + (size_t)(k + 1) * M::P;
+            a.part_pstride = (long long)n * L.ncta_a;
             a.part_h = ph + (size_t)k * L.ncta_a;
             a.part_ulo = pulo + (size_t)k * L.ncta_a;
             a.part_uhi = puhi + (size_t)k * L.ncta_a;
@@ -788,7 +831,8 @@ static int pde_adjoint(const oz_problem* pb) {
     OZ_CUDA_CHECK(cudaGetLastError());
     if (pb->h_bar || pb->p_bar) {
         const int k_cost_end = (pb->grid_flags & OZ_GRID_NO_CONTROL_COST) ? 0 : ((pb->grid_flags & OZ_GRID_SKIP_TERMINAL_FIELD) ? n : n + 1);
-        pde_grads_kernel<M><<<n + 1, 256, 0, st>>>(a.rhs, n, L.ncta_a, ph, pulo, puhi, u, a.field_bar, k_cost_end, (T*)pb->h_bar, (T*)pb->p_bar);
+        pde_grads_kernel<M><<<dim3(n + 1, M::P > 0 ? M::P : 1), 256, 0, st>>>(a.rhs, n, L.ncta_a, ph, pulo, puhi, u, a.field_bar, k_cost_end,
+                                                                           (long long)n * L.ncta_a, (T*)pb->h_bar, (T*)pb->p_bar);
         OZ_CUDA_CHECK(cudaGetLastError());
     }
     return 0;
@@ -807,10 +851,10 @@ static int pde_by_stage(const oz_problem* pb, int mode, size_t* ws_bytes) {
             if (mode == TM_FORWARD) return pde_forward<M, SS>(pb);                   \
             if (mode == TM_ADJOINT) return pde_adjoint<M, SS>(pb);                   \
             if (mode == TM_ADJOINT_WS) {                                             \
-                *ws_bytes = pde_layout<SS>(pb).total_adj * sizeof(T);                \
+                *ws_bytes = pde_layout<SS>(pb, M::P).total_adj * sizeof(T);                \
                 return 0;                                                            \
             }                                                                        \
-            *ws_bytes = pde_layout<SS>(pb).total_fwd * sizeof(T);                    \
+            *ws_bytes = pde_layout<SS>(pb, M::P).total_fwd * sizeof(T);                    \
             return 0;                                                                \
         }
     OZ_PDE_CASE(1)

@@ -141,7 +141,8 @@ class GridShard:
         self.slab = sl = make_slab(nx, rank, world, 2 * s * num_inner)
         self.dtype, self.device = dtype, torch.device(device)
         self.h = h.to(self.device, dtype).contiguous()
-        self.u = u.to(self.device, dtype).reshape(n + 1, 1).contiguous()
+        self.u = u.to(self.device, dtype).reshape(n + 1, -1).contiguous()       # (n + 1, P): one row of controls per time point
+        P = self.u.shape[1]
         self.rhs_cfg = tuple(rhs_cfg or ())
         self.channel = channel
         self.traced, self.coef = traced, None
@@ -153,7 +154,7 @@ class GridShard:
         self.ckpts[0] = y0_global[sl.ext_lo:sl.ext_hi].to(self.device, dtype).reshape(-1, 1)
         self.lam = [new(ne, 1), new(ne, 1)]
         self.field_seg, self.field_bar = new(nseg, 1, 1), new(1, 1)
-        self.h_bar, self.u_seg = new(n), new(nseg, ni + 1, 1)
+        self.h_bar, self.u_seg = new(n), new(nseg, ni + 1, P)
         self._final_bar = None
         # descriptors
         self.pb_f, self.pb_a = [], []
@@ -268,8 +269,9 @@ class GridShard:
     def results(self):
         """Local (not yet all-reduced) field, h_bar, u_bar and the owned parts of the final state and of y0_bar."""
         n, ni, nseg = self.n, self.ni, self.nseg
-        u_bar = torch.zeros(n + 1, 1, dtype=self.dtype, device=self.device)
-        u_bar[:n].view(nseg, ni, 1).add_(self.u_seg[:, :ni])
+        P = self.u.shape[1]
+        u_bar = torch.zeros(n + 1, P, dtype=self.dtype, device=self.device)
+        u_bar[:n].view(nseg, ni, P).add_(self.u_seg[:, :ni])
         u_bar[ni::ni].add_(self.u_seg[:, ni])            # the last grid point of a segment is the first of the next
         return dict(field=self.field_seg.sum(dim=0), h_bar=self.h_bar, u_bar=u_bar,
                     final_owned=self.owned(self.ext), y0_bar_owned=self.owned(self.lam_cur))

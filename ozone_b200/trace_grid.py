@@ -18,10 +18,10 @@ system, ``exp`` and reciprocals through the same fast device routines -- and com
 (``csrc/oz_grid_plugin_impl.cuh``), cached under ``build/plugins``.
 
 What the kernels can express, and what is refused with an error that says so:
-  * one state (the grid), at most one scalar dynamic parameter, explicit methods, TimeMarching / TimeMarchingCheckpoints;
+  * one state (the grid), up to four scalar dynamic parameters, explicit methods, TimeMarching / TimeMarchingCheckpoints;
   * a three-point stencil with constant (zero or non-zero) or reflecting boundary values whose NEIGHBOUR terms are linear, with weights that are constants or
     coefficient fields (variable diffusivity, upwind advection); the cell's own value may enter in any smooth way;
-  * the dynamic parameter enters linearly (its weight may be a coefficient field);
+  * the dynamic parameters enter linearly (their weights may be coefficient fields);
   * at most one field output of the form  const * sum_cells q(x, coefficients) + r(parameter); no profile outputs;
   * captured data must be floats or numpy arrays (they are constants of the generated code / coefficient fields), not
     tensors to differentiate.
@@ -403,11 +403,12 @@ class TracedGridRHS:
     kind = 'grid'
     config_parameters = ()
     COEF_NAME = '_grid_coefficients'
+    MAX_PARAMS = 4                 # kPdeMaxP in csrc/oz_pde_kernels.cuh
 
     def __init__(self, f, args, kwargs, state_name: str, nx: int, param_names):
         from .func_wrapper import ODEVars
-        if len(param_names) > 1:
-            raise NotImplementedError('a grid right-hand side takes at most one (scalar) dynamic parameter; got '
+        if len(param_names) > self.MAX_PARAMS:
+            raise NotImplementedError(f'a grid right-hand side takes at most {self.MAX_PARAMS} (scalar) dynamic parameters; got '
                                       f'{list(param_names)}')
         self.state_name, self.nx = state_name, int(nx)
         self.param_names = list(param_names)
@@ -482,13 +483,13 @@ class TracedGridRHS:
         # (J^T G)_j = (weight of the right neighbour in cell j-1) G_{j-1} + dg_j G_j + (weight of the left neighbour in cell j+1) G_{j+1}
         self.wr_of_left, self.wl_of_right = tr.shift(wr, -1), tr.shift(wl, 1)
         self.dg = diff(self.f, xc, memo)
-        self.du = Expr.const(0.0)
-        if self.param_names:
-            u = leaf('p', 0)
-            self.du = diff(self.f, u, memo)
-            if any(l.op != 'gc' for l in leaves_of(self.du)):
-                raise NotImplementedError('the dynamic parameter must enter the state derivative linearly, with a constant or '
-                                          'per-cell weight')
+        self.du = []
+        for q, name in enumerate(self.param_names):
+            d = diff(self.f, leaf('p', q), memo)
+            if any(l.op != 'gc' for l in leaves_of(d)):
+                raise NotImplementedError(f"dynamic parameter '{name}' must enter the state derivative linearly, with a constant "
+                                          f'or per-cell weight')
+            self.du.append(d)
         # field output: J = sum_k a_k sum_cells q_k + r(u)
         self.q, self.r = Expr.const(0.0), Expr.const(0.0)
         if self.J is not None:
@@ -501,7 +502,7 @@ class TracedGridRHS:
             if any(l.op != 'p' for l in leaves_of(self.r)):
                 raise NotImplementedError('a field output must be  const * sum_cells(...) + r(parameter)')
         self.dq = diff(self.q, xc, memo)
-        self.dr = diff(self.r, leaf('p', 0), memo) if self.param_names else Expr.const(0.0)
+        self.dr = [diff(self.r, leaf('p', q), memo) for q in range(len(self.param_names))]
 
     # ---- code generation
     @staticmethod
@@ -521,7 +522,7 @@ class TracedGridRHS:
             elif op == 'gc':
                 s = f'c[{e.idx}]'
             elif op == 'p':
-                s = 'u'
+                s = f'u[{e.idx}]'
             elif op == 'v':                       # arguments of jt()
                 s = ('gl', 'g', 'gr', 'dg')[e.idx]
             else:
@@ -562,11 +563,13 @@ class TracedGridRHS:
         only = self._block([('return', self.f)], fast=True)
         jt = self._block([('return', self.wr_of_left * leaf('v', 0) + self.wl_of_right * leaf('v', 2) + leaf('v', 1) * leaf('v', 3))],
                          fast=False)
-        du = self._block([('return', self.du)], fast=False)
+        per_q = lambda exprs, prefix: '\n'.join(
+            f'        if (q == {q}) {{\n' + self._block([(prefix, e)], fast=False) + '\n        }' for q, e in enumerate(exprs))
+        du = per_q(self.du, 'return') + '\n        return T(0);'
         q = self._block([('return', self.q)], fast=False)
         dq = self._block([('return', self.dq)], fast=False)
         r = self._block([('return own *', self.r)], fast=False)
-        dr = self._block([('return fb *', self.dr)], fast=False)
+        dr = per_q(self.dr, 'return fb *') + '\n        return T(0);'
         return f'''// generated by ozone_b200/trace_grid.py from a Python right-hand side callback over a 1-D grid
 #include "oz_pde_kernels.cuh"
 namespace oz {{
@@ -574,14 +577,15 @@ template <typename T_>
 struct GridTraced {{
     using T = T_;
     static constexpr int NCOEF = {K}, NFIELD = {len(self.field_decl)};
-    static constexpr bool WINDOW = false, HAS_U = {'true' if self.param_names else 'false'};
+    static constexpr int P = {len(self.param_names)};
+    static constexpr bool WINDOW = false;
     void configure(const oz_problem*, long long, T* field_scale, T* fb_scale) {{
         *field_scale = T(1);
         *fb_scale = T(1);
     }}
     OZ_D T stage_u(T ulo, T du, T cs) const {{ return ulo + cs * du; }}
     template <bool WITH_DIAG>
-    OZ_D T f(T xl, T x, T xr, T, const T* c, T u, const T* etab, T& dg) const {{
+    OZ_D T f(T xl, T x, T xr, T, const T* c, const T* u, const T* etab, T& dg) const {{
         if constexpr (WITH_DIAG) {{
 {both}
         }} else {{
@@ -591,7 +595,7 @@ struct GridTraced {{
     OZ_D T jt(T gl, T g, T gr, T dg, const T* c) const {{
 {jt}
     }}
-    OZ_D T du(T, const T* c) const {{
+    OZ_D T du(T, const T* c, int q) const {{
 {du}
     }}
     OZ_D T du_scale() const {{ return T(1); }}
@@ -601,10 +605,10 @@ struct GridTraced {{
     OZ_D T dq(T x, const T* c) const {{
 {dq}
     }}
-    OZ_D T ucost(T own, T u) const {{
+    OZ_D T ucost(T own, const T* u) const {{
 {r}
     }}
-    OZ_D T ducost(T fb, T u) const {{
+    OZ_D T ducost(T fb, const T* u, int q) const {{
 {dr}
     }}
 }};

@@ -131,3 +131,47 @@ class DirichletHeatOracle(Rhs):
         hi = np.full_like(y, self.right)
         hi[:-1] = y[1:]
         return self.kappa * (lo - 2.0 * y + hi) - 0.5 * y ** 3
+
+
+def two_control_fields(nx):
+    z = (np.arange(nx) + 0.5) / nx
+    return dict(heater=np.exp(-60.0 * (z - 0.25) ** 2), cooler=np.exp(-60.0 * (z - 0.7) ** 2))
+
+
+def two_controls(ozone_vars, nx, kappa):
+    """x' = kappa (x[k-1] - 2 x[k] + x[k+1]) - x^3 + heat(t) a(z) - cool(t) b(z);  cost = sum x^2 / nx + heat^2 + 0.5 heat cool + 2 cool^2"""
+    fl = two_control_fields(nx)
+    x = ozone_vars.states['x'][0, :]
+    heat, cool = ozone_vars.dynamic_parameters['heat'], ozone_vars.dynamic_parameters['cool']
+    zero = np.zeros(1)
+    lap = csdl.concatenate((zero, x[:-1])) - 2.0 * x + csdl.concatenate((x[1:], zero))
+    ozone_vars.d_states['x'] = (kappa * lap - x ** 3 + csdl.expand(heat[0], (nx,)) * fl['heater']
+                                + csdl.expand(cool[0], (nx,)) * (-1.0 * fl['cooler'])).reshape(1, nx)
+    ozone_vars.field_outputs['cost'] = (csdl.sum(x * x) / nx + heat[0] * heat[0] + 0.5 * heat[0] * cool[0]
+                                        + 2.0 * cool[0] * cool[0]).reshape(1, 1)
+
+
+class TwoControlsOracle(Rhs):
+    name = 'two_controls'
+    P, S, NFIELD = 2, 0, 1
+
+    def __init__(self, nx, kappa):
+        self.D = self.nx = nx
+        self.kappa = kappa
+        self.fl = two_control_fields(nx)
+
+    def _col(self, a, like):
+        return a.reshape((self.nx,) + (1,) * (like.ndim - 1))
+
+    def f(self, y, p, th):
+        lo = np.zeros_like(y)
+        lo[1:] = y[:-1]
+        hi = np.zeros_like(y)
+        hi[:-1] = y[1:]
+        return (self.kappa * (lo - 2.0 * y + hi) - y ** 3 + self._col(self.fl['heater'], y) * p[0]
+                - self._col(self.fl['cooler'], y) * p[1])
+
+    def out(self, y, p, th):
+        J = np.sum(y * y, axis=0) / self.nx + p[0] * p[0] + 0.5 * p[0] * p[1] + 2.0 * p[1] * p[1]
+        shp = np.broadcast_shapes(y.shape[1:], p[0].shape)
+        return np.zeros((0,) + shp), np.broadcast_to(J, shp)[None]

@@ -271,3 +271,36 @@ def test_reflecting_boundaries_conserve_the_total_and_give_the_transposed_propag
     w = np.random.default_rng(9).standard_normal(nx)
     g, = torch.autograd.grad((out.final_states['T'] * var(w, False)).sum(), [T0])
     assert np.abs(g.cpu().numpy() - Rn.T @ w).max() < 1e-12
+
+
+@pytest.mark.parametrize('approach', ['history', 'checkpoints'])
+def test_two_dynamic_parameters_against_the_oracle(approach):
+    from oracle import integrators as I, adjoint as Adj
+    nx, n = 260, 12
+    kappa = 0.2 * nx * nx
+    rng = np.random.default_rng(21)
+    x0_np = 0.4 * np.sin(np.pi * (np.arange(nx) + 0.5) / nx)
+    heat_np, cool_np = rng.uniform(0.0, 3.0, size=n + 1), rng.uniform(0.0, 2.0, size=n + 1)
+    h_np = np.full(n, 1.0 / (nx * nx))
+    x0, heat, cool, h = var(x0_np), var(heat_np), var(cool_np), var(h_np)
+    prob = ozone.ODEProblem(ozone.methods.RK4(), TimeMarching() if approach == 'history' else TimeMarchingCheckpoints(num_checkpoints=3),
+                            verbose=False)
+    prob.add_state('x', x0, store_final=True)
+    prob.add_dynamic_parameter('heat', heat)
+    prob.add_dynamic_parameter('cool', cool)
+    prob.set_timespan(ozone.timespans.StepVector(start=0.0, step_vector=h))
+    prob.set_function(G.two_controls, nx=nx, kappa=kappa)
+    out = prob.solve()
+    assert prob.integrator.spec.info['P'] == 2
+    rhs = G.TwoControlsOracle(nx, kappa)
+    p_np = np.stack([heat_np, cool_np], axis=1)[:, :, None]
+    ref = I.time_marching(rhs, 'RK4', x0_np[:, None], h_np, p_np, None)
+    assert np.abs(out.final_states['x'].detach().cpu().numpy() - ref['final'][:, 0]).max() <= 1e-12 * np.abs(ref['final']).max()
+    assert float(out.field_outputs['cost'].sum().detach()) == pytest.approx(float(ref['field'][0, 0]), rel=1e-12)
+    fb = rng.standard_normal(nx)
+    loss = 0.9 * out.field_outputs['cost'].sum() + (out.final_states['x'] * var(fb, False)).sum()
+    g_heat, g_cool, g_h, g_x0 = torch.autograd.grad(loss, [heat, cool, h, x0])
+    g = Adj.tm_adjoint(rhs, 'RK4', x0_np[:, None], h_np, p_np, None, history=ref['history'], final_bar=fb[:, None],
+                       field_bar=np.full((1, 1), 0.9))
+    for mine, theirs in ((g_heat, g['p'][:, 0]), (g_cool, g['p'][:, 1]), (g_h, g['h']), (g_x0, g['y0'])):
+        assert np.abs(mine.cpu().numpy().ravel() - np.ravel(theirs)).max() <= 1e-10 * np.abs(theirs).max()

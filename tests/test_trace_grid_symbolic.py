@@ -121,7 +121,7 @@ def test_what_the_stencil_kernels_cannot_express_is_refused_with_the_reason():
         x = ov.states['x'][0, :]
         u = ov.dynamic_parameters['u']
         ov.d_states['x'] = (ops.expand(u[0] * u[0], (50,)) - x).reshape(1, -1)
-    with pytest.raises(NotImplementedError, match='parameter must enter'):
+    with pytest.raises(NotImplementedError, match='must enter the state derivative linearly'):
         _trace(parameter_squared)
 
     def captured_tensor(ov):
@@ -142,8 +142,8 @@ def test_what_the_stencil_kernels_cannot_express_is_refused_with_the_reason():
     with pytest.raises(KeyError):                         # the reference's own check (func_wrapper.py:28-53)
         _trace(missing_derivative)
 
-    with pytest.raises(NotImplementedError, match='at most one'):
-        _trace(lambda ov: None, params=('u', 'v'))
+    with pytest.raises(NotImplementedError, match='at most 4'):
+        _trace(lambda ov: None, params=('a', 'b', 'c', 'd', 'e'))
 
 
 def test_generated_grid_model_compiles_and_registers_without_a_gpu():
@@ -210,3 +210,16 @@ def test_reflecting_boundaries_are_an_indicator_field_times_the_boundary_cell_an
         ov.d_states['x'] = (ops.concatenate((x[-1:], x[:-1])) - x).reshape(1, -1)
     with pytest.raises(NotImplementedError, match='three-point stencil'):
         TracedGridRHS(periodic, (), {}, 'x', nx, [])
+
+
+def test_several_dynamic_parameters_each_get_their_own_weight_field():
+    nx = 48
+    t = TracedGridRHS(G.two_controls, (), dict(nx=nx, kappa=3.0), 'x', nx, ['heat', 'cool'])
+    assert len(t.du) == 2 and t.spec_info(nx)['P'] == 2
+    fl = G.two_control_fields(nx)
+    tab = t.tracer.coefficient_table()
+    for q, key in enumerate(('heater', 'cooler')):
+        l, = leaves_of(t.du[q])
+        assert l.op == 'gc' and np.array_equal(tab[l.idx], fl[key] * (1.0 if q == 0 else -1.0))
+    src = t.cuda_source()
+    assert 'static constexpr int P = 2' in src and 'if (q == 1)' in src and 'u[1]' in src
