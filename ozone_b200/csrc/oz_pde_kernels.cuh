@@ -61,7 +61,8 @@ constexpr int kPdeFuseAdj = OZ_PDE_FUSE_ADJ;
 // ---- the grid model ---------------------------------------------------------------------------------------------
 // Everything below is written against a model M: the built-in diffusion-reaction system (DiffusionReaction in oz_pde.cu)
 // or the functor ozone_b200/trace_grid.py generates from a Python callback.  A model describes ONE cell of a
-// three-point stencil with zero ghost cells whose neighbour weights are constants:
+// three-point stencil with zero ghost cells whose neighbour weights do not depend on the state (constants, or coefficient
+// fields; other boundary conditions are coefficient fields at the boundary cells, see trace_grid.py):
 //   using T;                                        arithmetic type
 //   static constexpr int NCOEF;                     per-cell coefficient fields read from HBM (a.coef, [NCOEF][nx_global])
 //   static constexpr bool WINDOW;                   the control acts on the index window [h_lo, h_hi) (members of M)
