@@ -643,7 +643,8 @@ struct GridTraced {{
             tmp = f'{so}.{os.getpid()}.tmp'
             open(cu, 'w').write(src)
             cmd = ['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-std=c++17', '-lineinfo',
-                   '--expt-relaxed-constexpr', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden', '-shared',
+                   '--expt-relaxed-constexpr', '-split-compile', '0', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden',
+                   '-shared',
                    f'-I{csrc}', *flags, cu, '-o', tmp, '-lcudart_static', '-lrt', '-lpthread', '-ldl']
             res = subprocess.run(cmd, capture_output=True, text=True)
             if res.returncode != 0:
