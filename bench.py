@@ -58,7 +58,7 @@ DEFAULT_WORKLOAD = 'van_der_pol_gl6_tm_adjoint_N65536_nt40'
 STATE_SIZE = {'van_der_pol': 3, 'lotka_volterra': 2, 'lunar_ascent': 7}     # packed state components per trajectory
 # compact entries of the default bench line (one short run each): the other BASELINE configs, driver-timed
 OTHER_WORKLOADS = ('lotka_volterra_rk4_tm_adjoint_N1M_nt101', 'diffusion_reaction_rk4_checkpoints_nx1M_n1024',
-                   'lunar_ascent_rk4_collocation_N16384_nt101')
+                   'diffusion_reaction_rk4_checkpoints_nx1M_n1024_traced', 'lunar_ascent_rk4_collocation_N16384_nt101')
 
 
 def workload_config(name, wl, world, newton_tol):
