@@ -6,22 +6,9 @@
 #pragma once
 #include <cstdarg>
 #include "oz_plugin.h"
+#include "oz_plugin_common.cuh"
 
 namespace oz {
-static thread_local char g_plugin_err[512] = "";
-void set_error(const char* fmt, ...) {
-    va_list ap;
-    va_start(ap, fmt);
-    vsnprintf(g_plugin_err, sizeof(g_plugin_err), fmt, ap);
-    va_end(ap);
-}
-int sm_count() {
-    int dev = 0, n = 0;
-    if (cudaGetDevice(&dev) != cudaSuccess || cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0)
-        return 148;
-    return n;
-}
-
 static int grid_plugin_tm(const oz_problem* pb, int mode, size_t* ws_bytes, const EvalArgs* ev) {
     if (int rc = pde_check(pb, mode, ev)) return rc;
     if constexpr (OZ_WANT_F64(true))

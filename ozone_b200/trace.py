@@ -381,6 +381,40 @@ def _arr(o):
     return np.asarray(o, dtype=np.float64) if not isinstance(o, np.ndarray) or o.dtype != object else o
 
 
+def build_and_register_plugin(src: str, flags, stem: str, what: str) -> int:
+    """nvcc the generated translation unit into ``build/plugins/<stem>_<hash>.so`` (cached: the hash covers the source, the
+    flags and every kernel template header) and register it with the library; returns the rhs_id."""
+    csrc = os.path.join(_HERE, 'csrc')
+    stamp = hashlib.sha256()
+    stamp.update(src.encode())
+    stamp.update(' '.join(flags).encode())
+    for fn in sorted(os.listdir(csrc)):                      # kernel templates are part of the plugin
+        if fn.endswith(('.cuh', '.h')):
+            stamp.update(open(os.path.join(csrc, fn), 'rb').read())
+    tag = stamp.hexdigest()[:20]
+    os.makedirs(PLUGIN_DIR, exist_ok=True)
+    so = os.path.join(PLUGIN_DIR, f'{stem}_{tag}.so')
+    if not os.path.exists(so):
+        # every rank under torchrun may build the same plugin at once: private file names, atomic publish
+        cu = os.path.join(PLUGIN_DIR, f'{stem}_{tag}.{os.getpid()}.cu')
+        tmp = f'{so}.{os.getpid()}.tmp'
+        open(cu, 'w').write(src)
+        cmd = ['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-std=c++17', '-lineinfo',
+               '--expt-relaxed-constexpr', '-split-compile', '0', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden',
+               '-shared', f'-I{csrc}', *flags, cu, '-o', tmp, '-lcudart_static', '-lrt', '-lpthread', '-ldl']
+        res = subprocess.run(cmd, capture_output=True, text=True)
+        if res.returncode != 0:
+            raise RuntimeError(f'nvcc failed on {what}:\n{res.stderr[-4000:]}')
+        os.replace(tmp, so)
+    rid = _REGISTERED.get(so)                 # one registration per shared object and process
+    if rid is None:
+        rid = nat.lib.oz_register_rhs_plugin(so.encode())
+        if rid < 0:
+            raise nat.OzError(f'oz_register_rhs_plugin: {nat.lib.oz_last_error().decode()}')
+        _REGISTERED[so] = rid
+    return rid
+
+
 # ================================================================================================
 class Tracer:
     """Records one call of a callback on symbolic inputs."""
@@ -638,38 +672,9 @@ struct RhsTraced {{
         key = (num_stages, bool(implicit), bool(fp64), kind)
         if key in self._plugins:
             return self._plugins[key]
-        src = self.cuda_source()
         flags = [f'-DOZ_ONLY_S={num_stages}', f'-DOZ_ONLY_IMPL={int(implicit)}', f'-DOZ_ONLY_F64={int(fp64)}',
                  f'-DOZ_ONLY_KIND={kind}']
-        csrc = os.path.join(_HERE, 'csrc')
-        stamp = hashlib.sha256()
-        stamp.update(src.encode())
-        stamp.update(' '.join(flags).encode())
-        for fn in sorted(os.listdir(csrc)):                      # kernel templates are part of the plugin
-            if fn.endswith(('.cuh', '.h')):
-                stamp.update(open(os.path.join(csrc, fn), 'rb').read())
-        tag = stamp.hexdigest()[:20]
-        os.makedirs(PLUGIN_DIR, exist_ok=True)
-        so = os.path.join(PLUGIN_DIR, f'oz_rhs_{tag}.so')
-        if not os.path.exists(so):
-            # every rank under torchrun may build the same plugin at once: private file names, atomic publish
-            cu = os.path.join(PLUGIN_DIR, f'oz_rhs_{tag}.{os.getpid()}.cu')
-            tmp = f'{so}.{os.getpid()}.tmp'
-            open(cu, 'w').write(src)
-            cmd = ['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-std=c++17', '-lineinfo',
-                   '--expt-relaxed-constexpr', '-split-compile', '0', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden',
-                   '-shared',
-                   f'-I{csrc}', *flags, cu, '-o', tmp, '-lcudart_static', '-lrt', '-lpthread', '-ldl']
-            res = subprocess.run(cmd, capture_output=True, text=True)
-            if res.returncode != 0:
-                raise RuntimeError(f'nvcc failed on the traced right-hand side:\n{res.stderr[-4000:]}')
-            os.replace(tmp, so)
-        rid = _REGISTERED.get(so)                 # one registration per shared object and process
-        if rid is None:
-            rid = nat.lib.oz_register_rhs_plugin(so.encode())
-            if rid < 0:
-                raise nat.OzError(f'oz_register_rhs_plugin: {nat.lib.oz_last_error().decode()}')
-            _REGISTERED[so] = rid
+        rid = build_and_register_plugin(self.cuda_source(), flags, 'oz_rhs', 'the traced right-hand side')
         self._plugins[key] = rid
         return rid
 

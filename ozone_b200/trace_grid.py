@@ -28,16 +28,12 @@ What the kernels can express, and what is refused with an error that says so:
 """
 from __future__ import annotations
 
-import hashlib
 import math
-import os
-import subprocess
 
 import numpy as np
 import torch
 
-from . import _native as nat
-from .trace import Expr, TVar, leaf, diff, _ACTIVE, PLUGIN_DIR, _REGISTERED, _HERE
+from .trace import Expr, TVar, leaf, diff, _ACTIVE, build_and_register_plugin
 
 _UNARY = {'exp': math.exp, 'log': math.log, 'sin': math.sin, 'cos': math.cos, 'tan': math.tan, 'tanh': math.tanh,
           'sqrt': math.sqrt, 'atan': math.atan, 'abs': abs}
@@ -626,36 +622,8 @@ struct GridTraced {{
         key = (num_stages, bool(fp64))
         if key in self._plugins:
             return self._plugins[key]
-        src = self.cuda_source()
         flags = [f'-DOZ_ONLY_S={num_stages}', f'-DOZ_ONLY_F64={int(fp64)}']
-        csrc = os.path.join(_HERE, 'csrc')
-        stamp = hashlib.sha256()
-        stamp.update(src.encode())
-        stamp.update(' '.join(flags).encode())
-        for fn in sorted(os.listdir(csrc)):                      # kernel templates are part of the plugin
-            if fn.endswith(('.cuh', '.h')):
-                stamp.update(open(os.path.join(csrc, fn), 'rb').read())
-        tag = stamp.hexdigest()[:20]
-        os.makedirs(PLUGIN_DIR, exist_ok=True)
-        so = os.path.join(PLUGIN_DIR, f'oz_grid_{tag}.so')
-        if not os.path.exists(so):
-            cu = os.path.join(PLUGIN_DIR, f'oz_grid_{tag}.{os.getpid()}.cu')
-            tmp = f'{so}.{os.getpid()}.tmp'
-            open(cu, 'w').write(src)
-            cmd = ['nvcc', '-gencode', 'arch=compute_100a,code=sm_100a', '-O3', '-std=c++17', '-lineinfo',
-                   '--expt-relaxed-constexpr', '-split-compile', '0', '-Xcompiler', '-fPIC', '-Xcompiler', '-fvisibility=hidden',
-                   '-shared',
-                   f'-I{csrc}', *flags, cu, '-o', tmp, '-lcudart_static', '-lrt', '-lpthread', '-ldl']
-            res = subprocess.run(cmd, capture_output=True, text=True)
-            if res.returncode != 0:
-                raise RuntimeError(f'nvcc failed on the traced grid right-hand side:\n{res.stderr[-4000:]}')
-            os.replace(tmp, so)
-        rid = _REGISTERED.get(so)
-        if rid is None:
-            rid = nat.lib.oz_register_rhs_plugin(so.encode())
-            if rid < 0:
-                raise nat.OzError(f'oz_register_rhs_plugin: {nat.lib.oz_last_error().decode()}')
-            _REGISTERED[so] = rid
+        rid = build_and_register_plugin(self.cuda_source(), flags, 'oz_grid', 'the traced grid right-hand side')
         self._plugins[key] = rid
         return rid
 
