@@ -47,7 +47,15 @@ def expand(x, shape, action=None):
         return GridVar(tr, _grid.Expr.wrap(v[0]), shape)
     if isinstance(x, TVar):
         return x.expand(shape, action)
+    from .trace import _ACTIVE
     if isinstance(x, torch.Tensor):
+        if not _ACTIVE:                                     # eager evaluation on plain tensors
+            if action is None:
+                return x.expand(tuple(shape)).clone()
+            src, dst = action.replace(' ', '').split('->')
+            view = x.permute([src.index(c) for c in dst if c in src])
+            view = view.reshape(tuple(view.shape[[c for c in dst if c in src].index(c)] if c in src else 1 for c in dst))
+            return view.expand(tuple(shape)).clone()
         return TVar(_arr(x)).expand(shape, action)          # captured tensor used inside a trace
     return TVar(np.asarray(x, dtype=object)).expand(shape, action)
 
@@ -61,7 +69,9 @@ def concatenate(xs, axis=0):
         return _grid.concatenate(xs, axis)
     if any(isinstance(x, TVar) for x in xs):
         return TVar(np.concatenate([_arr(x) for x in xs], axis=axis))
-    return torch.cat(list(xs), dim=axis)
+    ref = next(x for x in xs if isinstance(x, torch.Tensor))       # eager evaluation: numpy pieces join the tensors
+    return torch.cat([x if isinstance(x, torch.Tensor) else torch.as_tensor(np.asarray(x), dtype=ref.dtype, device=ref.device)
+                      for x in xs], dim=axis)
 
 
 def norm(x):

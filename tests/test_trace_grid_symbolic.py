@@ -24,7 +24,8 @@ def _evaluate(e, env):
         else:
             a = [go(y) for y in x.args]
             r = {'add': lambda: a[0] + a[1], 'sub': lambda: a[0] - a[1], 'mul': lambda: a[0] * a[1], 'div': lambda: a[0] / a[1],
-                 'neg': lambda: -a[0], 'powc': lambda: a[0] ** x.val, 'exp': lambda: math.exp(a[0])}[x.op]()
+                 'neg': lambda: -a[0], 'powc': lambda: a[0] ** x.val, 'exp': lambda: math.exp(a[0]), 'sin': lambda: math.sin(a[0]),
+                 'cos': lambda: math.cos(a[0]), 'log': lambda: math.log(a[0]), 'sqrt': lambda: math.sqrt(a[0])}[x.op]()
         memo[id(x)] = r
         return r
     return go(e)
@@ -223,3 +224,76 @@ def test_several_dynamic_parameters_each_get_their_own_weight_field():
         assert l.op == 'gc' and np.array_equal(tab[l.idx], fl[key] * (1.0 if q == 0 else -1.0))
     src = t.cuda_source()
     assert 'static constexpr int P = 2' in src and 'if (q == 1)' in src and 'u[1]' in src
+
+
+# ---------------------------------------------------------------- traced expression == eager evaluation of the same callback
+def _random_grid_callback(rng, nx):
+    """A stencil right-hand side drawn from what trace_grid.py accepts, written with ozone_b200.ops so that the SAME function
+    runs eagerly on torch tensors (the ground truth) and on a symbolic grid."""
+    cl, cr = rng.uniform(0.5, 2.0, 2)
+    fields = [rng.uniform(0.5, 1.5, nx) for _ in range(3)]
+    left_kind, right_kind = rng.integers(0, 3, 2)             # 0 zero ghost, 1 constant, 2 reflecting
+    lval, rval = rng.uniform(-1.0, 1.0, 2)
+    nonlin = int(rng.integers(0, 4))
+    var_weights = bool(rng.integers(0, 2))
+    two_params = bool(rng.integers(0, 2))
+
+    def f(ov):
+        x = ov.states['x'][0, :]
+        A = torch.as_tensor if isinstance(x, torch.Tensor) else (lambda a: a)      # eager run: per-cell arrays as tensors
+        lpad = {0: np.zeros(1), 1: np.full(1, lval), 2: x[:1]}[int(left_kind)]
+        rpad = {0: np.zeros(1), 1: np.full(1, rval), 2: x[-1:]}[int(right_kind)]
+        left, right = ops.concatenate((lpad, x[:-1])), ops.concatenate((x[1:], rpad))
+        w = A(fields[0]) if var_weights else 1.0
+        lin = (cl * left - (cl + cr) * x + cr * right) * w        # tensor operand first: the eager run mixes torch and numpy
+        centre = [lambda v: -v ** 3, lambda v: 2.0 * ops.exp(-1.5 / (1.0 + v * v)), lambda v: ops.sin(v) * v,
+                  lambda v: v / (2.0 + v * v)][nonlin](x)
+        u = ov.dynamic_parameters['u']
+        src = ops.expand(u[0], (nx,)) * A(fields[1])
+        if two_params:
+            src = src + ops.expand(ov.dynamic_parameters['v'][0], (nx,)) * A(0.5 * fields[2])
+        ov.d_states['x'] = (lin + centre + src).reshape(1, nx)
+        cost = 0.3 * ops.sum(x * x * A(fields[2])) + 0.7 * u[0] * u[0]
+        if two_params:
+            cost = cost + 0.2 * u[0] * ov.dynamic_parameters['v'][0]
+        ov.field_outputs['J'] = cost.reshape(1, 1)
+    return f, (['u', 'v'] if two_params else ['u'])
+
+
+@pytest.mark.parametrize('seed', range(12))
+def test_traced_grid_expression_equals_eager_evaluation_of_the_same_callback(seed):
+    from ozone_b200.func_wrapper import ODEVars
+    rng = np.random.default_rng(100 + seed)
+    nx = 24
+    f, params = _random_grid_callback(rng, nx)
+    t = TracedGridRHS(f, (), {}, 'x', nx, params)
+    x = rng.uniform(-0.8, 0.8, nx)
+    pv = rng.uniform(-1.0, 1.0, len(params))
+    ov = ODEVars({'x': torch.tensor(x).reshape(1, nx)}, {n: torch.tensor([[v]]) for n, v in zip(params, pv)}, 1)
+    f(ov)                                                           # eager: plain torch tensors
+    want_f = ov.d_states['x'].reshape(-1).numpy()
+    want_J = float(ov.field_outputs['J'])
+    tab = t.tracer.coefficient_table()
+    xe = np.concatenate(([0.0], x, [0.0]))
+    got_f, q_sum = np.empty(nx), 0.0
+    for k in range(nx):
+        env = {('gx', -1): xe[k], ('gx', 0): xe[k + 1], ('gx', 1): xe[k + 2]}
+        env.update({('p', q): float(v) for q, v in enumerate(pv)})
+        env.update({('gc', q): tab[q, k] for q in range(tab.shape[0])})
+        got_f[k] = _evaluate(t.f, env)
+        q_sum += _evaluate(t.q, env)
+    assert np.allclose(got_f, want_f, rtol=1e-13, atol=1e-13)
+    assert q_sum + _evaluate(t.r, {('p', q): float(v) for q, v in enumerate(pv)}) == pytest.approx(want_J, rel=1e-13)
+    # what the reverse sweep uses: the transposed stencil row by row against autograd of the eager evaluation
+    xt = torch.tensor(x, requires_grad=True)
+    ov = ODEVars({'x': xt.reshape(1, nx)}, {n: torch.tensor([[v]]) for n, v in zip(params, pv)}, 1)
+    f(ov)
+    G = rng.standard_normal(nx)
+    want_vjp, = torch.autograd.grad((ov.d_states['x'].reshape(-1) * torch.tensor(G)).sum(), [xt])
+    Ge = np.concatenate(([0.0], G, [0.0]))
+    for k in range(nx):
+        env = {('gx', -1): xe[k], ('gx', 0): xe[k + 1], ('gx', 1): xe[k + 2]}
+        env.update({('p', q): float(v) for q, v in enumerate(pv)})
+        env.update({('gc', q): tab[q, k] for q in range(tab.shape[0])})
+        got = (_evaluate(t.wr_of_left, env) * Ge[k] + _evaluate(t.dg, env) * Ge[k + 1] + _evaluate(t.wl_of_right, env) * Ge[k + 2])
+        assert got == pytest.approx(float(want_vjp[k]), rel=1e-11, abs=1e-12)
