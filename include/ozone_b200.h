@@ -207,7 +207,9 @@ OZ_API double oz_fma_probe(int dtype, int iters, void* out, void* stream);
 /* Register a right-hand side compiled separately (ozone_b200/trace.py turns a Python callback into CUDA
  * source and builds it against the same kernel templates).  `so_path` is a shared object exporting
  * `oz_plugin_describe`; returns the rhs_id to put in oz_problem.rhs_id (>= OZ_RHS_PLUGIN_BASE) or < 0.
- * This is what stands in for "any Python f" of ozone/func_wrapper.py:90-107. */
+ * This is what stands in for "any Python f" of ozone/func_wrapper.py:90-107.  Two kinds (oz_rhs_info reports which): one ODE per
+ * trajectory, or a grid model (ozone_b200/trace_grid.py, from a whole-grid callback like pde_control.py:11-81) that runs through
+ * the fused stencil kernels of the built-in diffusion-reaction system; a grid model's per-cell arrays are passed as `th`. */
 OZ_API int oz_register_rhs_plugin(const char* so_path);
 
 /* No counterpart in the reference (it has no distributed code).  Plumbing of the two multi-GPU paths over peer-mapped
