@@ -1,7 +1,7 @@
 """Grid right-hand sides written as ordinary Python callbacks, for the traced-grid tests.
 
-``pde_control`` follows the reference's example line by line (ozone/paper_examples/pde_control/pde_control.py:11-81) with
-``csdl`` replaced by ``ozone_b200.ops``; ``advection_diffusion`` is a second system that exercises what the first does
+``pde_control`` is the PDE of the reference's example (ozone/paper_examples/pde_control/pde_control.py:11-81) in this package's
+spelling (``tests/test_reference_source_pins.py`` checks it against the reference's own function, traced from its source); ``advection_diffusion`` is a second system that exercises what the first does
 not: an asymmetric stencil (upwind advection), a variable diffusivity (per-cell neighbour weights), a per-cell source
 weight, a nonlinear reaction without an exponential and a field output with a per-cell weight.  Each comes with a numpy
 restatement in the oracle's conventions (oracle.rhs.Rhs, derivatives by complex step)."""
@@ -12,50 +12,21 @@ from oracle.rhs import Rhs
 
 
 def pde_control(ozone_vars, dx, nx, zero_bc, pi_bc, beta_t, beta_u, gamma):
-    beta_t_g = beta_t * (np.exp(-gamma))
-    heaviside_array = np.zeros((nx, 1))
-    heaviside_array[round(0.3 * nx):round(0.7 * nx)] = 1.0
-    x = ozone_vars.states['x']
+    """The PDE of the reference's example (same arguments as its ``ode_function``), written the way a user of this package
+    would: x' = (x[k-1] - 2 x[k] + x[k+1]) / dx^2 + beta_t (e^(-gamma / (1 + x)) - e^(-gamma)) + beta_u (H u - x), zero ghost
+    cells, H = 1 on the middle 40 % of the grid; J_space = (100 / nx) sum x^2 + 20 u^2."""
+    window = np.zeros((nx, 1))
+    window[round(0.3 * nx):round(0.7 * nx)] = 1.0
+    x = csdl.reshape(ozone_vars.states['x'][0, :], (nx, 1))
     u = ozone_vars.dynamic_parameters['u']
-    nn = ozone_vars.num_nodes
-    dx_dts = []
-    for node in range(nn):
-        x_vec = csdl.reshape(x[node, :], (nx, 1))
-        zeros = np.zeros((1, 1))
-        x_vec0 = csdl.concatenate((zeros, x_vec[:-1, :]))
-        x_vec1 = csdl.concatenate((x_vec[1:, :], zeros))
-        dxdz2_without_bc_new = x_vec0 + (-2.0) * x_vec + x_vec1
-        dxdz2_without_bc = dxdz2_without_bc_new / (dx ** 2)
-        dx_dz2 = csdl.reshape(dxdz2_without_bc, (1, nx))
-        exp_term = -gamma * 1 * ((1 + x_vec) ** (-1))
-        reaction_src_b4_reshape = beta_t * (np.exp(1) ** exp_term) + (-1 * beta_t_g)
-        reaction_src = csdl.reshape(reaction_src_b4_reshape, (1, nx))
-        t_sub_term = (-beta_u) * x_vec
-        control_input = csdl.reshape(u[node], (1,))
-        t_src_term = (csdl.expand(control_input, (nx, 1))) * (beta_u * heaviside_array)
-        transfer_src_b4_reshape = t_src_term + t_sub_term
-        transfer_src = csdl.reshape(transfer_src_b4_reshape, (1, nx))
-        dx_dts.append((dx_dz2 + reaction_src + transfer_src).reshape(1, -1))
-    if nn == 1:
-        ozone_vars.d_states['x'] = dx_dts[0]
-    else:
-        ozone_vars.d_states['x'] = csdl.concatenate(dx_dts)
-    dx = 1.0 / nx
-    xnn = x
-    unn = u
-    Jss = []
-    for n in range(nn):
-        x = csdl.reshape(xnn[n, :], (nx,))
-        u = csdl.reshape(unn[n, :], (1,))
-        x2 = x * 1 * x
-        u2 = u * 1 * u
-        x_term = (dx * 100) * csdl.sum(x2)
-        u_term = (dx * nx * 20) * (u2)
-        Jss.append((x_term + u_term).reshape(1, 1))
-    if nn == 1:
-        ozone_vars.field_outputs['J_space'] = Jss[0]
-    else:
-        ozone_vars.field_outputs['J_space'] = csdl.concatenate(Jss)
+    ghost = np.zeros((1, 1))
+    second_difference = (csdl.concatenate((ghost, x[:-1, :])) + (-2.0) * x + csdl.concatenate((x[1:, :], ghost))) / dx ** 2
+    reaction = beta_t * (np.exp(1) ** (-gamma * ((1 + x) ** (-1)))) - beta_t * np.exp(-gamma)
+    transfer = csdl.expand(csdl.reshape(u[0], (1,)), (nx, 1)) * (beta_u * window) - beta_u * x
+    ozone_vars.d_states['x'] = (second_difference + reaction + transfer).reshape(1, -1)
+    cells = csdl.reshape(x, (nx,))
+    control = csdl.reshape(u[0, :], (1,))
+    ozone_vars.field_outputs['J_space'] = ((100.0 / nx) * csdl.sum(cells * cells) + 20.0 * (control * control)).reshape(1, 1)
 
 
 def advection_fields(nx):

@@ -32,8 +32,9 @@ def _solve_pde(function, nx, n, approach, u_np, **kw):
 
 
 @pytest.mark.parametrize('approach', ['history', 'checkpoints'])
-def test_the_reference_pde_callback_runs_like_the_built_in_model(approach):
-    # pde_control.py:84-143 scaled down; the callback is the reference's own text with csdl -> ozone_b200.ops
+def test_the_pde_example_as_a_callback_runs_like_the_built_in_model(approach):
+    # pde_control.py:84-143 scaled down; the callback is the example's PDE in this package's spelling (pinned on the reference's
+    # own function by tests/test_reference_source_pins.py)
     nx, n = 1500, 36
     u_np = np.random.default_rng(3).uniform(-0.6, 0.0, size=n + 1)
     mk = (lambda: TimeMarching()) if approach == 'history' else (lambda: TimeMarchingCheckpoints())

@@ -123,14 +123,24 @@ def _trace_grid(f, nx):
 
 
 @needs_reference
-def test_reference_pde_callback_and_its_test_copy_generate_the_same_grid_model():
+def test_reference_pde_callback_and_the_test_callback_are_the_same_grid_model():
+    """The reference's own ``ode_function`` (csdl bound to ozone_b200.ops) and the callback the GPU tests run: same coefficient
+    field, and the same cell expression, diagonal, neighbour weights, control weight and field-output integrand at random points."""
     from ozone_b200 import ops
     from tests import grid_callbacks as G
     nx = 90
     ref = _trace_grid(RS.reference_callback('pde_control', {'csdl': ops}), nx)
     ours = _trace_grid(G.pde_control, nx)
-    assert ref.cuda_source() == ours.cuda_source()
     assert np.array_equal(ref.tracer.coefficient_table(), ours.tracer.coefficient_table())
+    rng = np.random.default_rng(5)
+    for _ in range(10):
+        xl, x, xr, c, u = rng.uniform(0.05, 1.2, 5)
+        env = {('gx', -1): xl, ('gx', 0): x, ('gx', 1): xr, ('gc', 0): c, ('p', 0): u}
+        for name in ('f', 'dg', 'wr_of_left', 'wl_of_right', 'q', 'dq', 'r'):
+            a, b = evaluate(getattr(ref, name), env), evaluate(getattr(ours, name), env)
+            assert a == pytest.approx(b, rel=1e-13, abs=1e-13), name
+        assert evaluate(ref.du[0], env) == pytest.approx(evaluate(ours.du[0], env), rel=1e-14)
+        assert evaluate(ref.dr[0], env) == pytest.approx(evaluate(ours.dr[0], env), rel=1e-14)
 
 
 @needs_reference
